@@ -1,0 +1,1030 @@
+/*
+ * shopt_oracle.c -- CPU restatement (FP64, plain C) of ShOpt.jl's per-star PSF fitting stage.
+ * TEST INFRASTRUCTURE ONLY; see shopt_oracle.h.  PARITY UNPINNED (no reference fixtures exist).
+ *
+ * Build:  make -C oracle     (gcc -O2 -ffp-contract=off -fopenmp; no -ffast-math: the IEEE operation
+ *                             sequence of the scalar reparameterisation matters)
+ *
+ * Every function cites the reference lines it restates (paths relative to the reference checkout,
+ * e.g. shopt/analyticLBFGS.jl) or the appendix of SURVEY.md that records the un-vendored
+ * third-party algorithm (Optim 1.7.8, LineSearches 7.2.0, ForwardDiff 0.10.36,
+ * MultivariateStats 0.10.2, LinearAlgebra).
+ */
+#include "shopt_oracle.h"
+
+#include <float.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+/* ------------------------------------------------------------------------------------------ */
+/* ForwardDiff-style dual numbers with 3 partials (ForwardDiff.gradient on a length-3 vector   */
+/* uses one chunk of 3 partials; analyticLBFGS.jl:89-101).                                     */
+/* ------------------------------------------------------------------------------------------ */
+typedef struct { double v, d[3]; } dual;
+
+static inline dual d_const(double v) { dual r = { v, { 0, 0, 0 } }; return r; }
+static inline dual d_seed(double v, int i) { dual r = { v, { 0, 0, 0 } }; r.d[i] = 1.0; return r; }
+static inline dual d_add(dual a, dual b) { dual r; r.v = a.v + b.v; for (int i = 0; i < 3; i++) r.d[i] = a.d[i] + b.d[i]; return r; }
+static inline dual d_sub(dual a, dual b) { dual r; r.v = a.v - b.v; for (int i = 0; i < 3; i++) r.d[i] = a.d[i] - b.d[i]; return r; }
+static inline dual d_radd(double a, dual b) { b.v = a + b.v; return b; }
+static inline dual d_rsub(double a, dual b) { dual r; r.v = a - b.v; for (int i = 0; i < 3; i++) r.d[i] = -b.d[i]; return r; }
+static inline dual d_subr(dual a, double b) { a.v = a.v - b; return a; }
+static inline dual d_neg(dual a) { dual r; r.v = -a.v; for (int i = 0; i < 3; i++) r.d[i] = -a.d[i]; return r; }
+/* x*y : partials(x)*vy + partials(y)*vx */
+static inline dual d_mul(dual a, dual b) { dual r; r.v = a.v * b.v; for (int i = 0; i < 3; i++) r.d[i] = a.d[i] * b.v + b.d[i] * a.v; return r; }
+static inline dual d_rmul(double a, dual b) { dual r; r.v = a * b.v; for (int i = 0; i < 3; i++) r.d[i] = b.d[i] * a; return r; }
+/* x/y : partials(x)*inv(vy) + partials(y)*(-(vx/(vy*vy))) */
+static inline dual d_div(dual a, dual b) {
+    dual r; double ib = 1.0 / b.v, w = -(a.v / (b.v * b.v));
+    r.v = a.v / b.v; for (int i = 0; i < 3; i++) r.d[i] = a.d[i] * ib + b.d[i] * w; return r;
+}
+/* real/dual : divv = x/v ; partials = -(divv/v) * partials(y) */
+static inline dual d_rdiv(double a, dual b) {
+    dual r; double divv = a / b.v, w = -(divv / b.v);
+    r.v = divv; for (int i = 0; i < 3; i++) r.d[i] = w * b.d[i]; return r;
+}
+/* sqrt: DiffRules  inv(2*sqrt(x)) */
+static inline dual d_sqrt(dual a) {
+    dual r; r.v = sqrt(a.v); double w = 1.0 / (2.0 * r.v);
+    for (int i = 0; i < 3; i++) r.d[i] = w * a.d[i]; return r;
+}
+static inline dual d_exp(dual a) {
+    dual r; r.v = exp(a.v); for (int i = 0; i < 3; i++) r.d[i] = r.v * a.d[i]; return r;
+}
+/* literal x^2 on a Dual: value v*v, derivative (2*v) * partials */
+static inline dual d_sq(dual a) {
+    dual r; r.v = a.v * a.v; double w = 2.0 * a.v;
+    for (int i = 0; i < 3; i++) r.d[i] = w * a.d[i]; return r;
+}
+/* Float64 x^4 as Julia >= 1.8 computes it (Base.Math.pow_body: compensated power by squaring,
+ * error-free products through fma) -- this is not (x*x)*(x*x) in the last bit, and the e->g map
+ * amplifies that bit by 1/|e|^4. */
+static inline double pow4(double x) {
+    double x2 = x * x;
+    double lo2 = fma(x, x, -x2);          /* two_mul(x,x) low part           */
+    double err = x2 * 2.0 * lo2;          /* err = x*2*xnlo (second squaring) */
+    double x4 = x2 * x2;
+    double lo4 = fma(x2, x2, -x4) + err;
+    if (!isfinite(x4)) return x4;
+    return x4 + lo4;                      /* muladd(x, 1, muladd(1, xnlo, 0)) */
+}
+/* Dual ^ Integer (y = 4): value v^4 ; partials(x) * y * v^(y-1), v^3 = v*v*v */
+static inline dual d_pow4(dual a) {
+    dual r; r.v = pow4(a.v); double v3 = a.v * a.v * a.v;
+    for (int i = 0; i < 3; i++) r.d[i] = a.d[i] * 4.0 * v3; return r;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* radialProfiles.jl:5-9  fGaussian                                                            */
+/* ------------------------------------------------------------------------------------------ */
+double orc_fgaussian(double u, double v, double g1, double g2, double s, double uc, double vc) {
+    double du = u - uc, dv = v - vc;
+    double w1 = (1.0 + g1) * du + g2 * dv;        /* M*d, generic matvec order */
+    double w2 = g2 * du + (1.0 - g1) * dv;
+    double q = w1 * w1 + w2 * w2;                 /* (M d)' (M d)              */
+    double ms = (s * s) / (1.0 - g1 * g1 - g2 * g2);
+    return exp(-(ms * q));
+}
+static inline dual fgaussian_dual(double du, double dv, dual a11, dual g2, dual a22, dual ms) {
+    dual w1 = d_add(d_rmul(du, a11), d_rmul(dv, g2));
+    dual w2 = d_add(d_rmul(du, g2), d_rmul(dv, a22));
+    dual q = d_add(d_sq(w1), d_sq(w2));
+    return d_exp(d_neg(d_mul(ms, q)));
+}
+
+/* analyticLBFGS.jl:10-18 (and shopt.jl:145-153): [e1,e2] -> [g1,g2], op for op */
+void orc_e_to_g(double e1, double e2, double *g1, double *g2) {
+    double ell = sqrt(e1 * e1 + e2 * e2);
+    double ell2 = ell * ell;
+    double normG = sqrt(1.0 + 0.5 * ((1.0 / ell2) - sqrt((4.0 / ell2) + (1.0 / pow4(ell)))));
+    double ratio = ell / normG;
+    *g1 = e1 / ratio;
+    *g2 = e2 / ratio;
+}
+static void e_to_g_dual(dual e1, dual e2, dual *g1, dual *g2) {
+    dual ell = d_sqrt(d_add(d_sq(e1), d_sq(e2)));
+    dual ell2 = d_sq(ell);
+    dual inner = d_sqrt(d_add(d_rdiv(4.0, ell2), d_rdiv(1.0, d_pow4(ell))));
+    dual normG = d_sqrt(d_radd(1.0, d_rmul(0.5, d_sub(d_rdiv(1.0, ell2), inner))));
+    dual ratio = d_div(ell, normG);
+    *g1 = d_div(e1, ratio);
+    *g2 = d_div(e2, ratio);
+}
+
+/* get_middle_nxn dataPreprocessing.jl:207-216: 0-based start offset of the centre crop */
+static inline int crop_start(int n, int n_a) { return (n - n_a) / 2; }   /* div(rows-n,2)+1, 1-based */
+
+/* analyticLBFGS.jl:8-46  cost(params)  (costD :49-87 is the same function on pixelGridFits) */
+double orc_cost(const double *stamp, int r, int c, int n_a, const double x[3]) {
+    double sg = x[0] * x[0];
+    double g1, g2;
+    orc_e_to_g(x[1], x[2], &g1, &g2);
+    const int r0 = crop_start(r, n_a), c0 = crop_start(c, n_a);
+    const double uc = n_a / 2.0, vc = n_a / 2.0;
+    double sum = 0.0;
+    for (int u = 1; u <= n_a; u++)
+        for (int v = 1; v <= n_a; v++)
+            sum += orc_fgaussian(u, v, g1, g2, sg, uc, vc);
+    double A = 1.0 / sum;
+    double total = 0.0;
+    for (int u = 1; u <= n_a; u++)
+        for (int v = 1; v <= n_a; v++) {
+            double d = stamp[(size_t)(r0 + u - 1) + (size_t)(c0 + v - 1) * r];
+            if (isnan(d)) continue;
+            double t = A * orc_fgaussian(u, v, g1, g2, sg, uc, vc) - d;
+            total += 0.5 * (t * t);
+        }
+    return total;
+}
+
+/* analyticLBFGS.jl:89-94  g! = ForwardDiff.gradient(cost, p): the same code path on Dual{3} */
+static double grad_val(const double *stamp, int r, int c, int n_a, const double x[3], double g[3]) {
+    dual sig = d_seed(x[0], 0), e1 = d_seed(x[1], 1), e2 = d_seed(x[2], 2);
+    dual sg = d_sq(sig);
+    dual g1, g2;
+    e_to_g_dual(e1, e2, &g1, &g2);
+    dual a11 = d_radd(1.0, g1), a22 = d_rsub(1.0, g1);
+    dual ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
+    const int r0 = crop_start(r, n_a), c0 = crop_start(c, n_a);
+    const double uc = n_a / 2.0, vc = n_a / 2.0;
+    dual sum = d_const(0.0);
+    for (int u = 1; u <= n_a; u++)
+        for (int v = 1; v <= n_a; v++)
+            sum = d_add(sum, fgaussian_dual(u - uc, v - vc, a11, g2, a22, ms));
+    dual A = d_rdiv(1.0, sum);
+    dual total = d_const(0.0);
+    for (int u = 1; u <= n_a; u++)
+        for (int v = 1; v <= n_a; v++) {
+            double d = stamp[(size_t)(r0 + u - 1) + (size_t)(c0 + v - 1) * r];
+            if (isnan(d)) continue;
+            dual t = d_subr(d_mul(A, fgaussian_dual(u - uc, v - vc, a11, g2, a22, ms)), d);
+            total = d_add(total, d_rmul(0.5, d_sq(t)));
+        }
+    g[0] = total.d[0]; g[1] = total.d[1]; g[2] = total.d[2];
+    return total.v;
+}
+void orc_grad(const double *stamp, int r, int c, int n_a, const double x[3], double g[3]) {
+    (void)grad_val(stamp, r, c, n_a, x, g);
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* Optim.optimize(cost, g!, x0, LBFGS(), Options(g_tol)) -- shopt.jl:139-143 / 367-371.        */
+/* Optim 1.7.8 + LineSearches 7.2.0 (HagerZhang, InitialStatic) + NLSolversBase 7.8.3 are not  */
+/* vendored in the reference; the algorithm restated here is recorded in SURVEY.md A.1 / A.2.  */
+/* ------------------------------------------------------------------------------------------ */
+static int g_reference_shaped = 0;   /* 1: run the separate f(x) pass like NLSolversBase's fg! does */
+void orc_set_reference_shaped(int on) { g_reference_shaped = on; }
+
+typedef struct {
+    const double *stamp; int r, c, n_a;
+    double x[3], s[3];           /* line-search base point and direction              */
+    double xl[3], fl, gl[3];     /* last evaluated point (NLSolversBase caches by x)   */
+    int have_last;
+    int nevals, ntrials;
+} evalctx;
+
+/* value_gradient!(d, x): g! (dual pass) then f(x).  The dual pass's value channel executes the
+ * same IEEE operation sequence as cost(), so the separate pass is only repeated when timing the
+ * reference-shaped baseline. */
+static void eval_fg(evalctx *E, const double xn[3], double *f, double g[3]) {
+    if (E->have_last && xn[0] == E->xl[0] && xn[1] == E->xl[1] && xn[2] == E->xl[2]) {
+        *f = E->fl; g[0] = E->gl[0]; g[1] = E->gl[1]; g[2] = E->gl[2];
+        return;
+    }
+    *f = grad_val(E->stamp, E->r, E->c, E->n_a, xn, g);
+    if (g_reference_shaped) *f = orc_cost(E->stamp, E->r, E->c, E->n_a, xn);
+    E->nevals++;
+    E->xl[0] = xn[0]; E->xl[1] = xn[1]; E->xl[2] = xn[2];
+    E->fl = *f; E->gl[0] = g[0]; E->gl[1] = g[1]; E->gl[2] = g[2];
+    E->have_last = 1;
+}
+static inline double dot3(const double a[3], const double b[3]) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
+/* LineSearches.make_phi_phidphi: x_new = x + alpha*s ; (f, dot(g, s)) */
+static void phidphi(evalctx *E, double alpha, double *phi, double *dphi) {
+    double xn[3], g[3];
+    for (int i = 0; i < 3; i++) xn[i] = E->x[i] + alpha * E->s[i];
+    eval_fg(E, xn, phi, g);
+    *dphi = dot3(g, E->s);
+    E->ntrials++;
+}
+
+static inline double eps_of(double b) {            /* Julia eps(x::Float64) */
+    double a = fabs(b);
+    if (!isfinite(a)) return NAN;
+    if (a < DBL_MIN) return 4.9406564584124654e-324;
+    int e; (void)frexp(a, &e);
+    return ldexp(DBL_EPSILON, e - 1);
+}
+static inline double nextfloat_(double x) { return nextafter(x, INFINITY); }
+
+#define HZ_OK 0
+#define HZ_LSEXC 1     /* LineSearchException(alpha) : Optim takes the step alpha and stops */
+#define HZ_ERROR 2     /* @assert / error() : propagates to shopt.jl's catch              */
+#define HZ_MAXPTS 4096
+
+typedef struct {
+    double al[HZ_MAXPTS], va[HZ_MAXPTS], sl[HZ_MAXPTS];
+    int n;
+    double phi_lim;
+    evalctx *E;
+    int err;
+} hzstate;
+
+static int hz_push(hzstate *H, double a, double v, double s) {
+    if (H->n >= HZ_MAXPTS) { H->err = 1; return H->n - 1; }
+    H->al[H->n] = a; H->va[H->n] = v; H->sl[H->n] = s;
+    return H->n++;
+}
+static inline int hz_wolfe(double c, double phi_c, double dphi_c, double phi_0, double dphi_0,
+                           double phi_lim, double delta, double sigma) {
+    int wolfe1 = (delta * dphi_0 >= (phi_c - phi_0) / c) && (dphi_c >= sigma * dphi_0);
+    int wolfe2 = ((2.0 * delta - 1.0) * dphi_0 >= dphi_c) && (dphi_c >= sigma * dphi_0) && (phi_c <= phi_lim);
+    return wolfe1 || wolfe2;
+}
+/* HZ stage U3 (theta = 1/2).  Indices are 0-based into the point arrays. */
+static void hz_bisect(hzstate *H, int ia, int ib, int *oa, int *ob) {
+    double a = H->al[ia], b = H->al[ib];
+    if (!(H->sl[ia] < 0.0) || !(H->va[ia] <= H->phi_lim) || !(H->sl[ib] < 0.0) ||
+        !(H->va[ib] > H->phi_lim) || !(b > a)) { H->err = 1; *oa = ia; *ob = ib; return; }
+    while (b - a > eps_of(b)) {
+        double d = (a + b) / 2.0, phi_d, g;
+        phidphi(H->E, d, &phi_d, &g);
+        if (!(isfinite(phi_d) && isfinite(g))) { H->err = 1; break; }
+        int id = hz_push(H, d, phi_d, g);
+        if (H->err) break;
+        if (g >= 0.0) { *oa = ia; *ob = id; return; }
+        if (phi_d <= H->phi_lim) { a = d; ia = id; } else { b = d; ib = id; }
+    }
+    *oa = ia; *ob = ib;
+}
+/* HZ stages U0-U3 */
+static void hz_update(hzstate *H, int ia, int ib, int ic, int *oa, int *ob) {
+    double a = H->al[ia], b = H->al[ib];
+    if (!(H->sl[ia] < 0.0) || !(H->va[ia] <= H->phi_lim) || !(H->sl[ib] >= 0.0) || !(b > a)) {
+        H->err = 1; *oa = ia; *ob = ib; return;
+    }
+    double c = H->al[ic], phi_c = H->va[ic], dphi_c = H->sl[ic];
+    if (c < a || c > b) { *oa = ia; *ob = ib; return; }
+    if (dphi_c >= 0.0) { *oa = ia; *ob = ic; return; }
+    if (phi_c <= H->phi_lim) { *oa = ic; *ob = ib; return; }
+    hz_bisect(H, ia, ic, oa, ob);
+}
+static inline double hz_secant(double a, double b, double dphi_a, double dphi_b) {
+    return (a * dphi_b - b * dphi_a) / (dphi_b - dphi_a);
+}
+/* HZ stages S1-S4.  returns iswolfe */
+static int hz_secant2(hzstate *H, int ia, int ib, double delta, double sigma, int *oA, int *oB) {
+    double phi_0 = H->va[0], dphi_0 = H->sl[0];
+    double a = H->al[ia], b = H->al[ib], dphi_a = H->sl[ia], dphi_b = H->sl[ib];
+    *oA = ia; *oB = ib;
+    if (!(dphi_a < 0.0 && dphi_b >= 0.0)) { H->err = 1; return 0; }
+    double c = hz_secant(a, b, dphi_a, dphi_b);
+    if (!isfinite(c)) { H->err = 1; return 0; }
+    double phi_c, dphi_c;
+    phidphi(H->E, c, &phi_c, &dphi_c);
+    if (!(isfinite(phi_c) && isfinite(dphi_c))) { H->err = 1; return 0; }
+    int ic = hz_push(H, c, phi_c, dphi_c);
+    if (H->err) return 0;
+    if (hz_wolfe(c, phi_c, dphi_c, phi_0, dphi_0, H->phi_lim, delta, sigma)) { *oA = ic; *oB = ic; return 1; }
+    int iA, iB;
+    hz_update(H, ia, ib, ic, &iA, &iB);
+    if (H->err) return 0;
+    a = H->al[iA]; b = H->al[iB];
+    if (iB == ic)      c = hz_secant(H->al[ib], H->al[iB], H->sl[ib], H->sl[iB]);
+    else if (iA == ic) c = hz_secant(H->al[ia], H->al[iA], H->sl[ia], H->sl[iA]);
+    if ((iA == ic || iB == ic) && a <= c && c <= b) {
+        phidphi(H->E, c, &phi_c, &dphi_c);
+        if (!(isfinite(phi_c) && isfinite(dphi_c))) { H->err = 1; return 0; }
+        ic = hz_push(H, c, phi_c, dphi_c);
+        if (H->err) return 0;
+        if (hz_wolfe(c, phi_c, dphi_c, phi_0, dphi_0, H->phi_lim, delta, sigma)) { *oA = ic; *oB = ic; return 1; }
+        int jA, jB;
+        hz_update(H, iA, iB, ic, &jA, &jB);
+        if (H->err) return 0;
+        iA = jA; iB = jB;
+    }
+    *oA = iA; *oB = iB;
+    return 0;
+}
+
+/* HagerZhang()(phi, phidphi, c, phi_0, dphi_0) with the LineSearches 7.2.0 defaults
+ * delta=.1 sigma=.9 alphamax=Inf rho=5 epsilon=1e-6 gamma=.66 linesearchmax=50 psi3=.1,
+ * mayterminate=false (InitialStatic never sets it). */
+static int hager_zhang(evalctx *E, double c, double phi_0, double dphi_0, double *alpha_out) {
+    const double delta = 0.1, sigma = 0.9, rho = 5.0, epsilon = 1e-6, gamma = 0.66, psi3 = 0.1;
+    const int linesearchmax = 50;
+    double alphamax = INFINITY;
+    *alpha_out = 0.0;
+    if (!(isfinite(phi_0) && isfinite(dphi_0))) return HZ_LSEXC;
+    if (dphi_0 >= DBL_EPSILON * fabs(phi_0)) return HZ_LSEXC;
+    else if (dphi_0 >= 0.0) return HZ_OK;
+    const int iterfinitemax = 52;            /* ceil(-log2(eps(Float64))) */
+    static _Thread_local hzstate Hs;
+    hzstate *H = &Hs;
+    H->n = 0; H->E = E; H->err = 0;
+    hz_push(H, 0.0, phi_0, dphi_0);
+    H->phi_lim = phi_0 + epsilon * fabs(phi_0);
+    if (!(c >= 0.0)) return HZ_ERROR;
+    if (c <= DBL_EPSILON) return HZ_OK;
+    if (!(isfinite(c) && c <= alphamax)) return HZ_ERROR;
+    double phi_c, dphi_c;
+    phidphi(E, c, &phi_c, &dphi_c);
+    int iterfinite = 1;
+    while (!(isfinite(phi_c) && isfinite(dphi_c)) && iterfinite < iterfinitemax) {
+        iterfinite++;
+        c *= psi3;
+        phidphi(E, c, &phi_c, &dphi_c);
+    }
+    if (!(isfinite(phi_c) && isfinite(dphi_c))) return HZ_OK;      /* alpha = 0 */
+    hz_push(H, c, phi_c, dphi_c);
+    /* bracketing, HZ stages B0-B3 */
+    int isbracketed = 0, ia = 0, ib = 1, iter = 1;
+    double cold = -1.0;
+    while (!isbracketed && iter < linesearchmax) {
+        if (dphi_c >= 0.0) {
+            ib = H->n - 1;
+            for (int i = ib - 1; i >= 0; i--)
+                if (H->va[i] <= H->phi_lim) { ia = i; break; }
+            isbracketed = 1;
+        } else if (H->va[H->n - 1] > H->phi_lim) {
+            ib = H->n - 1; ia = 0;
+            int na, nb;
+            hz_bisect(H, ia, ib, &na, &nb);
+            if (H->err) return HZ_ERROR;
+            ia = na; ib = nb;
+            isbracketed = 1;
+        } else {
+            cold = c;
+            if (nextfloat_(cold) >= alphamax) { *alpha_out = cold; return HZ_OK; }
+            c *= rho;
+            if (c > alphamax) c = alphamax;
+            phidphi(E, c, &phi_c, &dphi_c);
+            iterfinite = 1;
+            while (!(isfinite(phi_c) && isfinite(dphi_c)) && c > nextfloat_(cold) && iterfinite < iterfinitemax) {
+                alphamax = c;
+                iterfinite++;
+                c = (cold + c) / 2.0;
+                phidphi(E, c, &phi_c, &dphi_c);
+            }
+            if (!(isfinite(phi_c) && isfinite(dphi_c))) { *alpha_out = cold; return HZ_OK; }
+            hz_push(H, c, phi_c, dphi_c);
+            if (H->err) return HZ_ERROR;
+        }
+        iter++;
+    }
+    while (iter < linesearchmax) {
+        double a = H->al[ia], b = H->al[ib];
+        if (!(b > a)) return HZ_ERROR;
+        if (b - a <= eps_of(b)) { *alpha_out = a; return HZ_OK; }
+        int iA, iB;
+        int iswolfe = hz_secant2(H, ia, ib, delta, sigma, &iA, &iB);
+        if (H->err) return HZ_ERROR;
+        if (iswolfe) { *alpha_out = H->al[iA]; return HZ_OK; }
+        double A = H->al[iA], B = H->al[iB];
+        if (!(B > A)) return HZ_ERROR;
+        if (B - A < gamma * (b - a)) {
+            if (nextfloat_(H->va[ia]) >= H->va[ib] && nextfloat_(H->va[iA]) >= H->va[iB]) {
+                *alpha_out = A; return HZ_OK;
+            }
+            ia = iA; ib = iB;
+        } else {
+            c = (A + B) / 2.0;
+            phidphi(E, c, &phi_c, &dphi_c);
+            if (!(isfinite(phi_c) && isfinite(dphi_c))) return HZ_ERROR;
+            int ic = hz_push(H, c, phi_c, dphi_c);
+            if (H->err) return HZ_ERROR;
+            int na, nb;
+            hz_update(H, iA, iB, ic, &na, &nb);
+            if (H->err) return HZ_ERROR;
+            ia = na; ib = nb;
+        }
+        iter++;
+    }
+    *alpha_out = H->al[ia];
+    return HZ_LSEXC;
+}
+
+/* Optim 1.7.8 LBFGS (m=10, scaleinvH0=true, flat manifold, identity preconditioner) driven by the
+ * generic optimize() loop; SURVEY.md A.1.  Post-processing shopt.jl:145-153. */
+int orc_lbfgs_fit(const double *stamp, int r, int c, int n_a, const double x0[3],
+                  double g_tol, int max_iter, double out_x[3], double out_p[3], int counts[3]) {
+    enum { M = 10 };
+    evalctx E; memset(&E, 0, sizeof E);
+    E.stamp = stamp; E.r = r; E.c = c; E.n_a = n_a;
+    double x[3] = { x0[0], x0[1], x0[2] }, x_prev[3], g[3], g_prev[3], s[3], dx[3], dg[3];
+    double dxh[M][3], dgh[M][3], rho[M], tl_alpha[M];
+    double f, f_prev = NAN;
+    int pseudo = 0, iteration = 0, counter_f_tol = 0, status;
+    eval_fg(&E, x, &f, g);
+    int g_conv0 = fmax(fmax(fabs(g[0]), fabs(g[1])), fabs(g[2])) <= g_tol;
+    int stopped0 = !isfinite(f) || !isfinite(g[0]) || !isfinite(g[1]) || !isfinite(g[2]);
+    int converged = g_conv0 || stopped0;
+    status = stopped0 ? ORC_FIT_NONFINITE : ORC_FIT_CONVERGED;
+    int broke = 0;
+    while (!converged && iteration < max_iter) {
+        iteration++;
+        /* update_state!: two-loop recursion */
+        pseudo++;
+        {
+            int lower = pseudo - M, upper = pseudo - 1;
+            double q[3] = { g[0], g[1], g[2] };
+            for (int index = upper; index >= lower; index--) {
+                if (index < 1) continue;
+                int i = (index - 1) % M;
+                tl_alpha[i] = rho[i] * dot3(dxh[i], q);
+                for (int k = 0; k < 3; k++) q[k] -= tl_alpha[i] * dgh[i][k];
+            }
+            if (pseudo > 1) {
+                int i = (upper - 1) % M;
+                double scaling = dot3(dxh[i], dgh[i]) / (dgh[i][0] * dgh[i][0] + dgh[i][1] * dgh[i][1] + dgh[i][2] * dgh[i][2]);
+                for (int k = 0; k < 3; k++) s[k] = scaling * q[k];
+            } else {
+                for (int k = 0; k < 3; k++) s[k] = q[k];
+            }
+            for (int index = lower; index <= upper; index++) {
+                if (index < 1) continue;
+                int i = (index - 1) % M;
+                double beta = rho[i] * dot3(dgh[i], s);
+                for (int k = 0; k < 3; k++) s[k] += dxh[i][k] * (tl_alpha[i] - beta);
+            }
+            for (int k = 0; k < 3; k++) s[k] = -1.0 * s[k];
+        }
+        for (int k = 0; k < 3; k++) g_prev[k] = g[k];
+        /* perform_linesearch! */
+        double dphi_0 = dot3(g, s);
+        if (dphi_0 >= 0.0) {                       /* reset_search_direction! */
+            pseudo = 1;
+            for (int k = 0; k < 3; k++) s[k] = -g[k];
+            dphi_0 = dot3(g, s);
+        }
+        double phi_0 = f;
+        f_prev = phi_0;
+        for (int k = 0; k < 3; k++) { x_prev[k] = x[k]; E.x[k] = x[k]; E.s[k] = s[k]; }
+        double alpha = 1.0;                        /* InitialStatic(alpha = 1.0, scaled = false) */
+        int hz = hager_zhang(&E, alpha, phi_0, dphi_0, &alpha);
+        if (hz == HZ_ERROR) { status = ORC_FIT_THREW; broke = 1; break; }
+        for (int k = 0; k < 3; k++) { dx[k] = alpha * s[k]; x[k] = x[k] + dx[k]; }
+        if (hz == HZ_LSEXC) { status = ORC_FIT_LS_FAILED; broke = 1; break; }
+        /* update_g! */
+        eval_fg(&E, x, &f, g);
+        /* assess_convergence (x_abstol = x_reltol = f_abstol = f_reltol = 0) */
+        double xchg = fmax(fmax(fabs(x[0] - x_prev[0]), fabs(x[1] - x_prev[1])), fabs(x[2] - x_prev[2]));
+        int x_conv = xchg <= 0.0;
+        int f_conv = fabs(f - f_prev) <= 0.0;
+        int g_conv = fmax(fmax(fabs(g[0]), fabs(g[1])), fabs(g[2])) <= g_tol;
+        counter_f_tol = f_conv ? counter_f_tol + 1 : 0;
+        converged = x_conv || g_conv || (counter_f_tol > 1);
+        /* update_h! */
+        for (int k = 0; k < 3; k++) dg[k] = g[k] - g_prev[k];
+        double rho_it = 1.0 / dot3(dx, dg);
+        if (isinf(rho_it)) {
+            pseudo = 0;
+        } else {
+            int idx = (pseudo - 1) % M;
+            for (int k = 0; k < 3; k++) { dxh[idx][k] = dx[k]; dgh[idx][k] = dg[k]; }
+            rho[idx] = rho_it;
+        }
+        if (!isfinite(g[0]) || !isfinite(g[1]) || !isfinite(g[2])) { status = ORC_FIT_NONFINITE; broke = 1; break; }
+    }
+    if (!broke && !(g_conv0 || stopped0)) status = converged ? ORC_FIT_CONVERGED : ORC_FIT_MAXITER;
+    out_x[0] = x[0]; out_x[1] = x[1]; out_x[2] = x[2];
+    if (status == ORC_FIT_THREW) {
+        out_p[0] = out_p[1] = out_p[2] = 0.0;           /* shopt.jl:155-162 catch */
+    } else {
+        out_p[0] = x[0] * x[0];
+        orc_e_to_g(x[1], x[2], &out_p[1], &out_p[2]);
+    }
+    if (counts) { counts[0] = iteration; counts[1] = E.nevals; counts[2] = E.ntrials; }
+    return status;
+}
+
+int orc_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+/* shopt.jl:130-164 / 357-397 */
+void orc_fit_analytic_batch(const double *stamps, int r, int c, int64_t N, int n_a,
+                            const double *x0, double g_tol, int max_iter,
+                            double *s, double *g1, double *g2, int32_t *status, int32_t *iters,
+                            int nthreads) {
+    if (nthreads < 1) nthreads = 1;
+    #pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads)
+    for (int64_t i = 0; i < N; i++) {
+        double ox[3], op[3]; int cnt[3];
+        int st = orc_lbfgs_fit(stamps + (size_t)i * r * c, r, c, n_a, x0 + 3 * i, g_tol, max_iter, ox, op, cnt);
+        s[i] = op[0]; g1[i] = op[1]; g2[i] = op[2];
+        if (status) status[i] = st;
+        if (iters) iters[i] = cnt[0];
+    }
+}
+
+/* shopt.jl:166-171, 384-386 */
+int64_t orc_s_out_of_bounds(const double *s, int64_t N, double s_lo, double s_hi, int64_t *idx) {
+    int64_t n = 0;
+    for (int64_t i = 0; i < N; i++)
+        if (s[i] < s_lo || s[i] > s_hi) idx[n++] = i;
+    return n;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* Pixel-grid fit: masks.jl:38-50, pca.jl:1-18 (MultivariateStats 0.10.2 fit/transform/        */
+/* reconstruct), dataPreprocessing.jl:94-139 (sinc, lanczos_kernel, smooth).    */
+/* ------------------------------------------------------------------------------------------ */
+void orc_nan_to_zero(const double *in, int64_t n, double *out) {
+    for (int64_t i = 0; i < n; i++) out[i] = isnan(in[i]) ? 0.001 : in[i];   /* masks.jl:43 : 0.001, not 0 */
+}
+
+/* Base pairwise sum (mapreduce_impl, block 1024) -- used where the reference calls sum()/mean() on
+ * a whole matrix */
+static double pairwise_sum(const double *a, int64_t n) {
+    if (n <= 1024) { double s = 0.0; for (int64_t i = 0; i < n; i++) s += a[i]; return s; }
+    int64_t h = n >> 1;
+    return pairwise_sum(a, h) + pairwise_sum(a + h, n - h);
+}
+
+/* One-sided (Hestenes) Jacobi on the columns of W (m x n, column-major): on return the columns
+ * are sigma_j * u_j.  Chosen for the oracle because it is the most accurate dense SVD there is;
+ * tests/ cross-check it against LAPACK (numpy.linalg.svd). */
+static void hestenes_columns(double *W, int m, int n) {
+    const double tol = DBL_EPSILON;
+    for (int sweep = 0; sweep < 60; sweep++) {
+        int rotated = 0;
+        for (int p = 0; p < n - 1; p++) {
+            double *cp = W + (size_t)p * m;
+            for (int q = p + 1; q < n; q++) {
+                double *cq = W + (size_t)q * m;
+                double alpha = 0, beta = 0, gamma = 0;
+                for (int i = 0; i < m; i++) { alpha += cp[i] * cp[i]; beta += cq[i] * cq[i]; gamma += cp[i] * cq[i]; }
+                if (alpha == 0.0 || beta == 0.0) continue;
+                if (fabs(gamma) <= tol * sqrt(alpha) * sqrt(beta)) continue;
+                rotated = 1;
+                double zeta = (beta - alpha) / (2.0 * gamma);
+                double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                double cs = 1.0 / sqrt(1.0 + t * t), sn = cs * t;
+                for (int i = 0; i < m; i++) {
+                    double a = cp[i], b = cq[i];
+                    cp[i] = cs * a - sn * b;
+                    cq[i] = sn * a + cs * b;
+                }
+            }
+        }
+        if (!rotated) break;
+    }
+}
+
+/* pca.jl:1-18.  X is r x c: rows are variables (d = r), columns observations (n = c).
+ * returns 0, or 1 when the input is not finite (LAPACK would raise -> shopt.jl:305 catch). */
+int orc_pca_image(const double *X, int r, int c, int ncomp, double pratio, double *out, int *k_out) {
+    const size_t rc = (size_t)r * c;
+    for (size_t i = 0; i < rc; i++) if (!isfinite(X[i])) return 1;
+    double *mu = (double *)malloc(sizeof(double) * r);
+    double *Z = (double *)malloc(sizeof(double) * rc);
+    double *W = (double *)malloc(sizeof(double) * rc);
+    double *sv = (double *)malloc(sizeof(double) * c);
+    int *ord = (int *)malloc(sizeof(int) * c);
+    for (int i = 0; i < r; i++) {                       /* mean(X, dims=2): sequential over columns */
+        double s = 0.0;
+        for (int j = 0; j < c; j++) s += X[i + (size_t)j * r];
+        mu[i] = s / c;
+    }
+    for (int j = 0; j < c; j++)
+        for (int i = 0; i < r; i++) Z[i + (size_t)j * r] = X[i + (size_t)j * r] - mu[i];
+    memcpy(W, Z, sizeof(double) * rc);
+    hestenes_columns(W, r, c);
+    const int m = r < c ? r : c;                        /* number of principal values */
+    for (int j = 0; j < c; j++) {
+        double s = 0.0;
+        for (int i = 0; i < r; i++) s += W[i + (size_t)j * r] * W[i + (size_t)j * r];
+        sv[j] = s;                                      /* sigma_j^2 */
+        ord[j] = j;
+    }
+    for (int a = 1; a < c; a++) {                       /* stable insertion sort, descending */
+        int oj = ord[a]; double key = sv[oj]; int b = a - 1;
+        while (b >= 0 && sv[ord[b]] < key) { ord[b + 1] = ord[b]; b--; }
+        ord[b + 1] = oj;
+    }
+    /* v = S.^2/(n-1); vsum = sum(v); choose_pcadim */
+    double vsum = 0.0;
+    for (int j = 0; j < m; j++) vsum += sv[ord[j]] / (c - 1);
+    int k = 1;
+    double acc = sv[ord[0]] / (c - 1);
+    const double thres = vsum * pratio;
+    while (k < m && k < ncomp && acc < thres) { acc += sv[ord[k]] / (c - 1); k++; }
+    /* reconstruct(M, transform(M, X)) = P (P' Z) + mean */
+    double *Y = (double *)malloc(sizeof(double) * (size_t)k * c);
+    for (int a = 0; a < k; a++) {
+        double *ua = W + (size_t)ord[a] * r;
+        double nrm = sqrt(sv[ord[a]]);
+        if (nrm > 0) for (int i = 0; i < r; i++) ua[i] /= nrm;
+        for (int j = 0; j < c; j++) {
+            double s = 0.0;
+            for (int i = 0; i < r; i++) s += ua[i] * Z[i + (size_t)j * r];
+            Y[a + (size_t)j * k] = s;
+        }
+    }
+    for (int j = 0; j < c; j++)
+        for (int i = 0; i < r; i++) {
+            double s = 0.0;
+            for (int a = 0; a < k; a++) s += W[i + (size_t)ord[a] * r] * Y[a + (size_t)j * k];
+            out[i + (size_t)j * r] = s + mu[i];
+        }
+    if (k_out) *k_out = k;
+    free(Y); free(ord); free(sv); free(W); free(Z); free(mu);
+    return 0;
+}
+
+/* dataPreprocessing.jl:94-110 */
+static double sinc_(double x) { return x == 0 ? 1.0 : sin(x) / x; }
+static double lanczos_(double x, int a) {
+    if (fabs(x) >= a) return 0.0;
+    if (x == 0) return 1.0;
+    return a * sinc_(M_PI * x) * sinc_(M_PI * x / a);
+}
+void orc_lanczos_kernel2d(int a, double *kernel) {
+    const int w = 2 * a + 1;
+    double sum = 0.0;
+    for (int j = 0; j < w; j++)
+        for (int i = 0; i < w; i++) { kernel[i + j * w] = lanczos_(i - a, a) * lanczos_(j - a, a); }
+    for (int i = 0; i < w * w; i++) sum += kernel[i];
+    for (int i = 0; i < w * w; i++) kernel[i] /= sum;
+}
+/* dataPreprocessing.jl:112-139 */
+void orc_smooth(const double *in, int nx, int ny, int a, double *out) {
+    const int w = 2 * a + 1;
+    double *kernel = (double *)malloc(sizeof(double) * w * w);
+    orc_lanczos_kernel2d(a, kernel);
+    memcpy(out, in, sizeof(double) * (size_t)nx * ny);
+    for (int i = 1; i <= nx; i++)
+        for (int j = 1; j <= ny; j++) {
+            if (isnan(in[(i - 1) + (size_t)(j - 1) * nx])) continue;
+            double norm = 0.0, val = 0.0;
+            int dlo = i - a < 1 ? 1 : i - a, dhi = i + a > nx ? nx : i + a;
+            int elo = j - a < 1 ? 1 : j - a, ehi = j + a > ny ? ny : j + a;
+            for (int di = dlo; di <= dhi; di++)
+                for (int dj = elo; dj <= ehi; dj++) {
+                    double d = in[(di - 1) + (size_t)(dj - 1) * nx];
+                    if (!isnan(d)) {
+                        double kk = kernel[(di - i + a) + (dj - j + a) * w];
+                        val += kk * d;
+                        norm += kk;
+                    }
+                }
+            out[(i - 1) + (size_t)(j - 1) * nx] = val / norm;
+        }
+    free(kernel);
+}
+
+/* shopt.jl:281-314 (mode == "PCA").  unity_sum=true: the 1-argument smooth() call at :292 raises a
+ * MethodError, so the inner catch (:295) yields pca ./ sum(pca) without smoothing. */
+void orc_pixel_grid_pca_batch(const double *stamps, int r, int c, int64_t N, int ncomp, double pratio,
+                              int lanczos_a, int unity_sum, double *pgf, int32_t *k_out,
+                              int32_t *status, int nthreads) {
+    if (nthreads < 1) nthreads = 1;
+    const size_t rc = (size_t)r * c;
+    #pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
+    for (int64_t i = 0; i < N; i++) {
+        double *data = (double *)malloc(sizeof(double) * rc);
+        double *rec = (double *)malloc(sizeof(double) * rc);
+        double *dst = pgf + (size_t)i * rc;
+        int k = 0;
+        orc_nan_to_zero(stamps + (size_t)i * rc, (int64_t)rc, data);
+        int fail = orc_pca_image(data, r, c, ncomp, pratio, rec, &k);
+        if (fail) {
+            memset(dst, 0, sizeof(double) * rc);          /* shopt.jl:305-309 */
+            k = 0;
+        } else if (unity_sum) {
+            double s = pairwise_sum(rec, (int64_t)rc);
+            for (size_t p = 0; p < rc; p++) dst[p] = rec[p] / s;
+        } else {
+            orc_smooth(rec, r, c, lanczos_a, dst);
+        }
+        if (k_out) k_out[i] = k;
+        if (status) status[i] = fail;
+        free(rec); free(data);
+    }
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* Interpolation: interpolate.jl:89-147, shopt.jl:472-577, reader.jl:40-68.                     */
+/* ------------------------------------------------------------------------------------------ */
+int orc_num_terms(int degree) { return (degree + 1) * (degree + 2) / 2; }
+/* generate_polynomial_terms interpolate.jl:106-114 (same enumeration as objective_function :89-102) */
+void orc_poly_terms(int degree, int *p, int *q) {
+    int k = 0;
+    for (int i = 0; i <= degree; i++)
+        for (int j = 0; j <= degree - i; j++) { p[k] = i; q[k] = j; k++; }
+}
+/* Float64 ^ Int as Julia computes it (Base.Math.pow_body, compensated power by squaring) */
+static double ipow(double x, int n) {
+    if (n == 0) return 1.0;
+    if (n == 3) return x * x * x;
+    double y = 1.0, xnlo = 0.0, ynlo = 0.0;
+    while (n > 1) {
+        if (n & 1) {
+            double err = y * xnlo + x * ynlo;
+            double yy = x * y; ynlo = fma(x, y, -yy); y = yy;
+            ynlo += err;
+        }
+        double err = x * 2.0 * xnlo;
+        double xx = x * x; xnlo = fma(x, x, -xx); x = xx;
+        xnlo += err;
+        n >>= 1;
+    }
+    if (!isfinite(x)) return x * y;
+    return x * y + (y * xnlo + x * ynlo);
+}
+/* interpolate.jl:89-102 */
+double orc_objective_function(const double *coef, double x, double y, int degree) {
+    double value = 0.0; int counter = 0;
+    for (int i = 1; i <= degree + 1; i++)
+        for (int j = 1; j <= degree + 1; j++)
+            if ((i - 1) + (j - 1) <= degree) { value += coef[counter] * ipow(x, i - 1) * ipow(y, j - 1); counter++; }
+    return value;
+}
+static int cmp_double(const void *a, const void *b) {
+    double x = *(const double *)a, y = *(const double *)b;
+    return (x > y) - (x < y);
+}
+/* Statistics.median(filter(!isnan, z)): even count -> middle(a,b) = a/2 + b/2 */
+double orc_median(const double *z, int64_t n) {
+    double *t = (double *)malloc(sizeof(double) * (n > 0 ? n : 1));
+    int64_t m = 0;
+    for (int64_t i = 0; i < n; i++) if (!isnan(z[i])) t[m++] = z[i];
+    double med = NAN;
+    if (m > 0) {
+        qsort(t, m, sizeof(double), cmp_double);
+        med = (m & 1) ? t[m / 2] : t[m / 2 - 1] / 2 + t[m / 2] / 2;
+    }
+    free(t);
+    return med;
+}
+
+/* Column-pivoted Householder QR (LAPACK geqp3 semantics) of A (n x K, column-major, overwritten):
+ * R in the upper triangle, Householder vectors below, tau, jpvt. */
+typedef struct { int n, K, rank; double *A, *tau; int *jpvt; } pqr;
+static void pqr_factor(pqr *F) {
+    const int n = F->n, K = F->K; double *A = F->A;
+    double *cn = (double *)malloc(sizeof(double) * K), *cn0 = (double *)malloc(sizeof(double) * K);
+    for (int j = 0; j < K; j++) {
+        double s = 0.0; for (int i = 0; i < n; i++) s += A[i + (size_t)j * n] * A[i + (size_t)j * n];
+        cn[j] = cn0[j] = sqrt(s); F->jpvt[j] = j;
+    }
+    const int mn = n < K ? n : K;
+    for (int k = 0; k < mn; k++) {
+        int pv = k; for (int j = k + 1; j < K; j++) if (cn[j] > cn[pv]) pv = j;
+        if (pv != k) {
+            for (int i = 0; i < n; i++) { double t = A[i + (size_t)pv * n]; A[i + (size_t)pv * n] = A[i + (size_t)k * n]; A[i + (size_t)k * n] = t; }
+            int t = F->jpvt[pv]; F->jpvt[pv] = F->jpvt[k]; F->jpvt[k] = t;
+            cn[pv] = cn[k]; cn0[pv] = cn0[k];
+        }
+        double *x = A + k + (size_t)k * n;
+        double xn = 0.0; for (int i = 1; i < n - k; i++) xn += x[i] * x[i];
+        double alpha = x[0], tau = 0.0;
+        if (xn != 0.0) {
+            double beta = -copysign(sqrt(alpha * alpha + xn), alpha);
+            tau = (beta - alpha) / beta;
+            double sc = 1.0 / (alpha - beta);
+            for (int i = 1; i < n - k; i++) x[i] *= sc;
+            x[0] = beta;
+        }
+        F->tau[k] = tau;
+        for (int j = k + 1; j < K; j++) {               /* apply H_k to the trailing columns */
+            double *y = A + k + (size_t)j * n;
+            double w = y[0]; for (int i = 1; i < n - k; i++) w += x[i] * y[i];
+            w *= tau;
+            y[0] -= w; for (int i = 1; i < n - k; i++) y[i] -= w * x[i];
+            if (cn[j] != 0.0) {                         /* downdate, recompute when cancellation bites */
+                double t = fabs(y[0]) / cn[j]; t = 1.0 - t * t; if (t < 0) t = 0;
+                double t2 = t * (cn[j] / cn0[j]) * (cn[j] / cn0[j]);
+                if (t2 <= 1.4901161193847656e-08) {
+                    double s = 0.0; for (int i = 1; i < n - k; i++) s += y[i] * y[i];
+                    cn[j] = cn0[j] = sqrt(s);
+                } else cn[j] *= sqrt(t);
+            }
+        }
+    }
+    /* numerical rank: |R_kk| > rcond*|R_11| with rcond = min(n,K)*eps (Julia's ldiv!(QRPivoted) uses
+     * LAPACK's incremental condition estimator with the same rcond; identical unless cond ~ 1/rcond) */
+    const double rcond = mn * DBL_EPSILON;
+    int rank = 0; double r11 = fabs(A[0]);
+    if (r11 != 0.0) for (rank = 1; rank < mn; rank++) if (!(fabs(A[rank + (size_t)rank * n]) > rcond * r11)) break;
+    F->rank = rank;
+    free(cn); free(cn0);
+}
+/* x = A \ z through the factorisation: Q'z, triangular solve (min-norm completion if rank < K) */
+static void pqr_solve(const pqr *F, const double *z, double *work, double *coef) {
+    const int n = F->n, K = F->K, mn = n < K ? n : K, rk = F->rank; const double *A = F->A;
+    memcpy(work, z, sizeof(double) * n);
+    for (int k = 0; k < mn; k++) {
+        const double *x = A + k + (size_t)k * n;
+        double w = work[k]; for (int i = 1; i < n - k; i++) w += x[i] * work[k + i];
+        w *= F->tau[k];
+        work[k] -= w; for (int i = 1; i < n - k; i++) work[k + i] -= w * x[i];
+    }
+    double y[64] = { 0 };
+    if (rk == K || rk == 0) {
+        for (int i = rk - 1; i >= 0; i--) {
+            double s = work[i]; for (int j = i + 1; j < rk; j++) s -= A[i + (size_t)j * n] * y[j];
+            y[i] = s / A[i + (size_t)i * n];
+        }
+    } else {
+        /* minimum-norm solution of [R11 R12] y = c : y = R'(R R')^{-1} c via Cholesky of R R' */
+        double G[64 * 64], cc[64];
+        for (int a = 0; a < rk; a++) for (int b = 0; b < rk; b++) {
+            double s = 0.0; for (int j = (a > b ? a : b); j < K; j++) s += A[a + (size_t)j * n] * A[b + (size_t)j * n];
+            G[a + b * 64] = s;
+        }
+        for (int a = 0; a < rk; a++) {
+            for (int b = 0; b <= a; b++) {
+                double s = G[a + b * 64]; for (int t = 0; t < b; t++) s -= G[a + t * 64] * G[b + t * 64];
+                G[a + b * 64] = (a == b) ? sqrt(s) : s / G[b + b * 64];
+            }
+        }
+        for (int a = 0; a < rk; a++) { double s = work[a]; for (int t = 0; t < a; t++) s -= G[a + t * 64] * cc[t]; cc[a] = s / G[a + a * 64]; }
+        for (int a = rk - 1; a >= 0; a--) { double s = cc[a]; for (int t = a + 1; t < rk; t++) s -= G[t + a * 64] * cc[t]; cc[a] = s / G[a + a * 64]; }
+        for (int j = 0; j < K; j++) { double s = 0.0; for (int a = 0; a <= j && a < rk; a++) s += A[a + (size_t)j * n] * cc[a]; y[j] = s; }
+    }
+    for (int j = 0; j < K; j++) coef[F->jpvt[j]] = y[j];
+}
+/* square system: LU with partial pivoting (Julia's `\` for N == K) */
+static void lu_solve(double *A, int n, double *b) {
+    for (int k = 0; k < n; k++) {
+        int pv = k; for (int i = k + 1; i < n; i++) if (fabs(A[i + k * n]) > fabs(A[pv + k * n])) pv = i;
+        if (pv != k) { for (int j = 0; j < n; j++) { double t = A[k + j * n]; A[k + j * n] = A[pv + j * n]; A[pv + j * n] = t; } double t = b[k]; b[k] = b[pv]; b[pv] = t; }
+        for (int i = k + 1; i < n; i++) {
+            double l = A[i + k * n] / A[k + k * n]; A[i + k * n] = l;
+            for (int j = k + 1; j < n; j++) A[i + j * n] -= l * A[k + j * n];
+            b[i] -= l * b[k];
+        }
+    }
+    for (int i = n - 1; i >= 0; i--) { double s = b[i]; for (int j = i + 1; j < n; j++) s -= A[i + j * n] * b[j]; b[i] = s / A[i + i * n]; }
+}
+static void build_design(int degree, const double *x, const double *y, int64_t n, double first_col, int use_first, double *A) {
+    int K = orc_num_terms(degree), p[64], q[64];
+    orc_poly_terms(degree, p, q);
+    for (int64_t i = 0; i < n; i++)
+        for (int k = 0; k < K; k++)
+            A[i + (size_t)k * n] = (k == 0 && use_first) ? first_col : ipow(x[i], p[k]) * ipow(y[i], q[k]);
+}
+/* interpolate.jl:105-147 */
+void orc_polynomial_optimizer(int degree, const double *x, const double *y, double *z, int64_t n,
+                              int median_constraint, double *coef) {
+    const int K = orc_num_terms(degree);
+    double *A = (double *)malloc(sizeof(double) * (size_t)n * K + 8);
+    if (median_constraint) {
+        build_design(degree, x, y, n, orc_median(z, n), 1, A);           /* :118-124 */
+    } else {
+        int has_nan = 0; for (int64_t i = 0; i < n; i++) if (isnan(z[i])) { has_nan = 1; break; }
+        if (has_nan) { double med = orc_median(z, n); for (int64_t i = 0; i < n; i++) if (isnan(z[i])) z[i] = med; }  /* :126-130 */
+        build_design(degree, x, y, n, 0.0, 0, A);
+    }
+    if (n == K) {
+        double *b = (double *)malloc(sizeof(double) * n); memcpy(b, z, sizeof(double) * n);
+        lu_solve(A, (int)n, b); memcpy(coef, b, sizeof(double) * K); free(b);
+    } else {
+        pqr F; F.n = (int)n; F.K = K; F.A = A; F.tau = (double *)calloc(K, sizeof(double)); F.jpvt = (int *)malloc(sizeof(int) * K);
+        double *work = (double *)malloc(sizeof(double) * (n > K ? n : K));
+        pqr_factor(&F);
+        pqr_solve(&F, z, work, coef);
+        free(work); free(F.jpvt); free(F.tau);
+    }
+    if (median_constraint) coef[0] = orc_median(z, n);                     /* :139-141 */
+    if (n < 5) { double med = orc_median(z, n); for (int k = 0; k < K; k++) coef[k] = 0.0; coef[0] = med; }  /* :142-145 */
+    free(A);
+}
+
+typedef struct { int64_t i; double e; } idxerr;
+static void merge_sort_desc(idxerr *a, idxerr *tmp, int64_t n) {      /* stable, like sort!(…, rev=true) */
+    if (n < 2) return;
+    int64_t h = n / 2;
+    merge_sort_desc(a, tmp, h); merge_sort_desc(a + h, tmp, n - h);
+    int64_t i = 0, j = h, k = 0;
+    /* rev=true orders by isless(b, a); a NaN error sorts first (isless treats NaN as largest) */
+    while (i < h && j < n) {
+        double x = a[i].e, y = a[j].e;
+        int y_before_x = isnan(x) ? 0 : (isnan(y) ? 1 : (y > x));
+        tmp[k++] = y_before_x ? a[j++] : a[i++];
+    }
+    while (i < h) tmp[k++] = a[i++];
+    while (j < n) tmp[k++] = a[j++];
+    memcpy(a, tmp, sizeof(idxerr) * n);
+}
+/* shopt.jl:513-520 ; sigma_clip variant :522-532 */
+int64_t orc_worst_10_percent(const double *err, int64_t n, int sigma_clip, int64_t *idx_out) {
+    if (n <= 0) return 0;
+    if (sigma_clip) {
+        double mean = pairwise_sum(err, n) / n, ss = 0.0;
+        for (int64_t i = 0; i < n; i++) ss += (err[i] - mean) * (err[i] - mean);
+        double sd = sqrt(ss / (n - 1)), thr = mean + 3 * sd;
+        int64_t m = 0;
+        for (int64_t i = 0; i < n; i++) if (err[i] > thr) idx_out[m++] = i;
+        return m;
+    }
+    idxerr *a = (idxerr *)malloc(sizeof(idxerr) * n), *tmp = (idxerr *)malloc(sizeof(idxerr) * n);
+    for (int64_t i = 0; i < n; i++) { a[i].i = i; a[i].e = err[i]; }
+    merge_sort_desc(a, tmp, n);
+    int64_t m = (int64_t)ceil(0.10 * (double)n);
+    for (int64_t i = 0; i < m; i++) idx_out[i] = a[i].i;
+    free(a); free(tmp);
+    return m;
+}
+
+/* shopt.jl:534-577 */
+void orc_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, const double *v,
+                 const int64_t *train_idx, int64_t n_train, int degree, int iterations,
+                 int median_constraint, int sigma_clip, double *poly_out, double *mse_out,
+                 int64_t *kept_idx, int64_t *n_kept, int64_t *n_per_round, int nthreads) {
+    (void)N;
+    if (nthreads < 1) nthreads = 1;
+    const int K = orc_num_terms(degree);
+    const size_t rc = (size_t)r * c;
+    int64_t n = n_train;
+    int64_t *cur = (int64_t *)malloc(sizeof(int64_t) * (n > 0 ? n : 1));
+    memcpy(cur, train_idx, sizeof(int64_t) * n);
+    for (size_t i = 0; i < rc * K; i++) poly_out[i] = 1.0;             /* ones(r,c,K) shopt.jl:492 */
+    double *tu = (double *)malloc(sizeof(double) * (n > 0 ? n : 1)), *tv = (double *)malloc(sizeof(double) * (n > 0 ? n : 1));
+    double *err = (double *)malloc(sizeof(double) * (n > 0 ? n : 1));
+    int64_t *bad = (int64_t *)malloc(sizeof(int64_t) * (n > 0 ? n : 1));
+    char *isbad = (char *)malloc(n > 0 ? n : 1);
+    for (int loop = 1; loop <= iterations; loop++) {
+        if (n_per_round) n_per_round[loop - 1] = n;
+        for (int64_t t = 0; t < n; t++) { tu[t] = u[cur[t]]; tv[t] = v[cur[t]]; }
+        /* the design matrix does not depend on the pixel unless NaNs/median_constraint intervene:
+         * factor it once and reuse (bitwise the same result as factoring it per pixel) */
+        pqr F; F.n = (int)n; F.K = K; F.tau = NULL; F.jpvt = NULL; F.A = NULL;
+        int shared = (!median_constraint && n != K && n >= 5);
+        if (shared) {
+            F.A = (double *)malloc(sizeof(double) * (size_t)n * K + 8);
+            F.tau = (double *)calloc(K, sizeof(double)); F.jpvt = (int *)malloc(sizeof(int) * K);
+            build_design(degree, tu, tv, n, 0.0, 0, F.A);
+            pqr_factor(&F);
+        }
+        #pragma omp parallel num_threads(nthreads)
+        {
+            double *z = (double *)malloc(sizeof(double) * (n > K ? n : K) + 8);
+            double *work = (double *)malloc(sizeof(double) * (n > K ? n : K) + 8);
+            double coef[64];
+            #pragma omp for schedule(static)
+            for (int64_t px = 0; px < (int64_t)rc; px++) {
+                int has_nan = 0;
+                for (int64_t t = 0; t < n; t++) { z[t] = pgf[(size_t)cur[t] * rc + px]; if (isnan(z[t])) has_nan = 1; }
+                if (shared && !has_nan) pqr_solve(&F, z, work, coef);
+                else orc_polynomial_optimizer(degree, tu, tv, z, n, median_constraint, coef);
+                for (int k = 0; k < K; k++) poly_out[px + (size_t)k * rc] = coef[k];     /* PolynomialMatrix[i,j,:] */
+            }
+            free(z); free(work);
+        }
+        if (shared) { free(F.A); free(F.tau); free(F.jpvt); }
+        /* training errors shopt.jl:551-555 */
+        #pragma omp parallel num_threads(nthreads)
+        {
+            double *sq = (double *)malloc(sizeof(double) * rc);
+            double coef[64];
+            #pragma omp for schedule(static)
+            for (int64_t t = 0; t < n; t++) {
+                const double *star = pgf + (size_t)cur[t] * rc;
+                for (size_t px = 0; px < rc; px++) {
+                    for (int k = 0; k < K; k++) coef[k] = poly_out[px + (size_t)k * rc];
+                    double d = orc_objective_function(coef, tu[t], tv[t], degree) - star[px];
+                    sq[px] = d * d;
+                }
+                err[t] = pairwise_sum(sq, (int64_t)rc) / (double)rc;
+            }
+            free(sq);
+        }
+        int64_t nbad = orc_worst_10_percent(err, n, sigma_clip, bad);
+        if (loop == iterations) {
+            if (mse_out) memcpy(mse_out, err, sizeof(double) * n);
+        } else {
+            memset(isbad, 0, n);
+            for (int64_t b = 0; b < nbad; b++) isbad[bad[b]] = 1;
+            int64_t m = 0;
+            for (int64_t t = 0; t < n; t++) if (!isbad[t]) cur[m++] = cur[t];
+            n = m;
+        }
+    }
+    if (kept_idx) memcpy(kept_idx, cur, sizeof(int64_t) * n);
+    if (n_kept) *n_kept = n;
+    free(isbad); free(bad); free(err); free(tu); free(tv); free(cur);
+}
+
+/* reader.jl:40-68 */
+void orc_psf_at(const double *poly, int r, int c, int degree, double u, double v, double *star) {
+    const int K = orc_num_terms(degree); const size_t rc = (size_t)r * c;
+    double coef[64];
+    for (size_t px = 0; px < rc; px++) {
+        for (int k = 0; k < K; k++) coef[k] = poly[px + (size_t)k * rc];
+        star[px] = orc_objective_function(coef, u, v, degree);
+    }
+    double s = pairwise_sum(star, (int64_t)rc);
+    for (size_t px = 0; px < rc; px++) star[px] = star[px] / s;
+}
