@@ -1,0 +1,170 @@
+/*
+ * shopt_b200.h -- C ABI of libshopt_b200.so: the per-star PSF fitting stage of ShOpt.jl on B200.
+ *
+ * The reference (EdwardBerman/shopt) has no FFI/plugin interface: the stage is a set of script-level
+ * loops in shopt/shopt.jl.  Each entry point below replaces one of those loops with ONE batched call
+ * and is what a thin Julia `ccall` shim binds (INTEGRATION.md shows the shim).  Paths cited are
+ * relative to the reference checkout.
+ *
+ * Conventions
+ *   - FP64 throughout.  Julia column-major: a batch of N stamps of r x c pixels is the Julia array
+ *     Array{Float64,3}(r, c, N); pixel (u,v) (1-based) of star i (0-based) is stamps[i*r*c + (u-1) + (v-1)*r].
+ *   - All indices crossing this interface are 0-based (the Julia shim adds/subtracts 1).
+ *   - Host entry points (no suffix) take HOST pointers, copy H2D / D2H themselves and block until done.
+ *     `_dev` entry points take DEVICE pointers on the current device, enqueue on `stream`
+ *     (a cudaStream_t passed as void*) and do not synchronise; they are what the multi-GPU host code
+ *     and the benchmark's device-resident leg call.
+ *   - Every function returns SHOPT_OK (0) or a negative SHOPT_E_* code; nothing throws or aborts.
+ *     Per-star outcomes are reported in `status` arrays (the reference's per-star try/catch).
+ *   - There is no CPU fallback: without a CUDA device every compute call returns SHOPT_E_NODEVICE.
+ */
+#ifndef SHOPT_B200_H
+#define SHOPT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SHOPT_OK              0
+#define SHOPT_E_NODEVICE     -1   /* no CUDA device / driver                                   */
+#define SHOPT_E_BADARG       -2   /* null pointer, non-positive size, n_a > min(r,c), degree>8  */
+#define SHOPT_E_CUDA         -3   /* a CUDA runtime call failed; see shopt_last_error()         */
+#define SHOPT_E_NOMEM        -4   /* device allocation failed                                   */
+#define SHOPT_E_UNSUPPORTED  -5   /* size outside what the kernels are built for                */
+
+/* per-star status of one analytic fit (same meaning as the oracle's ORC_FIT_*) */
+#define SHOPT_FIT_CONVERGED   0   /* Optim assess_convergence: x-, f- or g-convergence          */
+#define SHOPT_FIT_MAXITER     1   /* iteration cap reached; minimiser = last iterate            */
+#define SHOPT_FIT_LS_FAILED   2   /* LineSearchException: step of the exception taken, stop     */
+#define SHOPT_FIT_NONFINITE   3   /* non-finite value/gradient: stop, keep the current x        */
+#define SHOPT_FIT_THREW      -1   /* an assert inside the line search fired -> shopt.jl:155-162
+                                     catch: s = g1 = g2 = 0                                      */
+
+/* per-star status of one pixel-grid (PCA) fit */
+#define SHOPT_PCA_OK          0
+#define SHOPT_PCA_FAILED      1   /* non-finite input -> shopt.jl:305-309: zeros(r,c), failedStars */
+#define SHOPT_PCA_NOCONV      2   /* subspace iteration hit its cap; result is the last iterate */
+
+/* ---- library ---------------------------------------------------------------------------- */
+int         shopt_b200_version(void);          /* 10000*major + 100*minor + patch               */
+int         shopt_device_count(void);          /* 0 when no device/driver                       */
+int         shopt_set_device(int dev);
+const char *shopt_last_error(void);            /* text of the last CUDA error on this thread    */
+/* wall-clock-free device timing of the last host call, milliseconds, per stage:
+ * [0]=H2D [1]=kernels [2]=D2H (CUDA events on the library's stream) */
+int         shopt_last_timing(double ms[3]);
+
+/* ---- (1) analytic profile fit ------------------------------------------------------------
+ * Replaces the loops  shopt/shopt.jl:130-164  (model stars, cost/g!)  and  :357-397  (learned
+ * stars, costD/gD!):  Optim.optimize(cost, g!, x0, LBFGS(), Options(g_tol))  per star, with
+ * cost = shopt/analyticLBFGS.jl:8-46 on the get_middle_nxn(n_a) crop (dataPreprocessing.jl:207-216),
+ * fGaussian = shopt/radialProfiles.jl:5-9, then s = x1^2, (g1,g2) from (e1,e2) (shopt.jl:145-153).
+ *   stamps  (r,c,N)      x0 (3,N): the reference draws rand(3) per star -- an explicit input here
+ *   g_tol   minAnalyticGradientModel / ...Learned (shopt.yml AnalyticFitParams)
+ *   max_iter  Optim default 1000
+ *   s,g1,g2 (N) out;  status,iters (N) out, may be NULL                                          */
+int shopt_fit_analytic_batch(const double *stamps, int r, int c, int64_t N, int n_a,
+                             const double *x0, double g_tol, int max_iter,
+                             double *s, double *g1, double *g2, int32_t *status, int32_t *iters);
+int shopt_fit_analytic_batch_dev(const double *d_stamps, int r, int c, int64_t N, int n_a,
+                                 const double *d_x0, double g_tol, int max_iter,
+                                 double *d_s, double *d_g1, double *d_g2,
+                                 int32_t *d_status, int32_t *d_iters, void *stream);
+
+/* s-blacklist (shopt.jl:166-171) and learned-fit failed list (shopt.jl:384-386):
+ * 0-based indices with s < s_lo or s > s_hi, ascending; returns the count (host arrays). */
+int64_t shopt_s_out_of_bounds(const double *s, int64_t N, double s_lo, double s_hi, int64_t *idx);
+
+/* ---- (2) pixel-grid fit, mode == "PCA" ------------------------------------------------------
+ * Replaces the loop shopt/shopt.jl:281-314: nanToZero (masks.jl:38-50, NaN -> 0.001), pca_image
+ * (pca.jl:1-18: MultivariateStats fit(PCA; maxoutdim=ncomp, pratio) / transform / reconstruct with
+ * rows = variables, columns = observations), then smooth(., lanczos_a)
+ * (dataPreprocessing.jl:94-139) when unity_sum == 0, or division by the stamp sum WITHOUT smoothing
+ * when unity_sum != 0 (the reference's 1-argument smooth() call at shopt.jl:292 always raises, so
+ * its catch branch :295 runs).  lanczos_a <= 0 skips the smoothing.
+ *   pgf (r,c,N) out;  k_out (N): number of components kept;  status (N): SHOPT_PCA_*             */
+int shopt_pca_batch(const double *stamps, int r, int c, int64_t N, int ncomp, double pratio,
+                    int lanczos_a, int unity_sum, double *pgf, int32_t *k_out, int32_t *status);
+int shopt_pca_batch_dev(const double *d_stamps, int r, int c, int64_t N, int ncomp, double pratio,
+                        int lanczos_a, int unity_sum, double *d_pgf, int32_t *d_k_out,
+                        int32_t *d_status, void *stream);
+
+/* smooth(data, a) alone (dataPreprocessing.jl:112-139; mode == "smooth", shopt.jl:316-348, applies
+ * it to nanToZero(star) -- pass nan_to_zero = 1 for that). */
+int shopt_smooth_batch(const double *stamps, int r, int c, int64_t N, int lanczos_a, int nan_to_zero,
+                       double *out);
+int shopt_smooth_batch_dev(const double *d_stamps, int r, int c, int64_t N, int lanczos_a,
+                           int nan_to_zero, double *d_out, void *stream);
+
+/* ---- (3) per-pixel polynomial interpolation with outlier-star rejection ----------------------
+ * Replaces shopt/shopt.jl:492-577: `iterations` rounds of
+ *   polynomial_optimizer(degree, u, v, z) per pixel (interpolate.jl:105-147; term order p outer,
+ *   q inner, A[i,k] = u_i^p v_i^q, least squares),
+ *   per-star MSE of the reconstruction (shopt.jl:496-511, interpolate.jl:89-102),
+ *   worst_10_percent (shopt.jl:513-520; sigma_clip != 0 -> the mean+3sigma variant :522-532),
+ *   rejected stars dropped except after the last round (shopt.jl:557-575).
+ * The least squares is solved through the normal equations V'V c = V'z (one K x K Cholesky shared
+ * by all pixels); median_constraint (interpolate.jl:118-124,139-141) and fewer than 5 training
+ * stars (:142-145) follow the reference's overrides.
+ *   pgf (r,c,N); u,v (N); train_idx (n_train) 0-based, the randperm split of shopt.jl:472-490 is an
+ *   INPUT;  poly_out (r,c,K) K=(degree+1)(degree+2)/2;  mse_out (>= n_train): last round's training
+ *   errors in that round's order;  kept_idx/n_kept: training set after the last applied rejection;
+ *   n_per_round (iterations): training-set size of each round.  Outputs other than poly_out may be NULL. */
+int shopt_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, const double *v,
+                  const int64_t *train_idx, int64_t n_train, int degree, int iterations,
+                  int median_constraint, int sigma_clip, double *poly_out, double *mse_out,
+                  int64_t *kept_idx, int64_t *n_kept, int64_t *n_per_round);
+
+/* Building blocks of one round on device buffers (what shopt_polyfit and the multi-GPU host loop call).
+ *  normal_dev : acc[0..K*K) += V'V, acc[K*K .. K*K + K*r*c) += V'P over the listed stars of this shard
+ *               (acc is zeroed by the call; layout V'P[k*rc + px]); the buffer every rank all-reduces.
+ *  solve_dev  : Cholesky of V'V, back-substitution for every pixel -> poly (r,c,K).
+ *               Returns SHOPT_OK; *d_info (device int) != 0 when V'V is not positive definite.
+ *  mse_dev    : mse[t] = mean_px (sum_k poly[px,k] u_t^p v_t^q - pgf[idx_t, px])^2 for the listed stars. */
+int64_t shopt_polyfit_acc_len(int r, int c, int degree);                   /* K*K + K*r*c doubles */
+int shopt_polyfit_normal_dev(const double *d_pgf, int r, int c, const double *d_u, const double *d_v,
+                             const int64_t *d_idx, int64_t n, int degree, double *d_acc, void *stream);
+int shopt_polyfit_solve_dev(const double *d_acc, int r, int c, int degree, double *d_poly,
+                            int32_t *d_info, void *stream);
+int shopt_polyfit_mse_dev(const double *d_pgf, int r, int c, const double *d_u, const double *d_v,
+                          const int64_t *d_idx, int64_t n, int degree, const double *d_poly,
+                          double *d_mse, void *stream);
+/* worst_10_percent on host arrays: returns count, idx_out = positions in err (stable descending). */
+int64_t shopt_worst_10_percent(const double *err, int64_t n, int sigma_clip, int64_t *idx_out);
+
+/* ---- consumer: reader.jl:40-68  p(u,v,polMatrix,degree) batched over M positions -------------
+ * stars_out (r,c,M): polynomial evaluated at (u_m,v_m), each stamp divided by its sum. */
+int shopt_psf_at_batch(const double *poly, int r, int c, int degree, const double *u, const double *v,
+                       int64_t M, double *stars_out);
+int shopt_psf_at_batch_dev(const double *d_poly, int r, int c, int degree, const double *d_u,
+                           const double *d_v, int64_t M, double *d_stars_out, void *stream);
+
+/* ---- whole stage on one GPU, host buffers (what shopt.jl's four loops become) -----------------
+ * model fit -> s-blacklist -> PCA -> learned fit -> failed list -> polyfit.  Parameters mirror
+ * shopt.yml (see shopt_params).  Outputs are sized for N stars; blacklisted / failed stars are
+ * reported through the index lists and are excluded from the training set exactly like the
+ * reference's splices (shopt.jl:177-184, 405-417). */
+typedef struct shopt_params {
+    int    n_a;                 /* AnalyticFitParams.analyticFitStampSize                        */
+    double g_tol_model;         /* AnalyticFitParams.minGradientAnalyticModel                    */
+    double g_tol_learned;       /* AnalyticFitParams.minGradientAnalyticLearned                  */
+    int    max_iter;            /* Optim default 1000                                            */
+    double s_lo, s_hi;          /* dataProcessing.sLowerBound / sUpperBound                      */
+    int    pca_terms;           /* NNparams.PCAterms (mode "PCA")                                */
+    double pratio;              /* MultivariateStats default 0.99                                */
+    int    lanczos;             /* lanczos                                                       */
+    int    unity_sum;           /* sum_pixel_grid_and_inputs_to_unity                            */
+    int    degree;              /* polynomialDegree                                              */
+    int    iterations;          /* iterations (polyfit rounds)                                   */
+    double training_ratio;      /* training_ratio                                                */
+    int    median_constraint;   /* median_constraint                                             */
+    int    sigma_clip;          /* outlier_sigma_clipping                                        */
+} shopt_params;
+void shopt_default_params(shopt_params *p);     /* README.md:300-330 documented defaults          */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,94 @@
+"""ctypes binding of libshopt_b200.so (include/shopt_b200.h).
+
+The shared library is the product; this module only declares its C ABI.  There is no fallback of any kind:
+if the library has not been built, importing the compute functions raises, and if no CUDA device is
+present every compute call returns SHOPT_E_NODEVICE, which `check()` turns into an exception.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libshopt_b200.so")
+
+OK, E_NODEVICE, E_BADARG, E_CUDA, E_NOMEM, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5
+FIT_CONVERGED, FIT_MAXITER, FIT_LS_FAILED, FIT_NONFINITE, FIT_THREW = 0, 1, 2, 3, -1
+PCA_OK, PCA_FAILED, PCA_NOCONV = 0, 1, 2
+
+_ERR = {E_NODEVICE: "no CUDA device", E_BADARG: "bad argument", E_CUDA: "CUDA error",
+        E_NOMEM: "device allocation failed", E_UNSUPPORTED: "size not supported by the kernels"}
+
+
+class ShoptError(RuntimeError):
+    def __init__(self, code, detail=""):
+        self.code = code
+        super().__init__(f"libshopt_b200: {_ERR.get(code, 'error')} ({code}) {detail}".strip())
+
+
+dp = C.POINTER(C.c_double)
+ip = C.POINTER(C.c_int32)
+lp = C.POINTER(C.c_int64)
+vp = C.c_void_p
+
+
+class Params(C.Structure):
+    """struct shopt_params (shopt.yml keys on the hot path)."""
+    _fields_ = [("n_a", C.c_int), ("g_tol_model", C.c_double), ("g_tol_learned", C.c_double),
+                ("max_iter", C.c_int), ("s_lo", C.c_double), ("s_hi", C.c_double), ("pca_terms", C.c_int),
+                ("pratio", C.c_double), ("lanczos", C.c_int), ("unity_sum", C.c_int), ("degree", C.c_int),
+                ("iterations", C.c_int), ("training_ratio", C.c_double), ("median_constraint", C.c_int),
+                ("sigma_clip", C.c_int)]
+
+
+# name -> (restype, argtypes); every symbol include/shopt_b200.h declares
+SIGNATURES = {
+    "shopt_b200_version": (C.c_int, []),
+    "shopt_device_count": (C.c_int, []),
+    "shopt_set_device": (C.c_int, [C.c_int]),
+    "shopt_last_error": (C.c_char_p, []),
+    "shopt_last_timing": (C.c_int, [dp]),
+    "shopt_fit_analytic_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, dp, C.c_double, C.c_int,
+                                           dp, dp, dp, ip, ip]),
+    "shopt_fit_analytic_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, C.c_double, C.c_int,
+                                               vp, vp, vp, vp, vp, vp]),
+    "shopt_s_out_of_bounds": (C.c_int64, [dp, C.c_int64, C.c_double, C.c_double, lp]),
+    "shopt_pca_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_double, C.c_int, C.c_int, dp, ip, ip]),
+    "shopt_pca_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_double, C.c_int, C.c_int,
+                                      vp, vp, vp, vp]),
+    "shopt_smooth_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, dp]),
+    "shopt_smooth_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, vp, vp]),
+    "shopt_polyfit": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, dp, dp, lp, C.c_int64, C.c_int, C.c_int, C.c_int,
+                                C.c_int, dp, dp, lp, lp, lp]),
+    "shopt_polyfit_acc_len": (C.c_int64, [C.c_int, C.c_int, C.c_int]),
+    "shopt_polyfit_normal_dev": (C.c_int, [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "shopt_polyfit_solve_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]),
+    "shopt_polyfit_mse_dev": (C.c_int, [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_int, vp, vp, vp]),
+    "shopt_worst_10_percent": (C.c_int64, [dp, C.c_int64, C.c_int, lp]),
+    "shopt_psf_at_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int, dp, dp, C.c_int64, dp]),
+    "shopt_psf_at_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int64, vp, vp]),
+    "shopt_default_params": (None, [C.POINTER(Params)]),
+}
+
+_LIB = None
+
+
+def lib():
+    """Load libshopt_b200.so; raises if it has not been built (python __graft_entry__.py / make -C shopt_b200/csrc)."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise ShoptError(E_NODEVICE, f"{LIB_PATH} is missing: build it with `make -C shopt_b200/csrc`; "
+                                         "there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)          # AttributeError if the library lacks a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = L
+    return _LIB
+
+
+def check(code):
+    if code != OK:
+        detail = lib().shopt_last_error()
+        raise ShoptError(code, detail.decode() if detail else "")
+    return code

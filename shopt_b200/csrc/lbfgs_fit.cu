@@ -1,0 +1,809 @@
+// lbfgs_fit.cu -- batched analytic profile fit: one persistent CTA per star.
+//
+// Replaces the loops shopt/shopt.jl:130-164 and :357-397 of the reference:
+//     Optim.optimize(cost, g!, x0, LBFGS(), Optim.Options(g_tol = ...))      (shopt.jl:139-143, 367-371)
+// with cost/costD = shopt/analyticLBFGS.jl:8-46 / 49-87 (sum-normalised elliptical Gaussian, fGaussian of
+// shopt/radialProfiles.jl:5-9, on the get_middle_nxn crop dataPreprocessing.jl:207-216) and
+// g!/gD! = ForwardDiff.gradient (analyticLBFGS.jl:89-101).  Optim 1.7.8 / LineSearches 7.2.0 are not
+// vendored in the reference; the algorithm followed is the one recorded in SURVEY.md Appendix A.
+//
+// Design (B200): the n_a x n_a crop of each stamp is staged into shared memory by 1-D bulk (TMA) copies,
+// one per crop column, double-buffered so the next star's crop lands while the current one is being
+// fitted.  Every value+gradient evaluation is two passes over the crop held in shared memory (profile
+// sums, then residual sums) with the per-pixel exp() cached in registers between the passes; the eleven
+// sums are reduced deterministically (common.cuh cta_sum) so that every thread of the CTA holds the same
+// bits and runs the scalar LBFGS / HagerZhang state machine redundantly in registers -- no broadcast, and
+// control flow stays uniform.  The manifold reparameterisation [sigma,e1,e2] -> [s,g1,g2] is evaluated with
+// explicitly rounded operations (no FMA contraction) in the same operation order as the reference's
+// expression, because that expression amplifies round-off by 1/|e|^4.
+#include <type_traits>
+#include "common.cuh"
+
+namespace shopt {
+
+// ---------------------------------------------------------------------------------------------
+// Scalar section: dual numbers with 3 partials, evaluated op for op like ForwardDiff does on the
+// reference's expression.  __dmul_rn/__dadd_rn/... are never contracted into FMAs.
+// ---------------------------------------------------------------------------------------------
+struct Dual {
+    double v, d[3];
+};
+__device__ __forceinline__ double mul_(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double add_(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double sub_(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double div_(double a, double b) { return __ddiv_rn(a, b); }
+__device__ __forceinline__ double sqrt_(double a) { return __dsqrt_rn(a); }
+
+__device__ __forceinline__ Dual d_seed(double v, int i) {
+    Dual r = {v, {0.0, 0.0, 0.0}};
+    r.d[i] = 1.0;
+    return r;
+}
+__device__ __forceinline__ Dual d_add(Dual a, Dual b) {
+    Dual r; r.v = add_(a.v, b.v);
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = add_(a.d[i], b.d[i]);
+    return r;
+}
+__device__ __forceinline__ Dual d_sub(Dual a, Dual b) {
+    Dual r; r.v = sub_(a.v, b.v);
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = sub_(a.d[i], b.d[i]);
+    return r;
+}
+__device__ __forceinline__ Dual d_radd(double a, Dual b) { b.v = add_(a, b.v); return b; }
+__device__ __forceinline__ Dual d_rsub(double a, Dual b) {
+    Dual r; r.v = sub_(a, b.v);
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = -b.d[i];
+    return r;
+}
+__device__ __forceinline__ Dual d_rmul(double a, Dual b) {
+    Dual r; r.v = mul_(a, b.v);
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = mul_(b.d[i], a);
+    return r;
+}
+__device__ __forceinline__ Dual d_div(Dual a, Dual b) {
+    Dual r; double ib = div_(1.0, b.v), w = -div_(a.v, mul_(b.v, b.v));
+    r.v = div_(a.v, b.v);
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = add_(mul_(a.d[i], ib), mul_(b.d[i], w));
+    return r;
+}
+__device__ __forceinline__ Dual d_rdiv(double a, Dual b) {
+    Dual r; double divv = div_(a, b.v), w = -div_(divv, b.v);
+    r.v = divv;
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = mul_(w, b.d[i]);
+    return r;
+}
+__device__ __forceinline__ Dual d_sqrt(Dual a) {
+    Dual r; r.v = sqrt_(a.v); double w = div_(1.0, mul_(2.0, r.v));
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = mul_(w, a.d[i]);
+    return r;
+}
+__device__ __forceinline__ Dual d_sq(Dual a) {
+    Dual r; r.v = mul_(a.v, a.v); double w = mul_(2.0, a.v);
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = mul_(w, a.d[i]);
+    return r;
+}
+// Float64 ^ 4 the way Julia >= 1.8 evaluates a literal integer power (compensated squaring).
+__device__ __forceinline__ double pow4_(double x) {
+    double x2 = mul_(x, x);
+    double lo2 = __fma_rn(x, x, -x2);
+    double err = mul_(mul_(x2, 2.0), lo2);
+    double x4 = mul_(x2, x2);
+    double lo4 = add_(__fma_rn(x2, x2, -x4), err);
+    if (!isfinite(x4)) return x4;
+    return add_(x4, lo4);
+}
+__device__ __forceinline__ Dual d_pow4(Dual a) {
+    Dual r; r.v = pow4_(a.v); double v3 = mul_(mul_(a.v, a.v), a.v);
+#pragma unroll
+    for (int i = 0; i < 3; i++) r.d[i] = mul_(mul_(a.d[i], 4.0), v3);
+    return r;
+}
+// analyticLBFGS.jl:10-18 on duals
+__device__ __forceinline__ void e_to_g_dual(Dual e1, Dual e2, Dual &g1, Dual &g2) {
+    Dual ell = d_sqrt(d_add(d_sq(e1), d_sq(e2)));
+    Dual ell2 = d_sq(ell);
+    Dual inner = d_sqrt(d_add(d_rdiv(4.0, ell2), d_rdiv(1.0, d_pow4(ell))));
+    Dual normG = d_sqrt(d_radd(1.0, d_rmul(0.5, d_sub(d_rdiv(1.0, ell2), inner))));
+    Dual ratio = d_div(ell, normG);
+    g1 = d_div(e1, ratio);
+    g2 = d_div(e2, ratio);
+}
+// shopt.jl:145-153 on plain doubles
+__device__ __forceinline__ void e_to_g(double e1, double e2, double &g1, double &g2) {
+    double ell = sqrt_(add_(mul_(e1, e1), mul_(e2, e2)));
+    double ell2 = mul_(ell, ell);
+    double normG = sqrt_(add_(1.0, mul_(0.5, sub_(div_(1.0, ell2), sqrt_(add_(div_(4.0, ell2), div_(1.0, pow4_(ell))))))));
+    double ratio = div_(ell, normG);
+    g1 = div_(e1, ratio);
+    g2 = div_(e2, ratio);
+}
+
+// ---------------------------------------------------------------------------------------------
+// One CTA's view of the star being fitted.
+// ---------------------------------------------------------------------------------------------
+template <int THREADS, int PPT>
+struct StarEval {
+    static constexpr int NWARPS = THREADS / 32;
+    const double *crop;   // shared memory, column v at crop + v*pitch + off(v)
+    const unsigned char *coff;   // per-column misalignment offset (0/1), shared memory
+    int n_a, pitch, npix;
+    unsigned magic;       // ceil(2^32 / n_a)
+    double uc;            // n_a / 2 (analyticLBFGS.jl:28,41: the centre is (r/2, c/2) of the crop)
+    double *scratch;      // 2 * NWARPS * 6 doubles
+    int buf;
+    // NLSolversBase caches the last evaluated point by value
+    double xl[3], fl, gl[3];
+    bool have_last;
+    int nevals;
+
+    __device__ __forceinline__ void pix(int p, double &du, double &dv, double &d) const {
+        const unsigned v = __umulhi((unsigned)p, magic);
+        const unsigned u = (unsigned)p - v * (unsigned)n_a;
+        du = (double)(int)(u + 1) - uc;
+        dv = (double)(int)(v + 1) - uc;
+        d = crop[v * pitch + coff[v] + u];
+    }
+
+    // value_gradient!(d, x): the reference runs g! (ForwardDiff over cost) and then cost(x); the value
+    // channel of the dual pass is the same operation sequence, so one evaluation yields both.
+    __device__ __noinline__ void fg(const double xn[3], double &f, double g[3]) {
+        if (have_last && xn[0] == xl[0] && xn[1] == xl[1] && xn[2] == xl[2]) {
+            f = fl; g[0] = gl[0]; g[1] = gl[1]; g[2] = gl[2];
+            return;
+        }
+        // scalar section (every thread, identical bits)
+        Dual sig = d_seed(xn[0], 0), e1 = d_seed(xn[1], 1), e2 = d_seed(xn[2], 2);
+        Dual sg = d_sq(sig);
+        Dual g1, g2;
+        e_to_g_dual(e1, e2, g1, g2);
+        Dual a11 = d_radd(1.0, g1), a22 = d_rsub(1.0, g1);
+        Dual ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
+        const double A11 = a11.v, A22 = a22.v, G2 = g2.v, MS = ms.v;
+
+        // pass A: profile sums over ALL pixels (analyticLBFGS.jl:24-34)
+        double fc[PPT];
+        double S[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            const int p = threadIdx.x + k * THREADS;
+            fc[k] = 0.0;
+            if (p < npix) {
+                double du, dv, d;
+                pix(p, du, dv, d);
+                const double w1 = A11 * du + G2 * dv;
+                const double w2 = G2 * du + A22 * dv;
+                const double q = w1 * w1 + w2 * w2;
+                const double fv = exp(-(MS * q));
+                fc[k] = fv;
+                S[0] += fv;
+                S[1] += fv * q;
+                S[2] += fv * (w1 * du);
+                S[3] += fv * (w1 * dv + w2 * du);
+                S[4] += fv * (w2 * dv);
+            }
+        }
+        cta_sum<5, NWARPS>(S, scratch, buf);
+        const double A = 1.0 / S[0];
+        // pass B: residual sums over non-NaN pixels (analyticLBFGS.jl:36-44)
+        double T[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            const int p = threadIdx.x + k * THREADS;
+            if (p < npix) {
+                double du, dv, d;
+                pix(p, du, dv, d);
+                if (!isnan(d)) {
+                    const double w1 = A11 * du + G2 * dv;
+                    const double w2 = G2 * du + A22 * dv;
+                    const double q = w1 * w1 + w2 * w2;
+                    const double fv = fc[k];
+                    const double rho = A * fv - d;
+                    const double rf = rho * fv;
+                    T[0] += 0.5 * (rho * rho);
+                    T[1] += rf;
+                    T[2] += rf * q;
+                    T[3] += rf * (w1 * du);
+                    T[4] += rf * (w1 * dv + w2 * du);
+                    T[5] += rf * (w2 * dv);
+                }
+            }
+        }
+        cta_sum<6, NWARPS>(T, scratch, buf);
+        // chain rule: sum.d_j = -(ms.d_j S1 + 2 ms (a11.d_j S2 + g2.d_j S3 + a22.d_j S4))
+        f = T[0];
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const double dS = -(ms.d[j] * S[1] + 2.0 * MS * (a11.d[j] * S[2] + g2.d[j] * S[3] + a22.d[j] * S[4]));
+            const double dA = -(A / S[0]) * dS;
+            const double dT = -(ms.d[j] * T[2] + 2.0 * MS * (a11.d[j] * T[3] + g2.d[j] * T[4] + a22.d[j] * T[5]));
+            g[j] = dA * T[1] + A * dT;
+        }
+        nevals++;
+        xl[0] = xn[0]; xl[1] = xn[1]; xl[2] = xn[2];
+        fl = f; gl[0] = g[0]; gl[1] = g[1]; gl[2] = g[2];
+        have_last = true;
+    }
+};
+
+// variant without the register cache of exp() (any crop size): pass B recomputes the profile
+template <int THREADS>
+struct StarEvalGeneric {
+    static constexpr int NWARPS = THREADS / 32;
+    const double *crop;
+    const unsigned char *coff;
+    int n_a, pitch, npix;
+    unsigned magic;
+    double uc;
+    double *scratch;
+    int buf;
+    double xl[3], fl, gl[3];
+    bool have_last;
+    int nevals;
+
+    __device__ __forceinline__ void pix(int p, double &du, double &dv, double &d) const {
+        const unsigned v = __umulhi((unsigned)p, magic);
+        const unsigned u = (unsigned)p - v * (unsigned)n_a;
+        du = (double)(int)(u + 1) - uc;
+        dv = (double)(int)(v + 1) - uc;
+        d = crop[(size_t)v * pitch + coff[v] + u];
+    }
+    __device__ __noinline__ void fg(const double xn[3], double &f, double g[3]) {
+        if (have_last && xn[0] == xl[0] && xn[1] == xl[1] && xn[2] == xl[2]) {
+            f = fl; g[0] = gl[0]; g[1] = gl[1]; g[2] = gl[2];
+            return;
+        }
+        Dual sig = d_seed(xn[0], 0), e1 = d_seed(xn[1], 1), e2 = d_seed(xn[2], 2);
+        Dual sg = d_sq(sig);
+        Dual g1, g2;
+        e_to_g_dual(e1, e2, g1, g2);
+        Dual a11 = d_radd(1.0, g1), a22 = d_rsub(1.0, g1);
+        Dual ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
+        const double A11 = a11.v, A22 = a22.v, G2 = g2.v, MS = ms.v;
+        double S[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+        for (int p = threadIdx.x; p < npix; p += THREADS) {
+            double du, dv, d;
+            pix(p, du, dv, d);
+            const double w1 = A11 * du + G2 * dv;
+            const double w2 = G2 * du + A22 * dv;
+            const double q = w1 * w1 + w2 * w2;
+            const double fv = exp(-(MS * q));
+            S[0] += fv;
+            S[1] += fv * q;
+            S[2] += fv * (w1 * du);
+            S[3] += fv * (w1 * dv + w2 * du);
+            S[4] += fv * (w2 * dv);
+        }
+        cta_sum<5, NWARPS>(S, scratch, buf);
+        const double A = 1.0 / S[0];
+        double T[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        for (int p = threadIdx.x; p < npix; p += THREADS) {
+            double du, dv, d;
+            pix(p, du, dv, d);
+            if (!isnan(d)) {
+                const double w1 = A11 * du + G2 * dv;
+                const double w2 = G2 * du + A22 * dv;
+                const double q = w1 * w1 + w2 * w2;
+                const double fv = exp(-(MS * q));
+                const double rho = A * fv - d;
+                const double rf = rho * fv;
+                T[0] += 0.5 * (rho * rho);
+                T[1] += rf;
+                T[2] += rf * q;
+                T[3] += rf * (w1 * du);
+                T[4] += rf * (w1 * dv + w2 * du);
+                T[5] += rf * (w2 * dv);
+            }
+        }
+        cta_sum<6, NWARPS>(T, scratch, buf);
+        f = T[0];
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const double dS = -(ms.d[j] * S[1] + 2.0 * MS * (a11.d[j] * S[2] + g2.d[j] * S[3] + a22.d[j] * S[4]));
+            const double dA = -(A / S[0]) * dS;
+            const double dT = -(ms.d[j] * T[2] + 2.0 * MS * (a11.d[j] * T[3] + g2.d[j] * T[4] + a22.d[j] * T[5]));
+            g[j] = dA * T[1] + A * dT;
+        }
+        nevals++;
+        xl[0] = xn[0]; xl[1] = xn[1]; xl[2] = xn[2];
+        fl = f; gl[0] = g[0]; gl[1] = g[1]; gl[2] = g[2];
+        have_last = true;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// HagerZhang line search (LineSearches 7.2.0 defaults), value form: trial points are
+// carried as (alpha, phi, dphi, id) tuples instead of indices into a history array.  The only use the
+// algorithm makes of older history is "the most recent earlier point with phi <= phi_lim" during
+// bracketing, which is tracked incrementally.
+// ---------------------------------------------------------------------------------------------
+struct Pt {
+    double a, v, s;
+    int id;
+};
+enum { HZ_OK = 0, HZ_LSEXC = 1, HZ_ERROR = 2 };
+
+__device__ __forceinline__ double eps_of(double b) {   // Julia eps(x::Float64)
+    double a = fabs(b);
+    if (!isfinite(a)) return nan("");
+    if (a < DBL_MIN) return 4.9406564584124654e-324;
+    int e;
+    (void)frexp(a, &e);
+    return ldexp(DBL_EPSILON, e - 1);
+}
+__device__ __forceinline__ double nextfloat_(double x) { return nextafter(x, (double)INFINITY); }
+
+template <class Eval>
+struct LineSearch {
+    Eval &E;
+    double x[3], s[3];
+    double phi_0, dphi_0, phi_lim;
+    int npts;
+    bool err;
+    int ntrials;
+
+    __device__ LineSearch(Eval &e) : E(e), npts(0), err(false), ntrials(0) {}
+
+    __device__ __forceinline__ void phidphi(double alpha, double &phi, double &dphi) {
+        double xn[3], g[3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) xn[i] = add_(x[i], mul_(alpha, s[i]));
+        E.fg(xn, phi, g);
+        dphi = add_(add_(mul_(g[0], s[0]), mul_(g[1], s[1])), mul_(g[2], s[2]));
+        ntrials++;
+    }
+    __device__ __forceinline__ Pt push(double a, double v, double sl) {
+        Pt p = {a, v, sl, npts};
+        npts++;
+        return p;
+    }
+    __device__ __forceinline__ bool wolfe(double c, double phi_c, double dphi_c) const {
+        const double delta = 0.1, sigma = 0.9;
+        bool w1 = (mul_(delta, dphi_0) >= div_(sub_(phi_c, phi_0), c)) && (dphi_c >= mul_(sigma, dphi_0));
+        bool w2 = (mul_(sub_(mul_(2.0, delta), 1.0), dphi_0) >= dphi_c) && (dphi_c >= mul_(sigma, dphi_0)) &&
+                  (phi_c <= phi_lim);
+        return w1 || w2;
+    }
+    // HZ stage U3 (theta = 1/2)
+    __device__ void bisect(Pt ia, Pt ib, Pt &oa, Pt &ob) {
+        double a = ia.a, b = ib.a;
+        if (!(ia.s < 0.0) || !(ia.v <= phi_lim) || !(ib.s < 0.0) || !(ib.v > phi_lim) || !(b > a)) {
+            err = true; oa = ia; ob = ib; return;
+        }
+        while (sub_(b, a) > eps_of(b)) {
+            double d = div_(add_(a, b), 2.0), phi_d, g;
+            phidphi(d, phi_d, g);
+            if (!(isfinite(phi_d) && isfinite(g))) { err = true; break; }
+            Pt id = push(d, phi_d, g);
+            if (g >= 0.0) { oa = ia; ob = id; return; }
+            if (phi_d <= phi_lim) { a = d; ia = id; } else { b = d; ib = id; }
+        }
+        oa = ia; ob = ib;
+    }
+    // HZ stages U0-U3
+    __device__ void update(Pt ia, Pt ib, Pt ic, Pt &oa, Pt &ob) {
+        double a = ia.a, b = ib.a;
+        if (!(ia.s < 0.0) || !(ia.v <= phi_lim) || !(ib.s >= 0.0) || !(b > a)) {
+            err = true; oa = ia; ob = ib; return;
+        }
+        if (ic.a < a || ic.a > b) { oa = ia; ob = ib; return; }
+        if (ic.s >= 0.0) { oa = ia; ob = ic; return; }
+        if (ic.v <= phi_lim) { oa = ic; ob = ib; return; }
+        bisect(ia, ic, oa, ob);
+    }
+    __device__ __forceinline__ static double secant(double a, double b, double dphi_a, double dphi_b) {
+        return div_(sub_(mul_(a, dphi_b), mul_(b, dphi_a)), sub_(dphi_b, dphi_a));
+    }
+    // HZ stages S1-S4; returns iswolfe
+    __device__ bool secant2(Pt ia, Pt ib, Pt &oA, Pt &oB) {
+        oA = ia; oB = ib;
+        if (!(ia.s < 0.0 && ib.s >= 0.0)) { err = true; return false; }
+        double c = secant(ia.a, ib.a, ia.s, ib.s);
+        if (!isfinite(c)) { err = true; return false; }
+        double phi_c, dphi_c;
+        phidphi(c, phi_c, dphi_c);
+        if (!(isfinite(phi_c) && isfinite(dphi_c))) { err = true; return false; }
+        Pt ic = push(c, phi_c, dphi_c);
+        if (wolfe(c, phi_c, dphi_c)) { oA = ic; oB = ic; return true; }
+        Pt iA, iB;
+        update(ia, ib, ic, iA, iB);
+        if (err) return false;
+        const double a = iA.a, b = iB.a;
+        const bool movedB = (iB.id == ic.id), movedA = (iA.id == ic.id);
+        if (movedB) c = secant(ib.a, iB.a, ib.s, iB.s);
+        else if (movedA) c = secant(ia.a, iA.a, ia.s, iA.s);
+        if ((movedA || movedB) && a <= c && c <= b) {
+            phidphi(c, phi_c, dphi_c);
+            if (!(isfinite(phi_c) && isfinite(dphi_c))) { err = true; return false; }
+            ic = push(c, phi_c, dphi_c);
+            if (wolfe(c, phi_c, dphi_c)) { oA = ic; oB = ic; return true; }
+            Pt jA, jB;
+            update(iA, iB, ic, jA, jB);
+            if (err) return false;
+            iA = jA; iB = jB;
+        }
+        oA = iA; oB = iB;
+        return false;
+    }
+
+    // returns HZ_*; alpha_out = accepted step
+    __device__ int run(double c, double phi0, double dphi0, double &alpha_out) {
+        const double rho = 5.0, epsilon = 1e-6, gamma = 0.66, psi3 = 0.1;
+        const int linesearchmax = 50, iterfinitemax = 52;
+        double alphamax = (double)INFINITY;
+        alpha_out = 0.0;
+        phi_0 = phi0; dphi_0 = dphi0;
+        if (!(isfinite(phi0) && isfinite(dphi0))) return HZ_LSEXC;
+        if (dphi0 >= mul_(DBL_EPSILON, fabs(phi0))) return HZ_LSEXC;
+        else if (dphi0 >= 0.0) return HZ_OK;
+        npts = 0; err = false;
+        Pt p0 = push(0.0, phi0, dphi0);
+        phi_lim = add_(phi0, mul_(epsilon, fabs(phi0)));
+        if (!(c >= 0.0)) return HZ_ERROR;
+        if (c <= DBL_EPSILON) return HZ_OK;
+        if (!(isfinite(c) && c <= alphamax)) return HZ_ERROR;
+        double phi_c, dphi_c;
+        phidphi(c, phi_c, dphi_c);
+        int iterfinite = 1;
+        while (!(isfinite(phi_c) && isfinite(dphi_c)) && iterfinite < iterfinitemax) {
+            iterfinite++;
+            c = mul_(c, psi3);
+            phidphi(c, phi_c, dphi_c);
+        }
+        if (!(isfinite(phi_c) && isfinite(dphi_c))) return HZ_OK;
+        Pt last = push(c, phi_c, dphi_c);
+        // most recent point with phi <= phi_lim among the points pushed BEFORE `last`
+        Pt prevok = p0;
+        // bracketing, HZ stages B0-B3
+        bool isbracketed = false;
+        Pt ia = p0, ib = last;
+        int iter = 1;
+        double cold = -1.0;
+        while (!isbracketed && iter < linesearchmax) {
+            if (dphi_c >= 0.0) {
+                ib = last; ia = prevok;
+                isbracketed = true;
+            } else if (last.v > phi_lim) {
+                Pt na, nb;
+                bisect(p0, last, na, nb);
+                if (err) return HZ_ERROR;
+                ia = na; ib = nb;
+                isbracketed = true;
+            } else {
+                cold = c;
+                if (nextfloat_(cold) >= alphamax) { alpha_out = cold; return HZ_OK; }
+                c = mul_(c, rho);
+                if (c > alphamax) c = alphamax;
+                phidphi(c, phi_c, dphi_c);
+                iterfinite = 1;
+                while (!(isfinite(phi_c) && isfinite(dphi_c)) && c > nextfloat_(cold) && iterfinite < iterfinitemax) {
+                    alphamax = c;
+                    iterfinite++;
+                    c = div_(add_(cold, c), 2.0);
+                    phidphi(c, phi_c, dphi_c);
+                }
+                if (!(isfinite(phi_c) && isfinite(dphi_c))) { alpha_out = cold; return HZ_OK; }
+                if (last.v <= phi_lim) prevok = last;
+                last = push(c, phi_c, dphi_c);
+            }
+            iter++;
+        }
+        while (iter < linesearchmax) {
+            const double a = ia.a, b = ib.a;
+            if (!(b > a)) return HZ_ERROR;
+            if (sub_(b, a) <= eps_of(b)) { alpha_out = a; return HZ_OK; }
+            Pt iA, iB;
+            bool iswolfe = secant2(ia, ib, iA, iB);
+            if (err) return HZ_ERROR;
+            if (iswolfe) { alpha_out = iA.a; return HZ_OK; }
+            const double A = iA.a, B = iB.a;
+            if (!(B > A)) return HZ_ERROR;
+            if (sub_(B, A) < mul_(gamma, sub_(b, a))) {
+                if (nextfloat_(ia.v) >= ib.v && nextfloat_(iA.v) >= iB.v) { alpha_out = A; return HZ_OK; }
+                ia = iA; ib = iB;
+            } else {
+                c = div_(add_(A, B), 2.0);
+                phidphi(c, phi_c, dphi_c);
+                if (!(isfinite(phi_c) && isfinite(dphi_c))) return HZ_ERROR;
+                Pt ic = push(c, phi_c, dphi_c);
+                Pt na, nb;
+                update(iA, iB, ic, na, nb);
+                if (err) return HZ_ERROR;
+                ia = na; ib = nb;
+            }
+            iter++;
+        }
+        alpha_out = ia.a;
+        return HZ_LSEXC;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// Optim 1.7.8 LBFGS (m = 10, InitialStatic(alpha = 1), HagerZhang, scaleinvH0, no preconditioner) under
+// the generic optimize() loop -- SURVEY.md A.1.  Scalar work, executed redundantly by every thread.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double dot3(const double a[3], const double b[3]) {
+    return add_(add_(mul_(a[0], b[0]), mul_(a[1], b[1])), mul_(a[2], b[2]));
+}
+__device__ __forceinline__ double maxabs3(const double a[3]) { return fmax(fmax(fabs(a[0]), fabs(a[1])), fabs(a[2])); }
+
+template <class Eval>
+__device__ int lbfgs_fit(Eval &E, const double x0[3], double g_tol, int max_iter, double out_p[3], int &iters_out) {
+    constexpr int M = 10;
+    double x[3] = {x0[0], x0[1], x0[2]}, x_prev[3], g[3], g_prev[3], s[3], dx[3], dg[3];
+    double dxh[M][3], dgh[M][3], rho[M], tl_alpha[M];
+    double f, f_prev = nan("");
+    int pseudo = 0, iteration = 0, counter_f_tol = 0, status;
+    E.fg(x, f, g);
+    const bool g_conv0 = maxabs3(g) <= g_tol;
+    const bool stopped0 = !isfinite(f) || !isfinite(g[0]) || !isfinite(g[1]) || !isfinite(g[2]);
+    bool converged = g_conv0 || stopped0;
+    status = stopped0 ? SHOPT_FIT_NONFINITE : SHOPT_FIT_CONVERGED;
+    bool broke = false;
+    LineSearch<Eval> LS(E);
+    while (!converged && iteration < max_iter) {
+        iteration++;
+        pseudo++;
+        {   // two-loop recursion
+            const int lower = pseudo - M, upper = pseudo - 1;
+            double q[3] = {g[0], g[1], g[2]};
+            for (int index = upper; index >= lower; index--) {
+                if (index < 1) continue;
+                const int i = (index - 1) % M;
+                tl_alpha[i] = mul_(rho[i], dot3(dxh[i], q));
+#pragma unroll
+                for (int k = 0; k < 3; k++) q[k] = sub_(q[k], mul_(tl_alpha[i], dgh[i][k]));
+            }
+            if (pseudo > 1) {
+                const int i = (upper - 1) % M;
+                const double scaling = div_(dot3(dxh[i], dgh[i]), dot3(dgh[i], dgh[i]));
+#pragma unroll
+                for (int k = 0; k < 3; k++) s[k] = mul_(scaling, q[k]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 3; k++) s[k] = q[k];
+            }
+            for (int index = lower; index <= upper; index++) {
+                if (index < 1) continue;
+                const int i = (index - 1) % M;
+                const double beta = mul_(rho[i], dot3(dgh[i], s));
+#pragma unroll
+                for (int k = 0; k < 3; k++) s[k] = add_(s[k], mul_(dxh[i][k], sub_(tl_alpha[i], beta)));
+            }
+#pragma unroll
+            for (int k = 0; k < 3; k++) s[k] = mul_(-1.0, s[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++) g_prev[k] = g[k];
+        double dphi_0 = dot3(g, s);
+        if (dphi_0 >= 0.0) {   // reset_search_direction!
+            pseudo = 1;
+#pragma unroll
+            for (int k = 0; k < 3; k++) s[k] = -g[k];
+            dphi_0 = dot3(g, s);
+        }
+        const double phi_0 = f;
+        f_prev = phi_0;
+#pragma unroll
+        for (int k = 0; k < 3; k++) { x_prev[k] = x[k]; LS.x[k] = x[k]; LS.s[k] = s[k]; }
+        double alpha = 1.0;   // InitialStatic(alpha = 1.0, scaled = false)
+        const int hz = LS.run(alpha, phi_0, dphi_0, alpha);
+        if (hz == HZ_ERROR) { status = SHOPT_FIT_THREW; broke = true; break; }
+#pragma unroll
+        for (int k = 0; k < 3; k++) { dx[k] = mul_(alpha, s[k]); x[k] = add_(x[k], dx[k]); }
+        if (hz == HZ_LSEXC) { status = SHOPT_FIT_LS_FAILED; broke = true; break; }
+        E.fg(x, f, g);
+        // assess_convergence with x_abstol = x_reltol = f_abstol = f_reltol = 0
+        const double xchg = fmax(fmax(fabs(sub_(x[0], x_prev[0])), fabs(sub_(x[1], x_prev[1]))), fabs(sub_(x[2], x_prev[2])));
+        const bool x_conv = xchg <= 0.0;
+        const bool f_conv = fabs(sub_(f, f_prev)) <= 0.0;
+        const bool g_conv = maxabs3(g) <= g_tol;
+        counter_f_tol = f_conv ? counter_f_tol + 1 : 0;
+        converged = x_conv || g_conv || (counter_f_tol > 1);
+        // update_h!
+#pragma unroll
+        for (int k = 0; k < 3; k++) dg[k] = sub_(g[k], g_prev[k]);
+        const double rho_it = div_(1.0, dot3(dx, dg));
+        if (isinf(rho_it)) {
+            pseudo = 0;
+        } else {
+            const int idx = (pseudo - 1) % M;
+#pragma unroll
+            for (int k = 0; k < 3; k++) { dxh[idx][k] = dx[k]; dgh[idx][k] = dg[k]; }
+            rho[idx] = rho_it;
+        }
+        if (!isfinite(g[0]) || !isfinite(g[1]) || !isfinite(g[2])) { status = SHOPT_FIT_NONFINITE; broke = true; break; }
+    }
+    if (!broke && !(g_conv0 || stopped0)) status = converged ? SHOPT_FIT_CONVERGED : SHOPT_FIT_MAXITER;
+    if (status == SHOPT_FIT_THREW) {
+        out_p[0] = out_p[1] = out_p[2] = 0.0;   // shopt.jl:155-162 catch
+    } else {
+        out_p[0] = mul_(x[0], x[0]);
+        e_to_g(x[1], x[2], out_p[1], out_p[2]);
+    }
+    iters_out = iteration;
+    return status;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel: persistent CTAs pull star indices from a global counter; crop staging by bulk copies.
+// Shared memory layout (dynamic): [ mbarriers 2 x 8 B | pad to 16 | scratch 2*NWARPS*6 doubles |
+//   coff nbuf * n_a bytes (padded to 16) | crop buffers nbuf * n_a * pitch doubles ]
+// ---------------------------------------------------------------------------------------------
+struct FitArgs {
+    const double *stamps;
+    int r, c, n_a;
+    long long N;
+    const double *x0;
+    double g_tol;
+    int max_iter;
+    double *s, *g1, *g2;
+    int *status, *iters;
+    unsigned long long *counter;   // device work counter, zeroed before launch
+    int nbuf, pitch;
+};
+
+// Issue the bulk copies of one star's crop (thread 0 only).  A column whose 16-byte-aligned superset would
+// leave the batch buffer is skipped here and loaded with plain loads by load_edges().
+__device__ __forceinline__ void stage_issue(const FitArgs &a, long long star, double *crop, unsigned char *coff,
+                                            uint64_t *bar) {
+    const int r0 = (a.r - a.n_a) / 2, c0 = (a.c - a.n_a) / 2;   // get_middle_nxn: div(rows-n,2)+1, 1-based
+    const long long total = a.N * (long long)a.r * a.c;
+    const long long base = star * (long long)a.r * a.c + r0 + (long long)c0 * a.r;
+    const int mis0 = (int)(((uintptr_t)a.stamps >> 3) & 1);
+    uint32_t bytes = 0;
+    for (int v = 0; v < a.n_a; v++) {
+        const long long ge = base + (long long)v * a.r;
+        const int m = (int)((ge + mis0) & 1);
+        const long long start = ge - m;
+        const int len = (m + a.n_a + 1) & ~1;
+        coff[v] = (unsigned char)m;
+        if (start >= 0 && start + len <= total) {
+            bulk_g2s(crop + (size_t)v * a.pitch, a.stamps + start, (uint32_t)len * 8u, bar);
+            bytes += (uint32_t)len * 8u;
+        }
+    }
+    mbar_arrive_expect_tx(bar, bytes);
+}
+// plain-load fallback for the (at most two) columns stage_issue skipped; all threads
+__device__ __forceinline__ void load_edges(const FitArgs &a, long long star, double *crop) {
+    const int r0 = (a.r - a.n_a) / 2, c0 = (a.c - a.n_a) / 2;
+    const long long total = a.N * (long long)a.r * a.c;
+    const long long base = star * (long long)a.r * a.c + r0 + (long long)c0 * a.r;
+    const int mis0 = (int)(((uintptr_t)a.stamps >> 3) & 1);
+    for (int v = 0; v < a.n_a; v += (a.n_a > 1 ? a.n_a - 1 : 1)) {   // only the first and last column can be edges
+        const long long ge = base + (long long)v * a.r;
+        const int m = (int)((ge + mis0) & 1);
+        const long long start = ge - m;
+        const int len = (m + a.n_a + 1) & ~1;
+        if (!(start >= 0 && start + len <= total)) {
+            for (int u = threadIdx.x; u < a.n_a; u += blockDim.x) crop[(size_t)v * a.pitch + m + u] = a.stamps[ge + u];
+        }
+    }
+}
+
+template <int THREADS, int PPT, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int NWARPS = THREADS / 32;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);
+    long long *next_star = reinterpret_cast<long long *>(smem_raw + 16);   // 2 slots
+    double *scratch = reinterpret_cast<double *>(smem_raw + 32);
+    unsigned char *coff_base = smem_raw + 32 + 2 * NWARPS * 6 * sizeof(double);
+    const int coff_stride = (a.n_a + 15) & ~15;
+    double *crop_base = reinterpret_cast<double *>(coff_base + (size_t)a.nbuf * coff_stride);
+    const size_t crop_stride = (size_t)a.n_a * a.pitch;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+        next_star[0] = (long long)atomicAdd(a.counter, 1ULL);
+        if (next_star[0] < a.N) stage_issue(a, next_star[0], crop_base, coff_base, &bars[0]);
+    }
+    __syncthreads();
+    long long cur = next_star[0];
+    int b = 0, slot = 0;
+    uint32_t phase[2] = {0u, 0u};
+    using EvalT = typename std::conditional<(PPT > 0), StarEval<THREADS, (PPT > 0 ? PPT : 1)>, StarEvalGeneric<THREADS>>::type;
+    while (cur < a.N) {
+        // grab the next star and (double-buffered) start its copies before fitting the current one
+        if (threadIdx.x == 0) {
+            const long long nx = (long long)atomicAdd(a.counter, 1ULL);
+            next_star[slot ^ 1] = nx;
+            if (a.nbuf == 2 && nx < a.N)
+                stage_issue(a, nx, crop_base + (b ^ 1) * crop_stride, coff_base + (b ^ 1) * coff_stride, &bars[b ^ 1]);
+        }
+        double *crop = crop_base + b * crop_stride;
+        unsigned char *coff = coff_base + b * coff_stride;
+        mbar_wait(&bars[b], phase[b]);
+        phase[b] ^= 1u;
+        load_edges(a, cur, crop);
+        __syncthreads();   // coff + edge columns + next_star visible
+
+        EvalT E;
+        E.crop = crop; E.coff = coff; E.n_a = a.n_a; E.pitch = a.pitch; E.npix = a.n_a * a.n_a;
+        E.magic = (a.n_a > 1) ? (unsigned)((0x100000000ULL + a.n_a - 1) / (unsigned)a.n_a) : 0u;
+        E.uc = a.n_a / 2.0;
+        E.scratch = scratch; E.buf = 0; E.have_last = false; E.nevals = 0;
+        const double x0[3] = {a.x0[3 * cur + 0], a.x0[3 * cur + 1], a.x0[3 * cur + 2]};
+        double p[3];
+        int iters = 0;
+        const int st = lbfgs_fit(E, x0, a.g_tol, a.max_iter, p, iters);
+        if (threadIdx.x == 0) {
+            a.s[cur] = p[0]; a.g1[cur] = p[1]; a.g2[cur] = p[2];
+            if (a.status) a.status[cur] = st;
+            if (a.iters) a.iters[cur] = iters;
+        }
+        __syncthreads();   // everyone is done with crop[b] and scratch
+        const long long nx = next_star[slot ^ 1];
+        slot ^= 1;
+        if (a.nbuf == 2) {
+            b ^= 1;
+        } else if (nx < a.N) {
+            if (threadIdx.x == 0) {
+                fence_proxy_async();
+                stage_issue(a, nx, crop_base, coff_base, &bars[0]);
+            }
+        }
+        cur = nx;
+    }
+}
+
+// ---- launch ---------------------------------------------------------------------------------
+static size_t fit_smem_bytes(int nwarps, int n_a, int pitch, int nbuf) {
+    const size_t coff_stride = (size_t)((n_a + 15) & ~15);
+    return 32 + (size_t)2 * nwarps * 6 * sizeof(double) + nbuf * coff_stride + (size_t)nbuf * n_a * pitch * sizeof(double);
+}
+
+template <int THREADS, int PPT, int MINB>
+static int launch_fit(FitArgs a, cudaStream_t stream) {
+    const int nw = THREADS / 32;
+    a.pitch = (a.n_a + 2 + 1) & ~1;
+    a.nbuf = 2;
+    size_t smem = fit_smem_bytes(nw, a.n_a, a.pitch, 2);
+    if (smem > 110 * 1024) {   // keep two CTAs per SM where possible, else single-buffer
+        a.nbuf = 1;
+        smem = fit_smem_bytes(nw, a.n_a, a.pitch, 1);
+    }
+    if (smem > 227 * 1024) return SHOPT_E_UNSUPPORTED;
+    auto kern = fit_kernel<THREADS, PPT, MINB>;
+    SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS, smem));
+    if (per_sm < 1) return SHOPT_E_UNSUPPORTED;
+    long long grid = (long long)sm_count() * per_sm;
+    if (grid > a.N) grid = a.N;
+    SHOPT_CUDA_TRY(cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream));
+    kern<<<(unsigned)grid, THREADS, smem, stream>>>(a);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+
+int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n_a, const double *d_x0, double g_tol,
+                        int max_iter, double *d_s, double *d_g1, double *d_g2, int *d_status, int *d_iters,
+                        unsigned long long *d_counter, cudaStream_t stream) {
+    if (!d_stamps || !d_x0 || !d_s || !d_g1 || !d_g2 || !d_counter) return SHOPT_E_BADARG;
+    if (r < 1 || c < 1 || n_a < 1 || n_a > r || n_a > c || N < 0 || max_iter < 0) return SHOPT_E_BADARG;
+    if (N == 0) return SHOPT_OK;
+    FitArgs a;
+    a.stamps = d_stamps; a.r = r; a.c = c; a.n_a = n_a; a.N = N; a.x0 = d_x0; a.g_tol = g_tol; a.max_iter = max_iter;
+    a.s = d_s; a.g1 = d_g1; a.g2 = d_g2; a.status = d_status; a.iters = d_iters; a.counter = d_counter;
+    a.nbuf = 2; a.pitch = 0;
+    const int npix = n_a * n_a;
+    if (npix <= 1024) return launch_fit<128, 8, 4>(a, stream);
+    if (npix <= 4096) return launch_fit<256, 16, 2>(a, stream);
+    if (npix <= 6144) return launch_fit<256, 24, 2>(a, stream);
+    if (npix <= 16384) return launch_fit<512, 32, 1>(a, stream);
+    if (n_a <= 160) return launch_fit<512, 0, 1>(a, stream);
+    return SHOPT_E_UNSUPPORTED;
+}
+
+}  // namespace shopt

@@ -1,0 +1,93 @@
+"""Host-side mirror of the reference's per-star fitting stage (the loops of shopt/shopt.jl), one batched call
+per loop, on top of libshopt_b200.so.
+
+Two flavours of every call:
+  * numpy arrays in host memory  -> the library's host entry points (H2D, kernels, D2H inside the call);
+  * torch CUDA tensors           -> the `_dev` entry points on the current torch stream (no copies).
+torch is used for device memory and streams only.  Arrays follow Julia's memory order: a batch of N stamps
+of r x c pixels has shape (N, c, r), C-contiguous, so that pixel (u, v) (1-based) is arr[i, v-1, u-1].
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check, dp, ip, lp
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _ptr(a, t=dp):
+    return None if a is None else a.ctypes.data_as(t)
+
+
+def _stream():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dev_check(t, dtype):
+    import torch
+    assert t.is_cuda and t.is_contiguous() and t.dtype == dtype, "need a contiguous CUDA tensor of " + str(dtype)
+    assert t.device.index == torch.cuda.current_device(), "tensor is not on the current device"
+    return C.c_void_p(t.data_ptr())
+
+
+# ------------------------------------------------------------------------------------------------
+# (1) analytic profile fit: shopt.jl:130-164 (model stars) / :357-397 (learned stars)
+# ------------------------------------------------------------------------------------------------
+def fit_analytic_batch(stamps, n_a, x0, g_tol=1e-6, max_iter=1000):
+    """Optim.optimize(cost, g!, x0, LBFGS(), Options(g_tol)) for every star of the batch.
+
+    stamps (N, c, r); x0 (N, 3) start points [sigma, e1, e2] (the reference draws rand(3), shopt.jl:134).
+    Returns s, g1, g2, status, iters.  Failed stars (status == FIT_THREW) carry s = g1 = g2 = 0 like the
+    reference's catch (shopt.jl:155-162).
+    """
+    L = _lib.lib()
+    if _is_torch(stamps):
+        import torch
+        N, c, r = stamps.shape
+        dev = stamps.device
+        s = torch.empty(N, dtype=torch.float64, device=dev)
+        g1 = torch.empty_like(s)
+        g2 = torch.empty_like(s)
+        status = torch.empty(N, dtype=torch.int32, device=dev)
+        iters = torch.empty_like(status)
+        check(L.shopt_fit_analytic_batch_dev(_dev_check(stamps, torch.float64), r, c, N, n_a,
+                                             _dev_check(x0, torch.float64), g_tol, max_iter,
+                                             _dev_check(s, torch.float64), _dev_check(g1, torch.float64),
+                                             _dev_check(g2, torch.float64), _dev_check(status, torch.int32),
+                                             _dev_check(iters, torch.int32), _stream()))
+        return s, g1, g2, status, iters
+    stamps = _f64(stamps)
+    x0 = _f64(x0)
+    N, c, r = stamps.shape
+    assert x0.shape == (N, 3)
+    s, g1, g2 = np.zeros(N), np.zeros(N), np.zeros(N)
+    status, iters = np.zeros(N, np.int32), np.zeros(N, np.int32)
+    check(L.shopt_fit_analytic_batch(_ptr(stamps), r, c, N, n_a, _ptr(x0), g_tol, max_iter, _ptr(s), _ptr(g1),
+                                     _ptr(g2), _ptr(status, ip), _ptr(iters, ip)))
+    return s, g1, g2, status, iters
+
+
+def s_out_of_bounds(s, s_lo=0.075, s_hi=1.0):
+    """s-blacklist of shopt.jl:166-171 / failed list of :384-386; 0-based indices, ascending."""
+    s = _f64(s)
+    idx = np.zeros(max(len(s), 1), np.int64)
+    n = _lib.lib().shopt_s_out_of_bounds(_ptr(s), len(s), s_lo, s_hi, _ptr(idx, lp))
+    if n < 0:
+        check(int(n))
+    return idx[:n].copy()
+
+
+def last_timing():
+    """(h2d_ms, kernel_ms, d2h_ms) of the last host-buffer call, from CUDA events on the library's stream."""
+    ms = (C.c_double * 3)()
+    check(_lib.lib().shopt_last_timing(ms))
+    return tuple(ms)
