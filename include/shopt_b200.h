@@ -73,6 +73,13 @@ int shopt_fit_analytic_batch_dev(const double *d_stamps, int r, int c, int64_t N
                                  double *d_s, double *d_g1, double *d_g2,
                                  int32_t *d_status, int32_t *d_iters, void *stream);
 
+/* cost(params) / g!(storage, params) of analyticLBFGS.jl:8-46, 89-94 (costD / gD! :49-87, 96-101 on
+ * pixel-grid fits) for one parameter vector [sigma, e1, e2] per star:  f (N), g (3,N). */
+int shopt_analytic_cost_grad_batch(const double *stamps, int r, int c, int64_t N, int n_a,
+                                   const double *x, double *f, double *g);
+int shopt_analytic_cost_grad_batch_dev(const double *d_stamps, int r, int c, int64_t N, int n_a,
+                                       const double *d_x, double *d_f, double *d_g, void *stream);
+
 /* s-blacklist (shopt.jl:166-171) and learned-fit failed list (shopt.jl:384-386):
  * 0-based indices with s < s_lo or s > s_hi, ascending; returns the count (host arrays). */
 int64_t shopt_s_out_of_bounds(const double *s, int64_t N, double s_lo, double s_hi, int64_t *idx);

@@ -50,6 +50,8 @@ SIGNATURES = {
                                            dp, dp, dp, ip, ip]),
     "shopt_fit_analytic_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, C.c_double, C.c_int,
                                                vp, vp, vp, vp, vp, vp]),
+    "shopt_analytic_cost_grad_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, dp, dp, dp]),
+    "shopt_analytic_cost_grad_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, vp, vp, vp]),
     "shopt_s_out_of_bounds": (C.c_int64, [dp, C.c_int64, C.c_double, C.c_double, lp]),
     "shopt_pca_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_double, C.c_int, C.c_int, dp, ip, ip]),
     "shopt_pca_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_double, C.c_int, C.c_int,

@@ -157,6 +157,35 @@ int shopt_fit_analytic_batch(const double *stamps, int r, int c, int64_t N, int 
     return finish_timing(ctx);
 }
 
+int shopt_analytic_cost_grad_batch_dev(const double *d_stamps, int r, int c, int64_t N, int n_a, const double *d_x,
+                                       double *d_f, double *d_g, void *stream) {
+    if (!d_f || !d_g) return SHOPT_E_BADARG;
+    Ctx *ctx; TRY(get_ctx(&ctx));
+    return fit_analytic_launch(d_stamps, r, c, (long long)N, n_a, d_x, 0.0, 0, nullptr, nullptr, nullptr, nullptr,
+                               nullptr, ctx->next_counter(), (cudaStream_t)stream, d_f, d_g);
+}
+
+int shopt_analytic_cost_grad_batch(const double *stamps, int r, int c, int64_t N, int n_a, const double *x, double *f,
+                                   double *g) {
+    if (!stamps || !x || !f || !g) return SHOPT_E_BADARG;
+    if (r < 1 || c < 1 || n_a < 1 || n_a > r || n_a > c || N < 0) return SHOPT_E_BADARG;
+    Ctx *ctx; TRY(get_ctx(&ctx));
+    if (N == 0) return SHOPT_OK;
+    const size_t rc = (size_t)r * c, n = (size_t)N;
+    DevBuf dst, dx, dout;
+    TRY(dst.alloc(n * rc * 8)); TRY(dx.alloc(n * 24)); TRY(dout.alloc(n * 32));
+    cudaStream_t st = ctx->stream;
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(dst.p, stamps, n * rc * 8, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(dx.p, x, n * 24, cudaMemcpyHostToDevice, st));
+    double *df = dout.as<double>();
+    TRY(fit_analytic_launch(dst.as<double>(), r, c, (long long)N, n_a, dx.as<double>(), 0.0, 0, nullptr, nullptr,
+                            nullptr, nullptr, nullptr, ctx->next_counter(), st, df, df + n));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(f, df, n * 8, cudaMemcpyDeviceToHost, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(g, df + n, n * 24, cudaMemcpyDeviceToHost, st));
+    SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+    return SHOPT_OK;
+}
+
 int64_t shopt_s_out_of_bounds(const double *s, int64_t N, double s_lo, double s_hi, int64_t *idx) {
     if (!s || !idx || N < 0) return SHOPT_E_BADARG;
     int64_t n = 0;

@@ -648,6 +648,7 @@ struct FitArgs {
     int *status, *iters;
     unsigned long long *counter;   // device work counter, zeroed before launch
     int nbuf, pitch;
+    double *f_out, *g_out;         // non-null: evaluate cost / gradient at x0 only (cost, g! of analyticLBFGS.jl)
 };
 
 // Issue the bulk copies of one star's crop (thread 0 only).  A column whose 16-byte-aligned superset would
@@ -736,8 +737,16 @@ __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
         const double x0[3] = {a.x0[3 * cur + 0], a.x0[3 * cur + 1], a.x0[3 * cur + 2]};
         double p[3];
         int iters = 0;
-        const int st = lbfgs_fit(E, x0, a.g_tol, a.max_iter, p, iters);
-        if (threadIdx.x == 0) {
+        if (a.f_out) {   // cost(x0), g!(G, x0) only
+            double f, g[3];
+            E.fg(x0, f, g);
+            if (threadIdx.x == 0) {
+                a.f_out[cur] = f;
+                a.g_out[3 * cur + 0] = g[0]; a.g_out[3 * cur + 1] = g[1]; a.g_out[3 * cur + 2] = g[2];
+            }
+        }
+        const int st = a.f_out ? 0 : lbfgs_fit(E, x0, a.g_tol, a.max_iter, p, iters);
+        if (threadIdx.x == 0 && !a.f_out) {
             a.s[cur] = p[0]; a.g1[cur] = p[1]; a.g2[cur] = p[2];
             if (a.status) a.status[cur] = st;
             if (a.iters) a.iters[cur] = iters;
@@ -789,14 +798,15 @@ static int launch_fit(FitArgs a, cudaStream_t stream) {
 
 int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n_a, const double *d_x0, double g_tol,
                         int max_iter, double *d_s, double *d_g1, double *d_g2, int *d_status, int *d_iters,
-                        unsigned long long *d_counter, cudaStream_t stream) {
-    if (!d_stamps || !d_x0 || !d_s || !d_g1 || !d_g2 || !d_counter) return SHOPT_E_BADARG;
+                        unsigned long long *d_counter, cudaStream_t stream, double *d_f, double *d_g) {
+    if (!d_stamps || !d_x0 || !d_counter) return SHOPT_E_BADARG;
+    if (d_f ? !d_g : (!d_s || !d_g1 || !d_g2)) return SHOPT_E_BADARG;
     if (r < 1 || c < 1 || n_a < 1 || n_a > r || n_a > c || N < 0 || max_iter < 0) return SHOPT_E_BADARG;
     if (N == 0) return SHOPT_OK;
     FitArgs a;
     a.stamps = d_stamps; a.r = r; a.c = c; a.n_a = n_a; a.N = N; a.x0 = d_x0; a.g_tol = g_tol; a.max_iter = max_iter;
     a.s = d_s; a.g1 = d_g1; a.g2 = d_g2; a.status = d_status; a.iters = d_iters; a.counter = d_counter;
-    a.nbuf = 2; a.pitch = 0;
+    a.nbuf = 2; a.pitch = 0; a.f_out = d_f; a.g_out = d_g;
     const int npix = n_a * n_a;
     if (npix <= 1024) return launch_fit<128, 8, 4>(a, stream);
     if (npix <= 4096) return launch_fit<256, 16, 2>(a, stream);

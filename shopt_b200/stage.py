@@ -76,6 +76,17 @@ def fit_analytic_batch(stamps, n_a, x0, g_tol=1e-6, max_iter=1000):
     return s, g1, g2, status, iters
 
 
+def analytic_cost_grad_batch(stamps, n_a, x):
+    """cost(x_i) and g!(., x_i) of analyticLBFGS.jl:8-46, 89-94 for every star i; host arrays. Returns f (N), g (N,3)."""
+    stamps = _f64(stamps)
+    x = _f64(x)
+    N, c, r = stamps.shape
+    assert x.shape == (N, 3)
+    f, g = np.zeros(N), np.zeros((N, 3))
+    check(_lib.lib().shopt_analytic_cost_grad_batch(_ptr(stamps), r, c, N, n_a, _ptr(x), _ptr(f), _ptr(g)))
+    return f, g
+
+
 def s_out_of_bounds(s, s_lo=0.075, s_hi=1.0):
     """s-blacklist of shopt.jl:166-171 / failed list of :384-386; 0-based indices, ascending."""
     s = _f64(s)
