@@ -8,12 +8,12 @@
 #include <numeric>
 #include <vector>
 
-#include "common.cuh"
-#include "kernels.h"
+#include "api_ctx.h"
 
 namespace shopt {
 
 static thread_local char g_err[512] = "";
+void set_last_error_text(const char *text) { snprintf(g_err, sizeof g_err, "%s", text); }
 void set_last_error(const char *what, cudaError_t e) {
     snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(e));
 }
@@ -29,19 +29,17 @@ int sm_count() {
     return cached[dev];
 }
 
-// Per-thread, per-device context of the host entry points: one stream, timing events, a work counter.
-struct Ctx {
-    int dev = -1;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    unsigned long long *counter = nullptr;   // 8 slots, rotated per launch so overlapping launches never share one
-    unsigned slot = 0;
-    double ms[3] = {0, 0, 0};
-    unsigned long long *next_counter() { return counter + (slot++ & 7u); }
-};
+int Ctx::need_scratch(size_t bytes) {
+    if (bytes <= scratch_bytes) return SHOPT_OK;
+    if (scratch) { cudaDeviceSynchronize(); cudaFree(scratch); scratch = nullptr; scratch_bytes = 0; }
+    cudaError_t e = cudaMalloc(&scratch, bytes);
+    if (e != cudaSuccess) { set_last_error("cudaMalloc(scratch)", e); (void)cudaGetLastError(); return SHOPT_E_NOMEM; }
+    scratch_bytes = bytes;
+    return SHOPT_OK;
+}
 static thread_local Ctx g_ctx[16];
 
-static int get_ctx(Ctx **out) {
+int get_ctx(Ctx **out) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || n < 1) {
         snprintf(g_err, sizeof g_err, "no CUDA device");
@@ -62,21 +60,7 @@ static int get_ctx(Ctx **out) {
     return SHOPT_OK;
 }
 
-// device scratch that frees itself
-struct DevBuf {
-    void *p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) {
-        if (bytes == 0) bytes = 16;
-        cudaError_t e = cudaMalloc(&p, bytes);
-        if (e != cudaSuccess) { p = nullptr; set_last_error("cudaMalloc", e); (void)cudaGetLastError(); return SHOPT_E_NOMEM; }
-        return SHOPT_OK;
-    }
-    template <class T> T *as() const { return static_cast<T *>(p); }
-};
-#define TRY(expr) do { int _rc = (expr); if (_rc != SHOPT_OK) return _rc; } while (0)
-
-static int finish_timing(Ctx *c) {
+int finish_timing(Ctx *c) {
     SHOPT_CUDA_TRY(cudaStreamSynchronize(c->stream));
     for (int i = 0; i < 3; i++) {
         float ms = 0.f;

@@ -10,4 +10,17 @@ int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n
                         unsigned long long *d_counter, cudaStream_t stream, double *d_f = nullptr,
                         double *d_g = nullptr);   // d_f/d_g non-null: evaluate cost and gradient at x0 only
 
+// polyfit.cu  (rc = r*c; idx may be null = stars 0..n-1; scratch: polyfit_scratch_bytes(rc, n, degree))
+size_t polyfit_scratch_bytes(long long rc, long long n, int degree);
+int polyfit_normal_launch(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+                          long long n, int degree, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st);
+int polyfit_solve_launch(const double *acc, long long rc, int degree, double *poly, int *info, cudaStream_t st);
+int polyfit_mse_launch(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+                       long long n, int degree, const double *poly, double *mse, double *scratch, size_t scratch_bytes,
+                       cudaStream_t st);
+int psf_at_launch(const double *poly, long long rc, int degree, const double *u, const double *v, long long M,
+                  double *out, cudaStream_t st);
+int small_median_launch(const double *pgf, long long rc, const long long *idx, int n, int degree, double *poly,
+                        cudaStream_t st);
+
 }  // namespace shopt

@@ -102,3 +102,50 @@ def last_timing():
     ms = (C.c_double * 3)()
     check(_lib.lib().shopt_last_timing(ms))
     return tuple(ms)
+
+
+# ------------------------------------------------------------------------------------------------
+# (3) per-pixel polynomial interpolation with outlier-star rejection: shopt.jl:492-577
+# ------------------------------------------------------------------------------------------------
+def num_terms(degree):
+    return (degree + 1) * (degree + 2) // 2
+
+
+def polyfit(pgf, u, v, train_idx, degree, iterations=3, median_constraint=False, sigma_clip=False):
+    """`iterations` rounds of polynomial_optimizer per pixel (interpolate.jl:105-147), per-star MSE and
+    worst_10_percent rejection (shopt.jl:513-575).  pgf (N, c, r) host array; train_idx: 0-based star indices
+    (the reference's randperm split, shopt.jl:472-490, is an input).
+    Returns dict(poly (K, c, r), mse, kept, n_per_round) like the oracle's driver."""
+    pgf = _f64(pgf); u = _f64(u); v = _f64(v)
+    train_idx = np.ascontiguousarray(train_idx, dtype=np.int64)
+    N, c, r = pgf.shape
+    K = num_terms(degree)
+    nt = len(train_idx)
+    poly = np.zeros((K, c, r))
+    mse = np.zeros(max(nt, 1)); kept = np.zeros(max(nt, 1), np.int64)
+    n_kept = C.c_int64(); npr = np.zeros(max(iterations, 1), np.int64)
+    check(_lib.lib().shopt_polyfit(_ptr(pgf), r, c, N, _ptr(u), _ptr(v), _ptr(train_idx, lp), nt, degree, iterations,
+                                   int(median_constraint), int(sigma_clip), _ptr(poly), _ptr(mse), _ptr(kept, lp),
+                                   C.byref(n_kept), _ptr(npr, lp)))
+    n_last = int(npr[iterations - 1]) if iterations > 0 else 0
+    return dict(poly=poly, mse=mse[:n_last].copy(), kept=kept[:n_kept.value].copy(), n_per_round=npr[:iterations].copy())
+
+
+def worst_10_percent(err, sigma_clip=False):
+    """shopt.jl:513-532: positions of the worst ceil(10 %) errors (stable descending) or the 3-sigma variant."""
+    err = _f64(err)
+    idx = np.zeros(max(len(err), 1), np.int64)
+    n = _lib.lib().shopt_worst_10_percent(_ptr(err), len(err), int(sigma_clip), _ptr(idx, lp))
+    if n < 0:
+        check(int(n))
+    return idx[:n].copy()
+
+
+def psf_at_batch(poly, degree, u, v):
+    """reader.jl:40-68 p(u, v, polMatrix, degree) for M positions: (M, c, r), each stamp divided by its sum."""
+    poly = _f64(poly); u = _f64(np.atleast_1d(u)); v = _f64(np.atleast_1d(v))
+    K, c, r = poly.shape
+    assert K == num_terms(degree) and u.shape == v.shape
+    out = np.zeros((len(u), c, r))
+    check(_lib.lib().shopt_psf_at_batch(_ptr(poly), r, c, degree, _ptr(u), _ptr(v), len(u), _ptr(out)))
+    return out

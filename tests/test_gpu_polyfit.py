@@ -1,0 +1,109 @@
+"""GPU parity: per-pixel polynomial interpolation (polyfit.cu) through the C ABI against the CPU oracle.
+Tolerance (north_star): polynomial coefficients within 1e-6 relative; outlier selection and star indexing bit-exact."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def make_case(seed, N, r, c, degree, noise=0.01, n_out=6, n_train=None):
+    rng = np.random.default_rng(seed)
+    u, v = rng.uniform(-1, 1, N), rng.uniform(-1, 1, N)
+    K = (degree + 1) * (degree + 2) // 2
+    terms = [(p, q) for p in range(degree + 1) for q in range(degree + 1 - p)]
+    V = np.stack([u ** p * v ** q for p, q in terms], axis=1)
+    truth = rng.normal(size=(K, c, r)) + 2.0
+    pgf = np.einsum("nk,kcr->ncr", V, truth) + noise * rng.normal(size=(N, c, r))
+    if n_out:
+        pgf[rng.choice(N, n_out, replace=False)] += rng.uniform(0.5, 2.0, (n_out, 1, 1))
+    train = rng.permutation(N)[:n_train if n_train is not None else int(0.8 * N)]
+    return pgf, u, v, train, truth
+
+
+def coef_close(a, b, rtol=1e-6):
+    scale = np.abs(b).max(axis=(1, 2), keepdims=True)       # per-term scale: coefficients of a term share a magnitude
+    return np.max(np.abs(a - b) / scale) <= rtol
+
+
+@pytest.mark.parametrize("degree,N,r,c,iterations", [(1, 300, 9, 7, 3), (3, 500, 13, 13, 3), (2, 200, 5, 40, 1),
+                                                     (5, 600, 11, 11, 3), (4, 300, 8, 8, 2), (6, 500, 6, 6, 2),
+                                                     (3, 2000, 33, 31, 3)])
+def test_polyfit_matches_oracle(stage, orc, degree, N, r, c, iterations):
+    pgf, u, v, train, _ = make_case(degree * 7 + N, N, r, c, degree)
+    got = stage.polyfit(pgf, u, v, train, degree, iterations)
+    want = orc.polyfit(pgf, u, v, train, degree, iterations, nthreads=orc.max_threads())
+    assert got["n_per_round"].tolist() == want["n_per_round"].tolist()
+    assert got["kept"].tolist() == want["kept"].tolist()            # outlier selection bit-exact
+    assert coef_close(got["poly"], want["poly"])
+    assert np.allclose(got["mse"], want["mse"], rtol=1e-9)
+
+
+def test_sigma_clip_variant_and_exact_polynomial(stage, orc):
+    pgf, u, v, train, truth = make_case(5, 400, 10, 10, 3, noise=0.0, n_out=0)
+    got = stage.polyfit(pgf, u, v, train, 3, 2, sigma_clip=True)
+    assert coef_close(got["poly"], truth, 1e-9)                      # pixels that ARE polynomials give them back
+    pgf, u, v, train, _ = make_case(6, 400, 10, 10, 2, n_out=5)
+    got = stage.polyfit(pgf, u, v, train, 2, 3, sigma_clip=True)
+    want = orc.polyfit(pgf, u, v, train, 2, 3, sigma_clip=True)
+    assert got["kept"].tolist() == want["kept"].tolist() and coef_close(got["poly"], want["poly"])
+
+
+def test_small_training_sets_and_zero_rounds(stage, orc):
+    pgf, u, v, _, _ = make_case(8, 30, 6, 6, 1)
+    for n in (0, 1, 2, 3, 4):                                        # interpolate.jl:142-145: [median, 0, 0]
+        train = np.arange(n) * 2
+        got = stage.polyfit(pgf, u, v, train, 1, 1)
+        if n == 0:
+            continue
+        want = orc.polyfit(pgf, u, v, train, 1, 1)
+        assert np.allclose(got["poly"], want["poly"], rtol=1e-15, atol=0)
+        assert np.allclose(got["mse"], want["mse"], rtol=1e-12)
+    got = stage.polyfit(pgf, u, v, np.arange(20), 1, 0)
+    assert np.all(got["poly"] == 1.0)                                # ones(r, c, K), shopt.jl:492
+    got = stage.polyfit(pgf, u, v, np.arange(12), 1, 3)              # 12 -> 10 -> 9 stars
+    want = orc.polyfit(pgf, u, v, np.arange(12), 1, 3)
+    assert got["n_per_round"].tolist() == want["n_per_round"].tolist() == [12, 10, 9]
+    assert got["kept"].tolist() == want["kept"].tolist()
+
+
+def test_psf_at_batch(stage, orc):
+    rng = np.random.default_rng(4)
+    for degree, r, c in [(1, 9, 9), (3, 31, 29), (5, 12, 12)]:
+        K = (degree + 1) * (degree + 2) // 2
+        poly = rng.normal(size=(K, c, r)) * 0.1
+        poly[0] += 1.0
+        u, v = rng.uniform(-1, 1, 17), rng.uniform(-1, 1, 17)
+        got = stage.psf_at_batch(poly, degree, u, v)
+        for m in range(17):
+            want = orc.psf_at(poly, degree, u[m], v[m])
+            assert np.allclose(got[m], want, rtol=1e-10, atol=1e-15)
+            assert np.isclose(got[m].sum(), 1.0, rtol=1e-12)
+
+
+def test_building_blocks_shard_additively(stage):
+    """Multi-GPU contract: the [V'V | V'P] accumulators of disjoint star shards add up to the accumulator of the
+    union (what the NCCL all-reduce relies on), and linearity in the pixel-grid fits holds."""
+    import ctypes as C
+    import torch
+    from shopt_b200 import _lib
+    L = _lib.lib()
+    N, r, c, deg = 900, 21, 19, 3
+    g = torch.Generator(device="cuda").manual_seed(1)
+    pgf = torch.rand(N, c, r, generator=g, device="cuda", dtype=torch.float64)
+    u = torch.rand(N, generator=g, device="cuda", dtype=torch.float64) * 2 - 1
+    v = torch.rand(N, generator=g, device="cuda", dtype=torch.float64) * 2 - 1
+    n_acc = L.shopt_polyfit_acc_len(r, c, deg)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def acc_of(idx):
+        idx = idx.contiguous()
+        acc = torch.empty(n_acc, device="cuda", dtype=torch.float64)
+        _lib.check(L.shopt_polyfit_normal_dev(pgf.data_ptr(), r, c, u.data_ptr(), v.data_ptr(), idx.data_ptr(), len(idx),
+                                              deg, acc.data_ptr(), st))
+        torch.cuda.synchronize()
+        return acc
+    idx = torch.randperm(N, device="cuda")[:700]
+    whole = acc_of(idx)
+    parts = acc_of(idx[:300]) + acc_of(idx[300:450]) + acc_of(idx[450:])
+    assert torch.allclose(whole, parts, rtol=1e-12, atol=1e-12)
+    assert torch.equal(acc_of(idx), whole)                            # deterministic: no floating-point atomics
