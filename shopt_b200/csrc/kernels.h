@@ -23,4 +23,12 @@ int psf_at_launch(const double *poly, long long rc, int degree, const double *u,
 int small_median_launch(const double *pgf, long long rc, const long long *idx, int n, int degree, double *poly,
                         cudaStream_t st);
 
+// pixelgrid.cu  (scratch: pca_scratch_bytes(r, c, ncomp), 0 when the stamp fits shared memory)
+size_t pca_scratch_bytes(int r, int c, int ncomp);
+int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, double pratio, int lanczos_a, int unity_sum,
+               double *d_pgf, int *d_k, int *d_status, unsigned long long *d_counter, double *scratch,
+               size_t scratch_bytes, cudaStream_t st);
+int smooth_launch(const double *d_in, int r, int c, long long N, int lanczos_a, int nan_to_zero_flag, double *d_out,
+                  cudaStream_t st);
+
 }  // namespace shopt

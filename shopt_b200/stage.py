@@ -149,3 +149,39 @@ def psf_at_batch(poly, degree, u, v):
     out = np.zeros((len(u), c, r))
     check(_lib.lib().shopt_psf_at_batch(_ptr(poly), r, c, degree, _ptr(u), _ptr(v), len(u), _ptr(out)))
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# (2) pixel-grid fit: shopt.jl:281-314 (mode "PCA") and :316-348 (mode "smooth")
+# ------------------------------------------------------------------------------------------------
+def pca_batch(stamps, ncomp=50, pratio=0.99, lanczos_a=3, unity_sum=False):
+    """nanToZero -> pca_image(., ncomp) -> smooth(., lanczos_a) (or ./sum when unity_sum) per star.
+    stamps (N, c, r) host array or CUDA tensor.  Returns pgf (N, c, r), k (components kept), status (PCA_*);
+    failed stars carry zeros like the reference's catch (shopt.jl:305-309)."""
+    L = _lib.lib()
+    if _is_torch(stamps):
+        import torch
+        N, c, r = stamps.shape
+        pgf = torch.empty_like(stamps)
+        k = torch.empty(N, dtype=torch.int32, device=stamps.device)
+        status = torch.empty_like(k)
+        check(L.shopt_pca_batch_dev(_dev_check(stamps, torch.float64), r, c, N, ncomp, pratio, lanczos_a, int(unity_sum),
+                                    _dev_check(pgf, torch.float64), _dev_check(k, torch.int32),
+                                    _dev_check(status, torch.int32), _stream()))
+        return pgf, k, status
+    stamps = _f64(stamps)
+    N, c, r = stamps.shape
+    pgf = np.zeros_like(stamps)
+    k, status = np.zeros(N, np.int32), np.zeros(N, np.int32)
+    check(L.shopt_pca_batch(_ptr(stamps), r, c, N, ncomp, pratio, lanczos_a, int(unity_sum), _ptr(pgf), _ptr(k, ip),
+                            _ptr(status, ip)))
+    return pgf, k, status
+
+
+def smooth_batch(stamps, lanczos_a=3, nan_to_zero=False):
+    """smooth(data, a) of dataPreprocessing.jl:112-139 per star (mode "smooth": nan_to_zero=True)."""
+    stamps = _f64(stamps)
+    N, c, r = stamps.shape
+    out = np.zeros_like(stamps)
+    check(_lib.lib().shopt_smooth_batch(_ptr(stamps), r, c, N, lanczos_a, int(nan_to_zero), _ptr(out)))
+    return out
