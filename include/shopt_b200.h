@@ -148,11 +148,11 @@ int shopt_psf_at_batch(const double *poly, int r, int c, int degree, const doubl
 int shopt_psf_at_batch_dev(const double *d_poly, int r, int c, int degree, const double *d_u,
                            const double *d_v, int64_t M, double *d_stars_out, void *stream);
 
-/* ---- whole stage on one GPU, host buffers (what shopt.jl's four loops become) -----------------
- * model fit -> s-blacklist -> PCA -> learned fit -> failed list -> polyfit.  Parameters mirror
- * shopt.yml (see shopt_params).  Outputs are sized for N stars; blacklisted / failed stars are
- * reported through the index lists and are excluded from the training set exactly like the
- * reference's splices (shopt.jl:177-184, 405-417). */
+/* ---- the whole stage: what shopt.jl's loops :130-184, :281-314, :357-417, :472-577 become ---------
+ * model fit -> s-blacklist -> PCA pixel-grid fit -> learned fit -> failed list -> training split -> polyfit rounds.
+ * Parameters mirror shopt.yml (shopt_params).  Stars keep their ORIGINAL indices: instead of splicing arrays like the
+ * reference (shopt.jl:177-184, 405-417) the stage reports per-star flags, and blacklisted / failed stars are excluded
+ * from the training set exactly as the splices would. */
 typedef struct shopt_params {
     int    n_a;                 /* AnalyticFitParams.analyticFitStampSize                        */
     double g_tol_model;         /* AnalyticFitParams.minGradientAnalyticModel                    */
@@ -170,6 +170,47 @@ typedef struct shopt_params {
     int    sigma_clip;          /* outlier_sigma_clipping                                        */
 } shopt_params;
 void shopt_default_params(shopt_params *p);     /* README.md:300-330 documented defaults          */
+
+#define SHOPT_FLAG_BLACKLISTED 1   /* model s out of [s_lo, s_hi]            (shopt.jl:166-171)   */
+#define SHOPT_FLAG_PCA_FAILED  2   /* pixel-grid fit failed -> zeros         (shopt.jl:305-309)   */
+#define SHOPT_FLAG_LEARNED_OOB 4   /* learned s out of bounds                (shopt.jl:384-386)   */
+#define SHOPT_FLAG_TRAINING    8   /* star was in the training split                              */
+#define SHOPT_FLAG_REJECTED   16   /* dropped by worst_10_percent in some round (shopt.jl:557-575) */
+
+/* Sum-all-reduce over the ranks of a sharded run, supplied by the host program (NCCL / torch.distributed / MPI):
+ * in-place on a DEVICE buffer of `count` elements, dtype 0 = float64, 1 = int32, enqueued on (or ordered after)
+ * `stream`; returns 0 on success.  The only exchange steps of the stage are these all-reduces:
+ * the [V'V | V'P] normal-equation partial sums, and two zero-padded gathers (survivor flags, per-star errors). */
+typedef int (*shopt_allreduce_fn)(void *d_buf, int64_t count, int dtype, void *stream, void *user);
+
+typedef struct shopt_stage_io {
+    /* inputs: this rank's shard (device pointers in shopt_stage_run_dev, host pointers in shopt_stage_run) */
+    const double *stamps;        /* (r, c, n_local)                                               */
+    int r, c;
+    int64_t n_local;
+    const double *u, *v;         /* (n_local)                                                     */
+    const double *x0_model;      /* (3, n_local) start points of the model fit   (shopt.jl:134)   */
+    const double *x0_learned;    /* (3, n_local) start points of the learned fit (shopt.jl:362)   */
+    int64_t n_global, offset;    /* size of the whole catalogue and this shard's first star       */
+    const int64_t *perm;         /* HOST, (n_global): the randperm of shopt.jl:474 over ORIGINAL indices; the training
+                                    set is the first round(training_ratio * n_survivors) survivors in this order   */
+    /* outputs, shard-sized */
+    double *model;               /* 3 x n_local: s[0..n), g1[0..n), g2[0..n) of the model fit      */
+    double *learned;             /* 3 x n_local of the learned fit, same layout                   */
+    double *pgf;                 /* (r, c, n_local) pixel-grid fits; may be NULL in shopt_stage_run */
+    int32_t *flags;              /* (n_local) SHOPT_FLAG_*                                        */
+    int32_t *pca_k;              /* (n_local) components kept; may be NULL                        */
+    /* outputs, replicated on every rank */
+    double *poly;                /* (r, c, K) PolynomialMatrix                                    */
+    int64_t *n_per_round;        /* HOST (iterations): training-set size of each round; may be NULL */
+    int64_t counts[4];           /* HOST: blacklisted, failed, training stars, kept after the last applied rejection */
+} shopt_stage_io;
+
+/* device-resident shard; comm == NULL runs a single GPU.  Blocks until the stage is done (the outlier selection
+ * between rounds runs on the host). */
+int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream);
+/* host buffers, one GPU: H2D, stage, D2H */
+int shopt_stage_run(const shopt_params *p, shopt_stage_io *io);
 
 #ifdef __cplusplus
 }

@@ -39,6 +39,17 @@ class Params(C.Structure):
                 ("sigma_clip", C.c_int)]
 
 
+class StageIO(C.Structure):
+    """struct shopt_stage_io."""
+    _fields_ = [("stamps", vp), ("r", C.c_int), ("c", C.c_int), ("n_local", C.c_int64), ("u", vp), ("v", vp),
+                ("x0_model", vp), ("x0_learned", vp), ("n_global", C.c_int64), ("offset", C.c_int64), ("perm", vp),
+                ("model", vp), ("learned", vp), ("pgf", vp), ("flags", vp), ("pca_k", vp), ("poly", vp),
+                ("n_per_round", vp), ("counts", C.c_int64 * 4)]
+
+
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p)
+FLAG_BLACKLISTED, FLAG_PCA_FAILED, FLAG_LEARNED_OOB, FLAG_TRAINING, FLAG_REJECTED = 1, 2, 4, 8, 16
+
 # name -> (restype, argtypes); every symbol include/shopt_b200.h declares
 SIGNATURES = {
     "shopt_b200_version": (C.c_int, []),
@@ -68,6 +79,8 @@ SIGNATURES = {
     "shopt_psf_at_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int, dp, dp, C.c_int64, dp]),
     "shopt_psf_at_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int64, vp, vp]),
     "shopt_default_params": (None, [C.POINTER(Params)]),
+    "shopt_stage_run_dev": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO), C.c_void_p, C.c_void_p, C.c_void_p]),
+    "shopt_stage_run": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO)]),
 }
 
 _LIB = None

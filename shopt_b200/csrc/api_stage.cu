@@ -1,0 +1,197 @@
+// api_stage.cu -- the whole per-star fitting stage as one call (include/shopt_b200.h, shopt_stage_run*): the host
+// control flow of shopt/shopt.jl:130-184, 281-314, 357-417, 472-577 around the kernels, for one GPU or one shard of a
+// multi-GPU run (the caller supplies the all-reduce).
+#include <algorithm>
+#include <cmath>
+#include <numeric>
+#include <vector>
+
+#include "api_ctx.h"
+
+namespace shopt {
+
+// flags[i] |= BLACKLISTED from the model s (shopt.jl:166-171); |= PCA_FAILED / LEARNED_OOB (shopt.jl:305-309, 384-386)
+__global__ void flag_kernel(const double *__restrict__ s_model, const int *__restrict__ pca_status,
+                            const double *__restrict__ s_learned, long long n, double lo, double hi, int *__restrict__ flags) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int f = 0;
+    const double sm = s_model[i];
+    if (sm < lo || sm > hi) f |= SHOPT_FLAG_BLACKLISTED;
+    if (pca_status[i] == SHOPT_PCA_FAILED) f |= SHOPT_FLAG_PCA_FAILED;
+    const double sl = s_learned[i];
+    if (sl < lo || sl > hi) f |= SHOPT_FLAG_LEARNED_OOB;
+    flags[i] = f;
+}
+
+}  // namespace shopt
+
+using namespace shopt;
+
+extern "C" {
+
+int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream) {
+    if (!p || !io || !io->stamps || !io->u || !io->v || !io->x0_model || !io->x0_learned || !io->model || !io->learned ||
+        !io->pgf || !io->flags || !io->poly)
+        return SHOPT_E_BADARG;
+    const int r = io->r, c = io->c;
+    const long long n = io->n_local, NG = io->n_global, off = io->offset;
+    if (r < 1 || c < 2 || n < 0 || NG < n || off < 0 || off + n > NG || (NG > 0 && !io->perm)) return SHOPT_E_BADARG;
+    if (p->degree < 0 || p->degree > 8 || p->iterations < 0 || p->n_a < 1 || p->n_a > r || p->n_a > c) return SHOPT_E_BADARG;
+    if (p->median_constraint) return SHOPT_E_UNSUPPORTED;
+    Ctx *ctx; TRY(get_ctx(&ctx));
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long rc = (long long)r * c;
+    const int K = (p->degree + 1) * (p->degree + 2) / 2;
+    const size_t nn = (size_t)std::max<long long>(n, 1);
+    DevBuf dint, dacc, didx, dmse, dkeep, dinfo;
+    TRY(dint.alloc(nn * 12));                       // fit status | fit iters (reused) | pca status
+    int *d_fst = dint.as<int>(), *d_fit = d_fst + nn, *d_pst = d_fit + nn;
+    size_t scratch = std::max(pca_scratch_bytes(r, c, p->pca_terms), polyfit_scratch_bytes(rc, n, p->degree));
+    TRY(ctx->need_scratch(scratch));
+
+    // ---- model fit, pixel-grid fit, learned fit (every star of the shard; flags decide who counts) ----
+    double *m = io->model, *l = io->learned;
+    TRY(fit_analytic_launch(io->stamps, r, c, n, p->n_a, io->x0_model, p->g_tol_model, p->max_iter, m, m + n, m + 2 * n,
+                            d_fst, d_fit, ctx->next_counter(), st));
+    TRY(pca_launch(io->stamps, r, c, n, p->pca_terms, p->pratio, p->lanczos, p->unity_sum, io->pgf, io->pca_k, d_pst,
+                   ctx->next_counter(), (double *)ctx->scratch, ctx->scratch_bytes, st));
+    TRY(fit_analytic_launch(io->pgf, r, c, n, p->n_a, io->x0_learned, p->g_tol_learned, p->max_iter, l, l + n, l + 2 * n,
+                            d_fst, d_fit, ctx->next_counter(), st));
+    if (n > 0) flag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(m, d_pst, l, n, p->s_lo, p->s_hi, io->flags);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    std::vector<int> flags((size_t)n);
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(flags.data(), io->flags, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+
+    // ---- survivors of the whole catalogue (a zero-padded gather through the all-reduce) ----
+    std::vector<int> gflag((size_t)NG, 0);
+    for (long long i = 0; i < n; i++) gflag[(size_t)(off + i)] = flags[(size_t)i] + 32;   // +32 marks "reported"
+    if (comm) {
+        TRY(dkeep.alloc((size_t)std::max<long long>(NG, 1) * 4));
+        SHOPT_CUDA_TRY(cudaMemcpyAsync(dkeep.p, gflag.data(), (size_t)NG * 4, cudaMemcpyHostToDevice, st));
+        if (comm(dkeep.p, NG, 1, stream, comm_user) != 0) { set_last_error_text("all-reduce callback failed"); return SHOPT_E_CUDA; }
+        SHOPT_CUDA_TRY(cudaMemcpyAsync(gflag.data(), dkeep.p, (size_t)NG * 4, cudaMemcpyDeviceToHost, st));
+        SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    long long n_black = 0, n_failed = 0, n_surv = 0;
+    for (long long g = 0; g < NG; g++) {
+        const int f = gflag[(size_t)g] & 31;
+        if (f & SHOPT_FLAG_BLACKLISTED) n_black++;
+        else if (f & (SHOPT_FLAG_PCA_FAILED | SHOPT_FLAG_LEARNED_OOB)) n_failed++;
+        else n_surv++;
+    }
+    // ---- training split: first round(training_ratio * n_surv) survivors in perm order (shopt.jl:472-478) ----
+    const long long n_train = (long long)std::nearbyint(p->training_ratio * (double)n_surv);   // round half to even
+    std::vector<long long> train;                    // global star ids, training order
+    train.reserve((size_t)std::max<long long>(n_train, 0));
+    for (long long i = 0; i < NG && (long long)train.size() < n_train; i++) {
+        const long long g = io->perm[i];
+        if (g < 0 || g >= NG) return SHOPT_E_BADARG;
+        if ((gflag[(size_t)g] & 31) == 0) train.push_back(g);
+    }
+    for (long long g : train) if (g >= off && g < off + n) flags[(size_t)(g - off)] |= SHOPT_FLAG_TRAINING;
+
+    // ---- polyfit rounds (shopt.jl:534-577) ----
+    const long long acc_len = (long long)K * K + (long long)K * rc;
+    TRY(dacc.alloc((size_t)acc_len * 8)); TRY(didx.alloc((size_t)std::max<long long>(n, 1) * 8));
+    TRY(dmse.alloc((size_t)std::max<size_t>(train.size(), 1) * 8)); TRY(dinfo.alloc(16));
+    std::vector<long long> cur(train);               // alive training stars (global ids) in training order
+    std::vector<long long> lidx, lpos;               // this shard's members: local index, position in `cur`
+    std::vector<double> err, lerr;
+    std::vector<int64_t> bad;
+    if (p->iterations == 0) {                        // ones(r, c, K), shopt.jl:492
+        std::vector<double> ones((size_t)K * rc, 1.0);
+        SHOPT_CUDA_TRY(cudaMemcpyAsync(io->poly, ones.data(), ones.size() * 8, cudaMemcpyHostToDevice, st));
+        SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    for (int loop = 1; loop <= p->iterations; loop++) {
+        const long long nc = (long long)cur.size();
+        if (io->n_per_round) io->n_per_round[loop - 1] = nc;
+        lidx.clear(); lpos.clear();
+        for (long long t = 0; t < nc; t++)
+            if (cur[(size_t)t] >= off && cur[(size_t)t] < off + n) { lidx.push_back(cur[(size_t)t] - off); lpos.push_back(t); }
+        const long long nl = (long long)lidx.size();
+        SHOPT_CUDA_TRY(cudaMemcpyAsync(didx.p, lidx.data(), (size_t)nl * 8, cudaMemcpyHostToDevice, st));
+        if (nc < 5) {                                // interpolate.jl:142-145
+            if (comm) return SHOPT_E_UNSUPPORTED;    // fewer than 5 training stars across a sharded run
+            TRY(small_median_launch(io->pgf, rc, didx.as<long long>(), (int)nl, p->degree, io->poly, st));
+        } else {
+            TRY(polyfit_normal_launch(io->pgf, rc, io->u, io->v, didx.as<long long>(), nl, p->degree, dacc.as<double>(),
+                                      (double *)ctx->scratch, ctx->scratch_bytes, st));
+            if (comm && comm(dacc.p, acc_len, 0, stream, comm_user) != 0) {
+                set_last_error_text("all-reduce callback failed"); return SHOPT_E_CUDA;
+            }
+            TRY(polyfit_solve_launch(dacc.as<double>(), rc, p->degree, io->poly, dinfo.as<int>(), st));
+        }
+        TRY(polyfit_mse_launch(io->pgf, rc, io->u, io->v, didx.as<long long>(), nl, p->degree, io->poly, dmse.as<double>(),
+                               (double *)ctx->scratch, ctx->scratch_bytes, st));
+        lerr.resize((size_t)nl);
+        SHOPT_CUDA_TRY(cudaMemcpyAsync(lerr.data(), dmse.p, (size_t)nl * 8, cudaMemcpyDeviceToHost, st));
+        SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+        err.assign((size_t)nc, 0.0);
+        for (long long i = 0; i < nl; i++) err[(size_t)lpos[(size_t)i]] = lerr[(size_t)i];
+        if (comm && nc > 0) {                        // zero-padded gather of the per-star errors
+            SHOPT_CUDA_TRY(cudaMemcpyAsync(dmse.p, err.data(), (size_t)nc * 8, cudaMemcpyHostToDevice, st));
+            if (comm(dmse.p, nc, 0, stream, comm_user) != 0) { set_last_error_text("all-reduce callback failed"); return SHOPT_E_CUDA; }
+            SHOPT_CUDA_TRY(cudaMemcpyAsync(err.data(), dmse.p, (size_t)nc * 8, cudaMemcpyDeviceToHost, st));
+            SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+        }
+        if (loop < p->iterations) {                  // shopt.jl:557-575; the last round's selection is not applied
+            bad.resize((size_t)std::max<long long>(nc, 1));
+            const int64_t nbad = shopt_worst_10_percent(err.data(), nc, p->sigma_clip, bad.data());
+            std::vector<char> isbad((size_t)nc, 0);
+            for (int64_t b = 0; b < nbad; b++) isbad[(size_t)bad[(size_t)b]] = 1;
+            size_t mkeep = 0;
+            for (long long t = 0; t < nc; t++) {
+                const long long g = cur[(size_t)t];
+                if (isbad[(size_t)t]) { if (g >= off && g < off + n) flags[(size_t)(g - off)] |= SHOPT_FLAG_REJECTED; }
+                else cur[mkeep++] = g;
+            }
+            cur.resize(mkeep);
+        }
+    }
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(io->flags, flags.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+    io->counts[0] = n_black; io->counts[1] = n_failed; io->counts[2] = (int64_t)train.size(); io->counts[3] = (int64_t)cur.size();
+    return SHOPT_OK;
+}
+
+int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) {
+    if (!p || !io || !io->stamps || !io->u || !io->v || !io->x0_model || !io->x0_learned || !io->model || !io->learned ||
+        !io->flags || !io->poly)
+        return SHOPT_E_BADARG;
+    if (io->r < 1 || io->c < 2 || io->n_local < 0 || io->n_global != io->n_local || io->offset != 0) return SHOPT_E_BADARG;
+    Ctx *ctx; TRY(get_ctx(&ctx));
+    const size_t n = (size_t)io->n_local, rc = (size_t)io->r * io->c, nn = std::max<size_t>(n, 1);
+    const size_t K = (size_t)(p->degree + 1) * (p->degree + 2) / 2;
+    DevBuf dst, dpgf, dsm, dout, dint, dpoly;
+    TRY(dst.alloc(nn * rc * 8)); TRY(dpgf.alloc(nn * rc * 8)); TRY(dsm.alloc(nn * 8 * 8)); TRY(dout.alloc(nn * 6 * 8));
+    TRY(dint.alloc(nn * 8)); TRY(dpoly.alloc(K * rc * 8));
+    cudaStream_t st = ctx->stream;
+    double *small = dsm.as<double>();                // u | v | x0_model (3n) | x0_learned (3n)
+    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[0], st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(dst.p, io->stamps, n * rc * 8, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(small, io->u, n * 8, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + n, io->v, n * 8, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + 2 * n, io->x0_model, n * 24, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + 5 * n, io->x0_learned, n * 24, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[1], st));
+    shopt_stage_io d = *io;
+    d.stamps = dst.as<double>(); d.u = small; d.v = small + n; d.x0_model = small + 2 * n; d.x0_learned = small + 5 * n;
+    d.model = dout.as<double>(); d.learned = dout.as<double>() + 3 * n; d.pgf = dpgf.as<double>();
+    d.flags = dint.as<int32_t>(); d.pca_k = io->pca_k ? dint.as<int32_t>() + n : nullptr; d.poly = dpoly.as<double>();
+    TRY(shopt_stage_run_dev(p, &d, nullptr, nullptr, st));
+    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[2], st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(io->model, d.model, n * 24, cudaMemcpyDeviceToHost, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(io->learned, d.learned, n * 24, cudaMemcpyDeviceToHost, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(io->flags, d.flags, n * 4, cudaMemcpyDeviceToHost, st));
+    if (io->pca_k) SHOPT_CUDA_TRY(cudaMemcpyAsync(io->pca_k, d.pca_k, n * 4, cudaMemcpyDeviceToHost, st));
+    if (io->pgf) SHOPT_CUDA_TRY(cudaMemcpyAsync(io->pgf, d.pgf, n * rc * 8, cudaMemcpyDeviceToHost, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(io->poly, d.poly, K * rc * 8, cudaMemcpyDeviceToHost, st));
+    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[3], st));
+    for (int i = 0; i < 4; i++) io->counts[i] = d.counts[i];
+    return finish_timing(ctx);
+}
+
+}  // extern "C"

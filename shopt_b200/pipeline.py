@@ -1,0 +1,116 @@
+"""The whole per-star fitting stage as one call: the host-side mirror of shopt/shopt.jl's loops :130-184 (model fit +
+s-blacklist), :281-314 (PCA pixel-grid fit), :357-417 (learned fit + failed list), :472-577 (training split + polyfit
+rounds with worst-10 % rejection), on top of libshopt_b200.so's shopt_stage_run / shopt_stage_run_dev.
+
+Multi-GPU: one process per GPU, each owning a contiguous shard of the catalogue.  Stars are independent up to the
+polyfit, whose only exchange is a sum-all-reduce of the normal-equation partials [V'V | V'P] (plus two zero-padded
+gathers: survivor flags, per-star errors).  The library takes the all-reduce as a callback; here it is
+torch.distributed (NCCL over NVLink on GPUs; gloo in the CPU tests of the sharding logic).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check
+
+
+def default_params(**over):
+    """shopt.yml keys on the hot path with the README's documented defaults (README.md:300-330)."""
+    p = _lib.Params()
+    _lib.lib().shopt_default_params(C.byref(p))
+    for k, v in over.items():
+        if not hasattr(p, k):
+            raise KeyError(k)
+        setattr(p, k, v)
+    return p
+
+
+def shard_bounds(n_global, world_size, rank):
+    """Contiguous shards of ceil(N/G) stars (the last ones may be shorter or empty)."""
+    per = -(-n_global // world_size)
+    a = min(n_global, rank * per)
+    return a, min(n_global, a + per)
+
+
+def num_terms(degree):
+    return (degree + 1) * (degree + 2) // 2
+
+
+class _DevView:
+    """Exposes a raw device pointer to torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr, count, dtype):
+        self.__cuda_array_interface__ = dict(shape=(count,), typestr="<f8" if dtype == 0 else "<i4",
+                                             data=(ptr, False), version=2)
+
+
+def make_allreduce(group=None):
+    """ctypes callback: in-place sum-all-reduce of a device buffer over `group` with torch.distributed."""
+    import torch
+    import torch.distributed as dist
+
+    def _cb(ptr, count, dtype, stream, user):
+        try:
+            t = torch.as_tensor(_DevView(ptr, count, dtype), device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+            return 0
+        except Exception as e:      # never let an exception cross the C boundary
+            print("shopt_b200 all-reduce failed:", e)
+            return 1
+    return _lib.ALLREDUCE_FN(_cb)
+
+
+def run_stage_dev(params, stamps, u, v, x0_model, x0_learned, perm, n_global=None, offset=0, group=None, pgf=None):
+    """Device-resident shard (torch CUDA tensors, float64): stamps (n, c, r), u, v (n), x0_* (n, 3);
+    perm: global permutation (host, int64).  `group`/torch.distributed initialised -> sharded run.
+    Returns dict of torch tensors (model/learned (3, n), pgf, flags, pca_k, poly (K, c, r)) + host counts."""
+    import torch
+    import torch.distributed as dist
+    n, c, r = stamps.shape
+    dev = stamps.device
+    n_global = n if n_global is None else n_global
+    perm = np.ascontiguousarray(perm, dtype=np.int64)
+    assert len(perm) == n_global
+    f64 = torch.float64
+    K = num_terms(params.degree)
+    out = dict(model=torch.empty(3, n, dtype=f64, device=dev), learned=torch.empty(3, n, dtype=f64, device=dev),
+               pgf=pgf if pgf is not None else torch.empty(n, c, r, dtype=f64, device=dev),
+               flags=torch.empty(n, dtype=torch.int32, device=dev), pca_k=torch.empty(n, dtype=torch.int32, device=dev),
+               poly=torch.empty(K, c, r, dtype=f64, device=dev))
+    npr = np.zeros(max(params.iterations, 1), np.int64)
+    for t in (stamps, u, v, x0_model, x0_learned):
+        assert t.is_cuda and t.is_contiguous() and t.dtype == f64
+    io = _lib.StageIO(stamps=stamps.data_ptr(), r=r, c=c, n_local=n, u=u.data_ptr(), v=v.data_ptr(),
+                      x0_model=x0_model.data_ptr(), x0_learned=x0_learned.data_ptr(), n_global=n_global, offset=offset,
+                      perm=perm.ctypes.data, model=out["model"].data_ptr(), learned=out["learned"].data_ptr(),
+                      pgf=out["pgf"].data_ptr(), flags=out["flags"].data_ptr(), pca_k=out["pca_k"].data_ptr(),
+                      poly=out["poly"].data_ptr(), n_per_round=npr.ctypes.data)
+    sharded = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    cb = make_allreduce(group) if sharded else None
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    check(_lib.lib().shopt_stage_run_dev(C.byref(params), C.byref(io), C.cast(cb, C.c_void_p) if cb else None, None, stream))
+    out["n_per_round"] = npr[:params.iterations].copy()
+    out["counts"] = dict(zip(("blacklisted", "failed", "training", "kept"), list(io.counts)))
+    return out
+
+
+def run_stage(params, stamps, u, v, x0_model, x0_learned, perm, want_pgf=True):
+    """Host arrays, one GPU (H2D, stage, D2H inside the call): stamps (N, c, r), u, v (N), x0_* (N, 3), perm (N)."""
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    stamps, u, v, x0_model, x0_learned = f(stamps), f(u), f(v), f(x0_model), f(x0_learned)
+    perm = np.ascontiguousarray(perm, dtype=np.int64)
+    N, c, r = stamps.shape
+    K = num_terms(params.degree)
+    out = dict(model=np.zeros((3, N)), learned=np.zeros((3, N)), pgf=np.zeros((N, c, r)) if want_pgf else None,
+               flags=np.zeros(N, np.int32), pca_k=np.zeros(N, np.int32), poly=np.zeros((K, c, r)))
+    npr = np.zeros(max(params.iterations, 1), np.int64)
+    io = _lib.StageIO(stamps=stamps.ctypes.data, r=r, c=c, n_local=N, u=u.ctypes.data, v=v.ctypes.data,
+                      x0_model=x0_model.ctypes.data, x0_learned=x0_learned.ctypes.data, n_global=N, offset=0,
+                      perm=perm.ctypes.data, model=out["model"].ctypes.data, learned=out["learned"].ctypes.data,
+                      pgf=out["pgf"].ctypes.data if want_pgf else None, flags=out["flags"].ctypes.data,
+                      pca_k=out["pca_k"].ctypes.data, poly=out["poly"].ctypes.data, n_per_round=npr.ctypes.data)
+    check(_lib.lib().shopt_stage_run(C.byref(params), C.byref(io)))
+    out["n_per_round"] = npr[:params.iterations].copy()
+    out["counts"] = dict(zip(("blacklisted", "failed", "training", "kept"), list(io.counts)))
+    return out

@@ -1,0 +1,79 @@
+"""GPU parity: the whole stage (model fit -> blacklist -> PCA -> learned fit -> failed list -> split -> polyfit rounds)
+through shopt_stage_run / shopt_stage_run_dev against the composed CPU oracle.
+Tolerances (north_star): s, g1, g2 and polynomial coefficients within 1e-6 relative; flags / selection bit-exact."""
+import numpy as np
+import pytest
+
+from shopt_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def fits_agree(a, b, tol=1e-6):
+    """Per-star agreement of two (3, n) fit results [s; g1; g2]: s within tol relative, the ellipticity compared as a
+    2-vector (|dg_i| <= tol |g|: a component that vanishes by symmetry, e.g. g2 of a rank-1 pixel-grid fit, has no
+    relative precision of its own).  Non-finite entries must coincide."""
+    fin = np.isfinite(a) == np.isfinite(b)
+    with np.errstate(invalid="ignore"):
+        gn = np.hypot(b[1], b[2])
+        ok = (np.abs(a[0] - b[0]) <= tol * np.abs(b[0])) & (np.abs(a[1] - b[1]) <= tol * gn) & (np.abs(a[2] - b[2]) <= tol * gn)
+    ok |= ~np.isfinite(b).all(axis=0)
+    return ok & fin.all(axis=0)
+
+
+def coef_close(a, b, rtol=1e-6):
+    scale = np.abs(b).max(axis=(1, 2), keepdims=True)
+    return np.max(np.abs(a - b) / scale) <= rtol
+
+
+def check_against_oracle(got, want, x0m, x0l, strict_poly=True):
+    assert np.array_equal(got["flags"], want["flags"])                      # blacklist / failed / training / rejected
+    assert got["counts"] == want["counts"]
+    assert got["n_per_round"].tolist() == want["n_per_round"].tolist()
+    assert np.array_equal(got["pca_k"], want["pca_k"])
+    # a few starts with sigma0 close to 1 are trajectory-chaotic (see test_gpu_analytic.py): bounded, not hidden
+    am = fits_agree(got["model"], want["model"])
+    assert am.mean() >= 0.97 and np.all(x0m[~am, 0] > 0.8)
+    ok = (want["flags"] & 2) == 0
+    al = fits_agree(got["learned"][:, ok], want["learned"][:, ok])
+    assert al.mean() >= 0.97 and np.all(x0l[ok][~al, 0] > 0.8)
+    if strict_poly:
+        assert coef_close(got["poly"], want["poly"])
+
+
+@pytest.mark.parametrize("N,r,n_a,degree,kw", [
+    (160, 41, 32, 1, {}),
+    (240, 33, 32, 3, dict(frac_bad_s=0.05, frac_contaminated=0.05)),
+    (120, 64, 48, 2, dict(frac_masked=0.01)),
+])
+def test_stage_host_entry_point(orc, N, r, n_a, degree, kw):
+    from oracle import stage_oracle
+    from shopt_b200 import pipeline
+    cat = synth.make_catalog(N, r, n_a, **kw)
+    a = {k: cat[k].numpy() for k in ("stamps", "u", "v", "x0_model", "x0_learned", "perm")}
+    a["stamps"][7, 2, 3] = np.inf                                          # one PCA failure
+    p = pipeline.default_params(n_a=n_a, degree=degree, iterations=3, training_ratio=0.8)
+    got = pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], a["perm"])
+    want = stage_oracle.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], a["perm"],
+                                  nthreads=orc.max_threads())
+    check_against_oracle(got, want, a["x0_model"], a["x0_learned"])
+    assert want["flags"][7] & 2
+    if kw.get("frac_bad_s"):
+        assert want["counts"]["blacklisted"] > 0
+    ok = (want["flags"] & 2) == 0
+    scale = np.abs(want["pgf"]).max(axis=(1, 2), keepdims=True)
+    assert np.max(np.abs(got["pgf"] - want["pgf"])[ok] / np.broadcast_to(scale, want["pgf"].shape)[ok]) < 1e-6
+
+
+def test_stage_device_entry_point_matches_host(orc):
+    import torch
+    from shopt_b200 import pipeline
+    cat = synth.make_catalog(200, 41, 32, frac_bad_s=0.03)
+    p = pipeline.default_params(n_a=32, degree=2, iterations=3, training_ratio=0.9)
+    host = pipeline.run_stage(p, *(cat[k].numpy() for k in ("stamps", "u", "v", "x0_model", "x0_learned", "perm")))
+    d = {k: cat[k].cuda() for k in ("stamps", "u", "v", "x0_model", "x0_learned")}
+    dev = pipeline.run_stage_dev(p, d["stamps"], d["u"], d["v"], d["x0_model"], d["x0_learned"], cat["perm"].numpy())
+    torch.cuda.synchronize()
+    for k in ("model", "learned", "flags", "pca_k", "poly", "pgf"):
+        assert np.array_equal(dev[k].cpu().numpy(), host[k], equal_nan=True), k    # same kernels, same bits
+    assert dev["counts"] == host["counts"]
