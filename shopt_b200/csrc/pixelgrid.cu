@@ -18,6 +18,8 @@
 // the output, pulled back into the (now free) shared buffer and smoothed from there.  Stamps too large for shared
 // memory (301 x 301) run the same code with W in a per-CTA global scratch block that stays L2-resident.
 // The stage is FP64-compute-bound (O(r c^2) flops per sweep on 8 r c bytes); see DESIGN.md for the roofline.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -36,6 +38,7 @@ struct PcaArgs {
     double *wglobal;      // non-null: per-CTA scratch of wstride doubles replaces the shared-memory W / Y buffers
     size_t wstride;
     int kmax;             // min(ncomp, r, c)
+    int fast;             // try the block subspace iteration first (0: always the full Jacobi SVD)
     double kern[15 * 15]; // normalised lanczos kernel (2a+1)^2, a <= 7, column-major like the reference's
 };
 
@@ -48,26 +51,330 @@ __device__ __forceinline__ double block_sum1(double v, double *scratch, int &buf
     return a[0];
 }
 
-// rows handled by one lane: i = lane + 32 t, t < RT
+// ---------------------------------------------------------------------------------------------
+// One-sided (Hestenes) Jacobi on the columns of A (nrows x ncols, leading dimension lda, shared or global memory):
+// on return the columns are mutually orthogonal (A <- A V).  B, when given, is co-rotated (B <- B V).  A sweep is a
+// round-robin tournament: npos-1 steps of npos/2 disjoint column pairs, one warp per pair.  Columns whose squared norm
+// is <= tiny are left alone.  Must be entered by every thread of the CTA with A (and B) visible; returns the
+// "still rotating" flag (non-zero when the sweep cap was hit).
+// ---------------------------------------------------------------------------------------------
+template <int NW, int RT>
+__device__ int jacobi_columns(double *A, int nrows, int ncols, int lda, double *B, int nrowsB, int ldb, double tiny,
+                              int max_sweeps, int &sweeps_out) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int npos = (ncols & 1) ? ncols + 1 : ncols;     // one dummy position when ncols is odd
+    const int nm1 = npos - 1, npairs = npos / 2;
+    int sweeps = 0, rotated = 1;
+    while (rotated && sweeps < max_sweeps) {
+        rotated = 0;
+        for (int step = 0; step < nm1; step++) {
+            for (int pr = warp; pr < npairs; pr += NW) {
+                int p, q;
+                if (pr == 0) { p = nm1; q = step; }
+                else { p = step + pr; if (p >= nm1) p -= nm1; q = step - pr; if (q < 0) q += nm1; }
+                if (p > q) { const int t = p; p = q; q = t; }
+                if (q >= ncols) continue;                   // the dummy position
+                double *cp = A + (size_t)p * lda, *cq = A + (size_t)q * lda;
+                double xa[RT], xb[RT];
+                double al = 0.0, be = 0.0, ga = 0.0;
+#pragma unroll
+                for (int t = 0; t < RT; t++) {
+                    const int i = lane + 32 * t;
+                    xa[t] = (i < nrows) ? cp[i] : 0.0;
+                    xb[t] = (i < nrows) ? cq[i] : 0.0;
+                    al = fma(xa[t], xa[t], al);
+                    be = fma(xb[t], xb[t], be);
+                    ga = fma(xa[t], xb[t], ga);
+                }
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) {
+                    al += __shfl_xor_sync(0xffffffffu, al, o);
+                    be += __shfl_xor_sync(0xffffffffu, be, o);
+                    ga += __shfl_xor_sync(0xffffffffu, ga, o);
+                }
+                if (al <= tiny || be <= tiny) continue;
+                if (fabs(ga) <= DBL_EPSILON * sqrt(al) * sqrt(be)) continue;
+                rotated = 1;
+                const double zeta = (be - al) / (2.0 * ga);
+                const double tt = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+#pragma unroll
+                for (int t = 0; t < RT; t++) {
+                    const int i = lane + 32 * t;
+                    if (i < nrows) {
+                        cp[i] = cs * xa[t] - sn * xb[t];
+                        cq[i] = sn * xa[t] + cs * xb[t];
+                    }
+                }
+                if (B) {
+                    double *bp = B + (size_t)p * ldb, *bq = B + (size_t)q * ldb;
+                    for (int i = lane; i < nrowsB; i += 32) {
+                        const double x = bp[i], y = bq[i];
+                        bp[i] = cs * x - sn * y;
+                        bq[i] = sn * x + cs * y;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        rotated = __syncthreads_or(rotated);
+        sweeps++;
+    }
+    sweeps_out = sweeps;
+    return rotated;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fast path: block subspace iteration for the few leading principal components.
+//
+// Star stamps are a handful of strong components over a noise floor, and pca_image keeps only the k components that
+// reach pratio of the variance (k = 1..3 for the benchmark catalogues), so diagonalising all c columns is wasted work.
+// The fast path iterates an FB = 8 column block  Q <- orth(Z Z' Q)  (two skinny products with Z in shared memory, a
+// Cholesky-QR applied twice), then Rayleigh-Ritz on the block (one-sided Jacobi on the 8 columns of T = Z'Q, Q
+// co-rotated) and ACCEPTS only when the answer is provably the one the full SVD gives:
+//   * the Ritz values theta_1..theta_8 reach pratio of |Z|_F^2 within k <= 6 components, no comparison of the
+//     cumulative variance against the threshold closer than 1e-11 relative;
+//   * everything outside the block sums to E = |Z|_F^2 - sum(theta) <= theta_k / 4, so no component that was missed can
+//     outrank the k kept ones (Ritz values are lower bounds of the eigenvalues they approximate);
+//   * the residuals |Z Z' u_a - theta_a u_a| <= 1e-13 theta_1 for a <= k.
+// Anything else (noise-dominated stamps, k > 6, slow convergence) falls through to the full Jacobi SVD below with Z
+// untouched.  Buffers are column-major: Q, Qn (r x 8, leading dimension ldq), T (c x 8, leading dimension c).
+// ---------------------------------------------------------------------------------------------
+constexpr int FB = 8;
+constexpr int FB_KMAX = 6;
+
+// T = Z' Q : lanes = (column jj = lane & 7, row-part = lane >> 3); eight columns of Z per warp
+template <int NW>
+__device__ __forceinline__ void mul_zt_q(const double *Z, int r, int c, const double *Q, int ldq, double *T) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, jj = lane & 7, part = lane >> 3;
+    for (int j0 = warp * 8; j0 < c; j0 += NW * 8) {
+        const int j = j0 + jj;
+        const bool live = j < c;
+        const double *zc = Z + (size_t)(live ? j : 0) * r;
+        double acc[FB];
+#pragma unroll
+        for (int b = 0; b < FB; b++) acc[b] = 0.0;
+        for (int i = part; i < r; i += 4) {
+            const double z = live ? zc[i] : 0.0;
+#pragma unroll
+            for (int b = 0; b < FB; b++) acc[b] = fma(z, Q[b * ldq + i], acc[b]);
+        }
+#pragma unroll
+        for (int b = 0; b < FB; b++) {
+            acc[b] += __shfl_xor_sync(0xffffffffu, acc[b], 8);
+            acc[b] += __shfl_xor_sync(0xffffffffu, acc[b], 16);
+        }
+        if (part == 0 && live) {
+#pragma unroll
+            for (int b = 0; b < FB; b++) T[b * c + j] = acc[b];
+        }
+    }
+}
+// Qn = Z T : lanes = (row ii = lane & 7, column-part = lane >> 3); eight rows of Z per warp
+template <int NW>
+__device__ __forceinline__ void mul_z_t(const double *Z, int r, int c, const double *T, double *Qn, int ldq) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, ii = lane & 7, part = lane >> 3;
+    for (int i0 = warp * 8; i0 < r; i0 += NW * 8) {
+        const int i = i0 + ii;
+        const bool live = i < r;
+        const double *zr = Z + (live ? i : 0);
+        double acc[FB];
+#pragma unroll
+        for (int b = 0; b < FB; b++) acc[b] = 0.0;
+        for (int j = part; j < c; j += 4) {
+            const double z = live ? zr[(size_t)j * r] : 0.0;
+#pragma unroll
+            for (int b = 0; b < FB; b++) acc[b] = fma(z, T[b * c + j], acc[b]);
+        }
+#pragma unroll
+        for (int b = 0; b < FB; b++) {
+            acc[b] += __shfl_xor_sync(0xffffffffu, acc[b], 8);
+            acc[b] += __shfl_xor_sync(0xffffffffu, acc[b], 16);
+        }
+        if (part == 0 && live) {
+#pragma unroll
+            for (int b = 0; b < FB; b++) Qn[b * ldq + i] = acc[b];
+        }
+    }
+}
+
+// Q <- Qn L^-T with Qn'Qn = L L' (Cholesky-QR); a column whose pivot collapses (numerically dependent) becomes zero.
+// G: 36 + 8 doubles of shared scratch.  In-place (Qdst == Qsrc) is allowed.  Ends with a __syncthreads.
+template <int NW>
+__device__ void cholqr(const double *Qsrc, double *Qdst, int r, int ldq, double *G) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int e = warp; e < FB * (FB + 1) / 2; e += NW) {       // lower triangle, e = i(i+1)/2 + j
+        int i = 0;
+        while ((i + 1) * (i + 2) / 2 <= e) i++;
+        const int j = e - i * (i + 1) / 2;
+        const double *ci = Qsrc + i * ldq, *cj = Qsrc + j * ldq;
+        double s = 0.0;
+        for (int t = lane; t < r; t += 32) s = fma(ci[t], cj[t], s);
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) G[e] = s;
+    }
+    __syncthreads();
+    if (warp == 0) {                                            // lane i owns row i of the factor
+        const int i = lane & 7;
+        double g[FB];
+#pragma unroll
+        for (int j = 0; j < FB; j++) g[j] = (j <= i) ? G[i * (i + 1) / 2 + j] : 0.0;
+        const double d0 = g[i >= 0 ? 0 : 0];
+        (void)d0;
+        double inv_mine = 0.0;
+#pragma unroll
+        for (int j = 0; j < FB; j++) {
+            const double orig = __shfl_sync(0xffffffffu, G[j * (j + 1) / 2 + j], 0);   // same value on every lane
+            const double d = __shfl_sync(0xffffffffu, g[j], j);
+            const bool dead = !(d > orig * 1e-22) || !(orig > 0.0);
+            const double inv = dead ? 0.0 : rsqrt(d);
+            const double lij = g[j] * inv;                       // L[i][j] for i >= j (sqrt(d) on the diagonal)
+#pragma unroll
+            for (int k = j + 1; k < FB; k++) {
+                const double lkj = __shfl_sync(0xffffffffu, lij, k);
+                g[k] = fma(-lij, lkj, g[k]);                     // meaningful for i >= k
+            }
+            g[j] = lij;
+            if (i == j) inv_mine = inv;
+        }
+        __syncwarp();
+        if (lane < FB) {
+#pragma unroll
+            for (int j = 0; j < FB; j++)
+                if (j <= i) G[i * (i + 1) / 2 + j] = g[j];
+            G[36 + i] = inv_mine;
+        }
+    }
+    __syncthreads();
+    if (tid < r) {
+        double y[FB];
+#pragma unroll
+        for (int j = 0; j < FB; j++) {
+            double s = Qsrc[j * ldq + tid];
+#pragma unroll
+            for (int a = 0; a < j; a++) s = fma(-G[j * (j + 1) / 2 + a], y[a], s);
+            y[j] = s * G[36 + j];
+        }
+#pragma unroll
+        for (int j = 0; j < FB; j++) Qdst[j * ldq + tid] = y[j];
+    }
+    __syncthreads();
+}
+
+// returns k >= 1 on acceptance (ford[0..k) = block columns of the kept components, Q = Ritz vectors, T = Z'Q), else 0
+template <int NW, int RT>
+__device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, double pratio, double *Q, double *Qn,
+                        double *T, int ldq, double *G, double *fth, int *ford, int *s_flag) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
+    const int j0 = c / 2 - FB / 2;
+    for (int e = tid; e < FB * r; e += nthr) {
+        const int b = e / r, i = e - b * r;
+        Qn[b * ldq + i] = Z[i + (size_t)(j0 + b) * r];
+    }
+    __syncthreads();
+    cholqr<NW>(Qn, Q, r, ldq, G);
+    cholqr<NW>(Q, Q, r, ldq, G);
+    for (int it = 1; it <= 12; it++) {
+        mul_zt_q<NW>(Z, r, c, Q, ldq, T);
+        __syncthreads();
+        const bool check = (it == 3 || it == 5 || it == 8 || it == 12);
+        if (check) {
+            // Rayleigh-Ritz: orthogonalise the columns of T = Z'Q, co-rotating Q (T'T = V Theta V')
+            int sw;
+            (void)jacobi_columns<NW, RT>(T, c, FB, c, Q, r, ldq, fro * 1e-300, 30, sw);
+            for (int b = warp; b < FB; b += NW) {
+                double s = 0.0;
+                for (int j = lane; j < c; j += 32) s = fma(T[b * c + j], T[b * c + j], s);
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+                if (lane == 0) fth[b] = s;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                for (int b = 0; b < FB; b++) {                  // stable descending rank
+                    int rank = 0;
+                    for (int i = 0; i < FB; i++) rank += (fth[i] > fth[b]) || (fth[i] == fth[b] && i < b);
+                    ford[rank] = b;
+                }
+                double sum8 = 0.0;
+                for (int b = 0; b < FB; b++) sum8 += fth[ford[b]];
+                double E = fro - sum8;
+                if (E < 0.0) E = 0.0;
+                const int m = r < c ? r : c;
+                const double den = (double)(c - 1), thres = (fro / den) * pratio;
+                int k = 1, ok = 1;
+                double acc = fth[ford[0]] / den;
+                for (;;) {                                       // choose_pcadim on the Ritz values
+                    if (!(k < m && k < ncomp)) break;
+                    if (fabs(acc - thres) <= 1e-11 * thres) { ok = 0; break; }
+                    if (!(acc < thres)) break;
+                    if (k >= FB_KMAX) { ok = 0; break; }
+                    acc += fth[ford[k]] / den;
+                    k++;
+                }
+                const double thk = fth[ford[k - 1]];
+                if (!(thk > 0.0) || !(E <= 0.25 * thk) || !isfinite(fro)) ok = 0;
+                *s_flag = ok ? k : 0;
+            }
+            __syncthreads();
+            const int k = *s_flag;
+            if (k == 0) return 0;
+            mul_z_t<NW>(Z, r, c, T, Qn, ldq);
+            __syncthreads();
+            for (int a = warp; a < k; a += NW) {                 // residual |Z Z'u - theta u|^2
+                const int b = ford[a];
+                const double th = fth[b];
+                double s = 0.0;
+                for (int i = lane; i < r; i += 32) {
+                    const double d = Qn[b * ldq + i] - th * Q[b * ldq + i];
+                    s = fma(d, d, s);
+                }
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+                if (lane == 0) G[48 + a] = s;
+            }
+            __syncthreads();
+            const double tol = 1e-13 * fro;
+            bool conv = true;
+            for (int a = 0; a < k; a++) conv = conv && (G[48 + a] <= tol * tol);
+            if (conv) return k;
+            __syncthreads();
+        } else {
+            mul_z_t<NW>(Z, r, c, T, Qn, ldq);
+            __syncthreads();
+        }
+        cholqr<NW>(Qn, Q, r, ldq, G);
+        cholqr<NW>(Q, Q, r, ldq, G);
+    }
+    return 0;
+}
+
+// rows handled by one lane in the Jacobi kernels: i = lane + 32 t, t < RT  (32 RT >= max(r, c))
 template <int NW, int RT>
 __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int r = a.r, c = a.c;
     const long long rc = (long long)r * c;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
-    // shared layout: [ misc 64 B | scratch 2*NW doubles | mu r | sv c | ord c ints | (W rc | Y kmax*c) unless global ]
+    const int kmaxp = (a.kmax + 1) & ~1, ldq = (r + 1) & ~1;
+    // shared layout: [ misc 64 B | scratch 2*NW | mu r | sv c | fth 8 | ord c' ints | uoff, yoff kmax' ints | ford 8 ints |
+    //                  (W rc | region) unless global ];  region = Y (kmax x c)  overlaid with  Q, Qn (8 x ldq), T (8 x c), G 64
     long long *s_next = reinterpret_cast<long long *>(smem_raw);
     int *s_flag = reinterpret_cast<int *>(smem_raw + 16);
     double *scratch = reinterpret_cast<double *>(smem_raw + 64);
     double *mu = scratch + 2 * NW;
     double *sv = mu + r;
-    int *ord = reinterpret_cast<int *>(sv + c);
-    double *tail = reinterpret_cast<double *>(ord + ((c + 1) & ~1));
+    double *fth = sv + c;
+    int *ord = reinterpret_cast<int *>(fth + FB);
+    int *uoff = ord + ((c + 1) & ~1);
+    int *yoff = uoff + kmaxp;
+    int *ford = yoff + kmaxp;
+    double *tail = reinterpret_cast<double *>(ford + FB);
     double *W = a.wglobal ? a.wglobal + (size_t)blockIdx.x * a.wstride : tail;
     double *Y = W + rc;
+    double *FQ = Y, *FQn = FQ + FB * ldq, *FT = FQn + FB * ldq, *FG = FT + FB * c;
     int buf = 0;
-    const int npos = (c & 1) ? c + 1 : c;     // tournament positions (one dummy when c is odd)
-    const int nm1 = npos - 1, npairs = npos / 2;
 
     for (;;) {
         __syncthreads();
@@ -104,124 +411,82 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
             W[p] = z;
             fro = fma(z, z, fro);
         }
-        // columns whose squared norm falls below eps^2 |Z|_F^2 are numerically zero (always c - r + 1 of them when
-        // c > r): rotating them only shuffles round-off, so they are left alone and do not hold up convergence
-        const double tiny = block_sum1<NW>(fro, scratch, buf) * (DBL_EPSILON * DBL_EPSILON);
+        fro = block_sum1<NW>(fro, scratch, buf);                // |Z|_F^2; the block sum also publishes W
 
-        // ---- one-sided Jacobi sweeps ----
-        int sweeps = 0, rotated = 1;
-        while (rotated && sweeps < 60) {
-            rotated = 0;
-            for (int step = 0; step < nm1; step++) {
-                for (int pr = warp; pr < npairs; pr += NW) {
-                    int p, q;
-                    if (pr == 0) { p = nm1; q = step; }
-                    else { p = step + pr; if (p >= nm1) p -= nm1; q = step - pr; if (q < 0) q += nm1; }
-                    if (p > q) { const int t = p; p = q; q = t; }
-                    if (q >= c) continue;                       // the dummy position
-                    double *cp = W + (size_t)p * r, *cq = W + (size_t)q * r;
-                    double xa[RT], xb[RT];
-                    double al = 0.0, be = 0.0, ga = 0.0;
-#pragma unroll
-                    for (int t = 0; t < RT; t++) {
-                        const int i = lane + 32 * t;
-                        xa[t] = (i < r) ? cp[i] : 0.0;
-                        xb[t] = (i < r) ? cq[i] : 0.0;
-                        al = fma(xa[t], xa[t], al);
-                        be = fma(xb[t], xb[t], be);
-                        ga = fma(xa[t], xb[t], ga);
-                    }
-#pragma unroll
-                    for (int o = 16; o >= 1; o >>= 1) {
-                        al += __shfl_xor_sync(0xffffffffu, al, o);
-                        be += __shfl_xor_sync(0xffffffffu, be, o);
-                        ga += __shfl_xor_sync(0xffffffffu, ga, o);
-                    }
-                    if (al <= tiny || be <= tiny) continue;
-                    if (fabs(ga) <= DBL_EPSILON * sqrt(al) * sqrt(be)) continue;
-                    rotated = 1;
-                    const double zeta = (be - al) / (2.0 * ga);
-                    const double tt = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-                    const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
-#pragma unroll
-                    for (int t = 0; t < RT; t++) {
-                        const int i = lane + 32 * t;
-                        if (i < r) {
-                            cp[i] = cs * xa[t] - sn * xb[t];
-                            cq[i] = sn * xa[t] + cs * xb[t];
-                        }
-                    }
-                }
-                __syncthreads();
+        // ---- fast path: block subspace iteration with a-posteriori acceptance ----
+        int k = 0, status = SHOPT_PCA_OK;
+        if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
+            k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag);
+        if (k > 0) {
+            if (tid < k) {
+                uoff[tid] = (int)(FQ - W) + ford[tid] * ldq;
+                yoff[tid] = (int)(FT - W) + ford[tid] * c;
             }
-            rotated = __syncthreads_or(rotated);
-            sweeps++;
-        }
-
-        // ---- principal variances, stable descending rank, choose k (choose_pcadim) ----
-        for (int j = tid; j < c; j += nthr) {
-            double s = 0.0;
-            const double *w = W + (size_t)j * r;
-            for (int i = 0; i < r; i++) s = fma(w[i], w[i], s);
-            sv[j] = s;
-        }
-        __syncthreads();
-        for (int j = tid; j < c; j += nthr) {
-            const double x = sv[j];
-            int rank = 0;
-            for (int i = 0; i < c; i++) rank += (sv[i] > x) || (sv[i] == x && i < j);
-            ord[rank] = j;
-        }
-        __syncthreads();
-        if (tid == 0) {
-            const int m = r < c ? r : c;
-            const double den = (double)(c - 1);
-            double vsum = 0.0;
-            for (int j = 0; j < m; j++) vsum += sv[ord[j]] / den;
-            int k = 1;
-            double acc = sv[ord[0]] / den;
-            const double thres = vsum * a.pratio;
-            while (k < m && k < a.ncomp && acc < thres) { acc += sv[ord[k]] / den; k++; }
-            *s_flag = k;
-        }
-        __syncthreads();
-        const int k = *s_flag;
-        // ---- normalise the k leading columns: u_a = w_a / sigma_a ----
-        for (int e = tid; e < k * r; e += nthr) {
-            const int aa = e / r, i = e - aa * r;
-            const int col = ord[aa];
-            const double nrm = sqrt(sv[col]);
-            if (nrm > 0.0) W[i + (size_t)col * r] /= nrm;
-        }
-        __syncthreads();
-        // ---- Y = U_k' Z, Z re-read from the stamp (transform) ----
-        for (int j = warp; j < c; j += NW) {
-            double z[RT];
-#pragma unroll
-            for (int t = 0; t < RT; t++) {
-                const int i = lane + 32 * t;
-                z[t] = (i < r) ? nan_to_zero(__ldg(X + i + (size_t)j * r)) - mu[i] : 0.0;
-            }
-            for (int aa = 0; aa < k; aa++) {
-                const double *ua = W + (size_t)ord[aa] * r;
+            __syncthreads();
+        } else {
+            // ---- full SVD: one-sided Jacobi on all c columns; the columns become sigma_j u_j ----
+            // columns whose squared norm falls below eps^2 |Z|_F^2 are numerically zero (always c - r + 1 of them when
+            // c > r): rotating them only shuffles round-off, so they are left alone and do not hold up convergence
+            int sweeps;
+            const int rotating = jacobi_columns<NW, RT>(W, r, c, r, nullptr, 0, 0, fro * (DBL_EPSILON * DBL_EPSILON), 60, sweeps);
+            if (rotating && sweeps >= 60) status = SHOPT_PCA_NOCONV;
+            // principal variances, stable descending rank, choose k (choose_pcadim)
+            for (int j = tid; j < c; j += nthr) {
                 double s = 0.0;
-#pragma unroll
-                for (int t = 0; t < RT; t++) {
-                    const int i = lane + 32 * t;
-                    if (i < r) s = fma(ua[i], z[t], s);
-                }
-#pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-                if (lane == 0) Y[aa + (size_t)j * k] = s;
+                const double *w = W + (size_t)j * r;
+                for (int i = 0; i < r; i++) s = fma(w[i], w[i], s);
+                sv[j] = s;
             }
+            __syncthreads();
+            for (int j = tid; j < c; j += nthr) {
+                const double x = sv[j];
+                int rank = 0;
+                for (int i = 0; i < c; i++) rank += (sv[i] > x) || (sv[i] == x && i < j);
+                ord[rank] = j;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                const int m = r < c ? r : c;
+                const double den = (double)(c - 1);
+                double vsum = 0.0;
+                for (int j = 0; j < m; j++) vsum += sv[ord[j]] / den;
+                int kk = 1;
+                double acc = sv[ord[0]] / den;
+                const double thres = vsum * a.pratio;
+                while (kk < m && kk < a.ncomp && acc < thres) { acc += sv[ord[kk]] / den; kk++; }
+                *s_flag = kk;
+            }
+            __syncthreads();
+            k = *s_flag;
+            // normalise the k leading columns: u_a = w_a / sigma_a
+            for (int e = tid; e < k * r; e += nthr) {
+                const int aa = e / r, i = e - aa * r;
+                const int col = ord[aa];
+                const double nrm = sqrt(sv[col]);
+                if (nrm > 0.0) W[i + (size_t)col * r] /= nrm;
+            }
+            if (tid < k) { uoff[tid] = ord[tid] * r; yoff[tid] = (int)rc + tid * c; }
+            __syncthreads();
+            // Y = U_k' Z, Z re-read from the stamp (transform)
+            for (int j = warp; j < c; j += NW) {
+                for (int aa = 0; aa < k; aa++) {
+                    const double *ua = W + uoff[aa];
+                    double s = 0.0;
+                    for (int i = lane; i < r; i += 32)
+                        s = fma(ua[i], nan_to_zero(__ldg(X + i + (size_t)j * r)) - mu[i], s);
+#pragma unroll
+                    for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+                    if (lane == 0) Y[(size_t)aa * c + j] = s;
+                }
+            }
+            __syncthreads();
         }
-        __syncthreads();
         // ---- reconstruct: out = U_k Y + mean ----
         double part = 0.0;
         for (long long p = tid; p < rc; p += nthr) {
             const int j = (int)(p / r), i = (int)(p - (long long)j * r);
             double s = 0.0;
-            for (int aa = 0; aa < k; aa++) s = fma(W[i + (size_t)ord[aa] * r], Y[aa + (size_t)j * k], s);
+            for (int aa = 0; aa < k; aa++) s = fma(W[uoff[aa] + i], W[yoff[aa] + j], s);
             s += mu[i];
             out[p] = s;
             part += s;
@@ -254,7 +519,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         }
         if (tid == 0) {
             if (a.k_out) a.k_out[star] = k;
-            if (a.status) a.status[star] = (rotated && sweeps >= 60) ? SHOPT_PCA_NOCONV : SHOPT_PCA_OK;
+            if (a.status) a.status[star] = status;
         }
     }
 }
@@ -309,24 +574,29 @@ static void lanczos_kernel2d(int a, double *kernel) {
 }
 
 // ---- launch -----------------------------------------------------------------------------------
-static size_t pca_fixed_smem(int nw, int r, int c) {
-    return 64 + (size_t)2 * nw * 8 + (size_t)r * 8 + (size_t)c * 8 + (size_t)((c + 1) & ~1) * 4;
+static size_t pca_fixed_smem(int nw, int r, int c, int kmax) {
+    return 64 + (size_t)2 * nw * 8 + (size_t)r * 8 + (size_t)c * 8 + FB * 8 + (size_t)((c + 1) & ~1) * 4 +
+           (size_t)2 * ((kmax + 1) & ~1) * 4 + FB * 4;
+}
+static size_t pca_w_doubles(int r, int c, int kmax) {      // W plus the region shared by Y and the fast-path buffers
+    const size_t y = (size_t)kmax * c, f = (size_t)2 * FB * ((r + 1) & ~1) + (size_t)FB * c + 64;
+    return (size_t)r * c + (y > f ? y : f);
 }
 size_t pca_scratch_bytes(int r, int c, int ncomp) {
     int kmax = ncomp < r ? ncomp : r; if (c < kmax) kmax = c; if (kmax < 1) kmax = 1;
-    const size_t wdoubles = (size_t)r * c + (size_t)kmax * c;
-    if (pca_fixed_smem(32, r, c) + wdoubles * 8 <= 227 * 1024) return 0;
+    const size_t wdoubles = pca_w_doubles(r, c, kmax);
+    if (pca_fixed_smem(32, r, c, kmax) + wdoubles * 8 <= 227 * 1024) return 0;
     return (size_t)sm_count() * wdoubles * 8;
 }
 
 template <int NW, int RT>
 static int pca_launch_t(PcaArgs a, double *scratch, size_t scratch_bytes, cudaStream_t st) {
-    const size_t wdoubles = (size_t)a.r * a.c + (size_t)a.kmax * a.c;
-    size_t smem = pca_fixed_smem(NW, a.r, a.c) + wdoubles * 8;
+    const size_t wdoubles = pca_w_doubles(a.r, a.c, a.kmax);
+    size_t smem = pca_fixed_smem(NW, a.r, a.c, a.kmax) + wdoubles * 8;
     long long grid = sm_count();
     a.wglobal = nullptr; a.wstride = wdoubles;
     if (smem > 227 * 1024) {
-        smem = pca_fixed_smem(NW, a.r, a.c);
+        smem = pca_fixed_smem(NW, a.r, a.c, a.kmax);
         if ((size_t)grid * wdoubles * 8 > scratch_bytes) return SHOPT_E_NOMEM;
         a.wglobal = scratch;
     }
@@ -354,14 +624,15 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
                size_t scratch_bytes, cudaStream_t st) {
     if (!d_stamps || !d_pgf || !d_counter || r < 1 || c < 2 || N < 0 || ncomp < 1 || lanczos_a > 7) return SHOPT_E_BADARG;
     if (N == 0) return SHOPT_OK;
-    if (r > 320) return SHOPT_E_UNSUPPORTED;
+    if (r > 320 || c > 320) return SHOPT_E_UNSUPPORTED;
     PcaArgs a;
     a.stamps = d_stamps; a.r = r; a.c = c; a.N = N; a.ncomp = ncomp; a.pratio = pratio;
     a.lanczos_a = lanczos_a; a.unity_sum = unity_sum; a.pgf = d_pgf; a.k_out = d_k; a.status = d_status;
     a.counter = d_counter; a.wglobal = nullptr; a.wstride = 0;
     a.kmax = ncomp < r ? ncomp : r; if (c < a.kmax) a.kmax = c;
+    a.fast = (getenv("SHOPT_PCA_NO_FAST") == nullptr);
     if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern);
-    const int rt = (r + 31) / 32;
+    const int rt = ((r > c ? r : c) + 31) / 32;
     switch (rt) {
         case 1: return pca_launch_nw<1>(a, scratch, scratch_bytes, st);
         case 2: return pca_launch_nw<2>(a, scratch, scratch_bytes, st);

@@ -11,6 +11,17 @@ from shopt_b200 import synth
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=["fast", "jacobi"], autouse=True)
+def pca_path(request, monkeypatch):
+    """Every case runs twice: with the block-subspace fast path enabled (it falls back to the full Jacobi SVD whenever
+    its acceptance test fails) and with the Jacobi SVD forced for every star."""
+    if request.param == "jacobi":
+        monkeypatch.setenv("SHOPT_PCA_NO_FAST", "1")
+    else:
+        monkeypatch.delenv("SHOPT_PCA_NO_FAST", raising=False)
+    return request.param
+
+
 def close(a, b, tol=1e-6):
     scale = np.abs(b).max(axis=(1, 2), keepdims=True)
     scale[scale == 0] = 1.0
