@@ -206,6 +206,12 @@ typedef struct shopt_stage_io {
     int64_t counts[4];           /* HOST: blacklisted, failed, training stars, kept after the last applied rejection */
 } shopt_stage_io;
 
+/* Host logic of the split, exposed for sharded hosts and tests (shopt.jl:472-478): flags (n_global) = SHOPT_FLAG_* of
+ * every star after the gather; train_out receives the first round(training_ratio * n_survivors) (half to even, like
+ * Julia's round(Int, .)) survivors (flags & 7 == 0) in `perm` order; returns their count, or a negative SHOPT_E_*. */
+int64_t shopt_training_split(const int32_t *flags, int64_t n_global, const int64_t *perm, double training_ratio,
+                             int64_t *train_out);
+
 /* device-resident shard; comm == NULL runs a single GPU.  Blocks until the stage is done (the outlier selection
  * between rounds runs on the host). */
 int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream);

@@ -79,6 +79,7 @@ SIGNATURES = {
     "shopt_psf_at_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int, dp, dp, C.c_int64, dp]),
     "shopt_psf_at_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int64, vp, vp]),
     "shopt_default_params": (None, [C.POINTER(Params)]),
+    "shopt_training_split": (C.c_int64, [ip, C.c_int64, lp, C.c_double, lp]),
     "shopt_stage_run_dev": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO), C.c_void_p, C.c_void_p, C.c_void_p]),
     "shopt_stage_run": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO)]),
 }

@@ -30,6 +30,21 @@ using namespace shopt;
 
 extern "C" {
 
+int64_t shopt_training_split(const int32_t *flags, int64_t n_global, const int64_t *perm, double training_ratio,
+                             int64_t *train_out) {
+    if (n_global < 0 || (n_global > 0 && (!flags || !perm || !train_out))) return SHOPT_E_BADARG;
+    int64_t n_surv = 0;
+    for (int64_t g = 0; g < n_global; g++) n_surv += ((flags[g] & 7) == 0);
+    const int64_t n_train = (int64_t)std::nearbyint(training_ratio * (double)n_surv);   // round half to even
+    int64_t m = 0;
+    for (int64_t i = 0; i < n_global && m < n_train; i++) {
+        const int64_t g = perm[i];
+        if (g < 0 || g >= n_global) return SHOPT_E_BADARG;
+        if ((flags[g] & 7) == 0) train_out[m++] = g;
+    }
+    return m;
+}
+
 int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream) {
     if (!p || !io || !io->stamps || !io->u || !io->v || !io->x0_model || !io->x0_learned || !io->model || !io->learned ||
         !io->pgf || !io->flags || !io->poly)
@@ -82,21 +97,18 @@ int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allredu
         else n_surv++;
     }
     // ---- training split: first round(training_ratio * n_surv) survivors in perm order (shopt.jl:472-478) ----
-    const long long n_train = (long long)std::nearbyint(p->training_ratio * (double)n_surv);   // round half to even
-    std::vector<long long> train;                    // global star ids, training order
-    train.reserve((size_t)std::max<long long>(n_train, 0));
-    for (long long i = 0; i < NG && (long long)train.size() < n_train; i++) {
-        const long long g = io->perm[i];
-        if (g < 0 || g >= NG) return SHOPT_E_BADARG;
-        if ((gflag[(size_t)g] & 31) == 0) train.push_back(g);
-    }
-    for (long long g : train) if (g >= off && g < off + n) flags[(size_t)(g - off)] |= SHOPT_FLAG_TRAINING;
+    for (auto &f : gflag) f &= 31;
+    std::vector<int64_t> train((size_t)std::max<long long>(n_surv, 1));   // global star ids, training order
+    const int64_t n_train = shopt_training_split(gflag.data(), NG, io->perm, p->training_ratio, train.data());
+    if (n_train < 0) return (int)n_train;
+    train.resize((size_t)n_train);
+    for (int64_t g : train) if (g >= off && g < off + n) flags[(size_t)(g - off)] |= SHOPT_FLAG_TRAINING;
 
     // ---- polyfit rounds (shopt.jl:534-577) ----
     const long long acc_len = (long long)K * K + (long long)K * rc;
     TRY(dacc.alloc((size_t)acc_len * 8)); TRY(didx.alloc((size_t)std::max<long long>(n, 1) * 8));
     TRY(dmse.alloc((size_t)std::max<size_t>(train.size(), 1) * 8)); TRY(dinfo.alloc(16));
-    std::vector<long long> cur(train);               // alive training stars (global ids) in training order
+    std::vector<long long> cur(train.begin(), train.end());   // alive training stars (global ids) in training order
     std::vector<long long> lidx, lpos;               // this shard's members: local index, position in `cur`
     std::vector<double> err, lerr;
     std::vector<int64_t> bad;

@@ -37,6 +37,18 @@ def num_terms(degree):
     return (degree + 1) * (degree + 2) // 2
 
 
+def training_split(flags, perm, training_ratio):
+    """shopt.jl:472-478 on the gathered per-star flags: global ids of the training stars, in `perm` order."""
+    flags = np.ascontiguousarray(flags, dtype=np.int32)
+    perm = np.ascontiguousarray(perm, dtype=np.int64)
+    out = np.zeros(max(len(flags), 1), np.int64)
+    n = _lib.lib().shopt_training_split(flags.ctypes.data_as(_lib.ip), len(flags), perm.ctypes.data_as(_lib.lp),
+                                        training_ratio, out.ctypes.data_as(_lib.lp))
+    if n < 0:
+        check(int(n))
+    return out[:n].copy()
+
+
 class _DevView:
     """Exposes a raw device pointer to torch through __cuda_array_interface__ (no copy)."""
 
