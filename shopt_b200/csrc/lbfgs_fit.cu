@@ -128,195 +128,154 @@ __device__ __forceinline__ void e_to_g(double e1, double e2, double &g1, double 
 
 // ---------------------------------------------------------------------------------------------
 // One CTA's view of the star being fitted.
+//
+// Thread layout: 2-D, thread (tu, tv) owns row u = tu of the crop and walks the columns v = tv, tv + TV, ... so that
+// du is a per-thread constant and dv advances by a constant -- no integer division or int->double conversion per
+// pixel.  With du fixed, the exponent  kappa q(du,dv) = c0 + dv (c1 + cc dv)  is two FMAs per pixel, and every sum
+// the value and gradient need is a MOMENT of the profile: q, w1 du, w1 dv + w2 du, w2 dv are all linear
+// combinations of du^2, du dv, dv^2, so the passes accumulate only
+//     pass A (all pixels):      sum f, sum f dv, sum f dv^2                 (x du^2, du applied once per thread)
+//     pass B (non-NaN pixels):  sum rho^2, sum rho f, sum rho f dv, sum rho f dv^2
+// and the scalar chain rule rebuilds the reference's sums from them.  The per-pixel profile value is parked in a
+// shared-memory plane between the passes (registers stay free; three CTAs fit an SM).
+// The dual-number scalar section (the manifold reparameterisation, ~10 IEEE divisions/square roots on 4-vectors)
+// is evaluated by warp 0 only and broadcast through shared memory.
 // ---------------------------------------------------------------------------------------------
-template <int THREADS, int PPT>
-struct StarEval {
-    static constexpr int NWARPS = THREADS / 32;
-    const double *crop;   // shared memory, column v at crop + v*pitch + off(v)
-    const unsigned char *coff;   // per-column misalignment offset (0/1), shared memory
-    int n_a, pitch, npix;
-    unsigned magic;       // ceil(2^32 / n_a)
-    double uc;            // n_a / 2 (analyticLBFGS.jl:28,41: the centre is (r/2, c/2) of the crop)
-    double *scratch;      // 2 * NWARPS * 6 doubles
-    int buf;
-    // NLSolversBase caches the last evaluated point by value
-    double xl[3], fl, gl[3];
-    bool have_last;
-    int nevals;
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts_f64(uint32_t addr, double v) {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
 
-    __device__ __forceinline__ void pix(int p, double &du, double &dv, double &d) const {
-        const unsigned v = __umulhi((unsigned)p, magic);
-        const unsigned u = (unsigned)p - v * (unsigned)n_a;
-        du = (double)(int)(u + 1) - uc;
-        dv = (double)(int)(v + 1) - uc;
-        d = crop[v * pitch + coff[v] + u];
-    }
+constexpr int SC_DOUBLES = 16;   // one broadcast block of the scalar section
+constexpr int LBFGS_M = 10;
 
-    // value_gradient!(d, x): the reference runs g! (ForwardDiff over cost) and then cost(x); the value
-    // channel of the dual pass is the same operation sequence, so one evaluation yields both.
-    __device__ __noinline__ void fg(const double xn[3], double &f, double g[3]) {
-        if (have_last && xn[0] == xl[0] && xn[1] == xl[1] && xn[2] == xl[2]) {
-            f = fl; g[0] = gl[0]; g[1] = gl[1]; g[2] = gl[2];
-            return;
-        }
-        // scalar section (every thread, identical bits)
-        Dual sig = d_seed(xn[0], 0), e1 = d_seed(xn[1], 1), e2 = d_seed(xn[2], 2);
-        Dual sg = d_sq(sig);
-        Dual g1, g2;
-        e_to_g_dual(e1, e2, g1, g2);
-        Dual a11 = d_radd(1.0, g1), a22 = d_rsub(1.0, g1);
-        Dual ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
-        const double A11 = a11.v, A22 = a22.v, G2 = g2.v, MS = ms.v;
-
-        // pass A: profile sums over ALL pixels (analyticLBFGS.jl:24-34)
-        double fc[PPT];
-        double S[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-        for (int k = 0; k < PPT; k++) {
-            const int p = threadIdx.x + k * THREADS;
-            fc[k] = 0.0;
-            if (p < npix) {
-                double du, dv, d;
-                pix(p, du, dv, d);
-                const double w1 = A11 * du + G2 * dv;
-                const double w2 = G2 * du + A22 * dv;
-                const double q = w1 * w1 + w2 * w2;
-                const double fv = exp(-(MS * q));
-                fc[k] = fv;
-                S[0] += fv;
-                S[1] += fv * q;
-                S[2] += fv * (w1 * du);
-                S[3] += fv * (w1 * dv + w2 * du);
-                S[4] += fv * (w2 * dv);
-            }
-        }
-        cta_sum<5, NWARPS>(S, scratch, buf);
-        const double A = 1.0 / S[0];
-        // pass B: residual sums over non-NaN pixels (analyticLBFGS.jl:36-44)
-        double T[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-        for (int k = 0; k < PPT; k++) {
-            const int p = threadIdx.x + k * THREADS;
-            if (p < npix) {
-                double du, dv, d;
-                pix(p, du, dv, d);
-                if (!isnan(d)) {
-                    const double w1 = A11 * du + G2 * dv;
-                    const double w2 = G2 * du + A22 * dv;
-                    const double q = w1 * w1 + w2 * w2;
-                    const double fv = fc[k];
-                    const double rho = A * fv - d;
-                    const double rf = rho * fv;
-                    T[0] += 0.5 * (rho * rho);
-                    T[1] += rf;
-                    T[2] += rf * q;
-                    T[3] += rf * (w1 * du);
-                    T[4] += rf * (w1 * dv + w2 * du);
-                    T[5] += rf * (w2 * dv);
-                }
-            }
-        }
-        cta_sum<6, NWARPS>(T, scratch, buf);
-        // chain rule: sum.d_j = -(ms.d_j S1 + 2 ms (a11.d_j S2 + g2.d_j S3 + a22.d_j S4))
-        f = T[0];
-#pragma unroll
-        for (int j = 0; j < 3; j++) {
-            const double dS = -(ms.d[j] * S[1] + 2.0 * MS * (a11.d[j] * S[2] + g2.d[j] * S[3] + a22.d[j] * S[4]));
-            const double dA = -(A / S[0]) * dS;
-            const double dT = -(ms.d[j] * T[2] + 2.0 * MS * (a11.d[j] * T[3] + g2.d[j] * T[4] + a22.d[j] * T[5]));
-            g[j] = dA * T[1] + A * dT;
-        }
-        nevals++;
-        xl[0] = xn[0]; xl[1] = xn[1]; xl[2] = xn[2];
-        fl = f; gl[0] = g[0]; gl[1] = g[1]; gl[2] = g[2];
-        have_last = true;
-    }
+// Per-CTA state in shared memory (offset 0 of the dynamic shared memory).  Everything the scalar optimiser code keeps
+// between evaluations lives here or in registers: the 126 KB of L1 left beside three CTAs' crops cannot hold
+// per-thread stacks, and local-memory traffic was what bounded the first version of this kernel (profiles/).
+struct EvalShared {
+    double sc[2][SC_DOUBLES];          // double-buffered broadcast of the dual-number scalar section
+    double xl[3], fl, gl[3];           // NLSolversBase caches the last evaluated point by value
+    double hist_dx[LBFGS_M][3], hist_dg[LBFGS_M][3], hist_rho[LBFGS_M], hist_alpha[LBFGS_M];
+    uint32_t crop_s, fbuf_s;           // shared-space byte addresses: staged crop, profile plane (same indexing)
+    int n_a, pitch, TV, m0, rodd, plane, have_last, scb, buf;
 };
+struct FG {
+    double f, g0, g1, g2;
+};
+extern __shared__ __align__(16) unsigned char smem_raw[];
+__device__ __forceinline__ EvalShared &eval_shared() { return *reinterpret_cast<EvalShared *>(smem_raw); }
+constexpr int ES_BYTES = (sizeof(EvalShared) + 15) & ~15;
 
-// variant without the register cache of exp() (any crop size): pass B recomputes the profile
+// value_gradient!(d, x): the reference runs g! (ForwardDiff over cost) and then cost(x); the value channel of the dual
+// pass is the same operation sequence, so one evaluation yields both.  Arguments and result travel in registers.
 template <int THREADS>
-struct StarEvalGeneric {
-    static constexpr int NWARPS = THREADS / 32;
-    const double *crop;
-    const unsigned char *coff;
-    int n_a, pitch, npix;
-    unsigned magic;
-    double uc;
-    double *scratch;
-    int buf;
-    double xl[3], fl, gl[3];
-    bool have_last;
-    int nevals;
-
-    __device__ __forceinline__ void pix(int p, double &du, double &dv, double &d) const {
-        const unsigned v = __umulhi((unsigned)p, magic);
-        const unsigned u = (unsigned)p - v * (unsigned)n_a;
-        du = (double)(int)(u + 1) - uc;
-        dv = (double)(int)(v + 1) - uc;
-        d = crop[(size_t)v * pitch + coff[v] + u];
+__device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
+    constexpr int NWARPS = THREADS / 32;
+    EvalShared &es = eval_shared();
+    FG out;
+    if (es.have_last && x0 == es.xl[0] && x1 == es.xl[1] && x2 == es.xl[2]) {
+        out.f = es.fl; out.g0 = es.gl[0]; out.g1 = es.gl[1]; out.g2 = es.gl[2];
+        return out;
     }
-    __device__ __noinline__ void fg(const double xn[3], double &f, double g[3]) {
-        if (have_last && xn[0] == xl[0] && xn[1] == xl[1] && xn[2] == xl[2]) {
-            f = fl; g[0] = gl[0]; g[1] = gl[1]; g[2] = gl[2];
-            return;
-        }
-        Dual sig = d_seed(xn[0], 0), e1 = d_seed(xn[1], 1), e2 = d_seed(xn[2], 2);
+    double *scratch = reinterpret_cast<double *>(smem_raw + ES_BYTES);
+    const int scb = es.scb;
+    int buf = es.buf;
+    double *s = es.sc[scb];
+    if (threadIdx.x < 32) {   // scalar section, warp 0
+        Dual sig = d_seed(x0, 0), e1 = d_seed(x1, 1), e2 = d_seed(x2, 2);
         Dual sg = d_sq(sig);
         Dual g1, g2;
         e_to_g_dual(e1, e2, g1, g2);
         Dual a11 = d_radd(1.0, g1), a22 = d_rsub(1.0, g1);
         Dual ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
-        const double A11 = a11.v, A22 = a22.v, G2 = g2.v, MS = ms.v;
-        double S[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-        for (int p = threadIdx.x; p < npix; p += THREADS) {
-            double du, dv, d;
-            pix(p, du, dv, d);
-            const double w1 = A11 * du + G2 * dv;
-            const double w2 = G2 * du + A22 * dv;
-            const double q = w1 * w1 + w2 * w2;
-            const double fv = exp(-(MS * q));
-            S[0] += fv;
-            S[1] += fv * q;
-            S[2] += fv * (w1 * du);
-            S[3] += fv * (w1 * dv + w2 * du);
-            S[4] += fv * (w2 * dv);
-        }
-        cta_sum<5, NWARPS>(S, scratch, buf);
-        const double A = 1.0 / S[0];
-        double T[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-        for (int p = threadIdx.x; p < npix; p += THREADS) {
-            double du, dv, d;
-            pix(p, du, dv, d);
-            if (!isnan(d)) {
-                const double w1 = A11 * du + G2 * dv;
-                const double w2 = G2 * du + A22 * dv;
-                const double q = w1 * w1 + w2 * w2;
-                const double fv = exp(-(MS * q));
-                const double rho = A * fv - d;
-                const double rf = rho * fv;
-                T[0] += 0.5 * (rho * rho);
-                T[1] += rf;
-                T[2] += rf * q;
-                T[3] += rf * (w1 * du);
-                T[4] += rf * (w1 * dv + w2 * du);
-                T[5] += rf * (w2 * dv);
-            }
-        }
-        cta_sum<6, NWARPS>(T, scratch, buf);
-        f = T[0];
+        if (threadIdx.x == 0) {
+            s[0] = a11.v; s[1] = a22.v; s[2] = g2.v; s[3] = ms.v;
 #pragma unroll
-        for (int j = 0; j < 3; j++) {
-            const double dS = -(ms.d[j] * S[1] + 2.0 * MS * (a11.d[j] * S[2] + g2.d[j] * S[3] + a22.d[j] * S[4]));
-            const double dA = -(A / S[0]) * dS;
-            const double dT = -(ms.d[j] * T[2] + 2.0 * MS * (a11.d[j] * T[3] + g2.d[j] * T[4] + a22.d[j] * T[5]));
-            g[j] = dA * T[1] + A * dT;
+            for (int j = 0; j < 3; j++) { s[4 + j] = a11.d[j]; s[7 + j] = a22.d[j]; s[10 + j] = g2.d[j]; s[13 + j] = ms.d[j]; }
         }
-        nevals++;
-        xl[0] = xn[0]; xl[1] = xn[1]; xl[2] = xn[2];
-        fl = f; gl[0] = g[0]; gl[1] = g[1]; gl[2] = g[2];
-        have_last = true;
     }
-};
+    const int n_a = es.n_a, pitch = es.pitch, TV = es.TV, m0 = es.m0, rodd = es.rodd;
+    const bool plane = es.plane != 0;
+    const uint32_t crop_s = es.crop_s, fbuf_s = es.fbuf_s;
+    const int tv = threadIdx.x / n_a, tu = threadIdx.x - tv * n_a;
+    const bool active = tv < TV;
+    const double du = (double)(tu + 1) - n_a / 2.0;    // analyticLBFGS.jl:28,41: the centre is (r/2, c/2) of the crop
+    const double dv0 = (double)(tv + 1) - n_a / 2.0;
+    __syncthreads();
+    const double A11 = s[0], A22 = s[1], G2 = s[2], MS = s[3];
+    // q = qa du^2 + qb du dv + qc dv^2
+    const double qa = A11 * A11 + G2 * G2, qb = 2.0 * (G2 * (A11 + A22)), qc = G2 * G2 + A22 * A22;
+    const double c0 = (MS * qa) * (du * du), c1 = (MS * qb) * du, cc = MS * qc;
+    const double step = (double)TV;
+    // pass A: profile moments over ALL pixels (analyticLBFGS.jl:24-34)
+    double S0 = 0.0, S1 = 0.0, S2 = 0.0;
+    if (active) {
+        double dv = dv0;
+        for (int v = tv; v < n_a; v += TV) {
+            const double arg = fma(dv, fma(cc, dv, c1), c0);
+            const double fv = exp(-arg);
+            if (plane) sts_f64(fbuf_s + (uint32_t)((v * pitch + ((m0 + v * rodd) & 1) + tu) * 8), fv);
+            const double fd = fv * dv;
+            S0 += fv;
+            S1 += fd;
+            S2 = fma(fd, dv, S2);
+            dv += step;
+        }
+    }
+    double M[4] = {S0, (du * du) * S0, du * S1, S2};   // sum f, sum f du^2, sum f du dv, sum f dv^2
+    cta_sum<4, NWARPS>(M, scratch, buf);
+    const double A = 1.0 / M[0];
+    // pass B: residual moments over non-NaN pixels (analyticLBFGS.jl:36-44)
+    double R0 = 0.0, R1 = 0.0, R2 = 0.0, R3 = 0.0;
+    if (active) {
+        double dv = dv0;
+        for (int v = tv; v < n_a; v += TV) {
+            const uint32_t o = (uint32_t)((v * pitch + ((m0 + v * rodd) & 1) + tu) * 8);
+            const double d = lds_f64(crop_s + o);
+            if (!isnan(d)) {
+                const double fv = plane ? lds_f64(fbuf_s + o) : exp(-fma(dv, fma(cc, dv, c1), c0));
+                const double rho = fma(A, fv, -d);
+                const double t = rho * fv, td = t * dv;
+                R0 = fma(rho, rho, R0);
+                R1 += t;
+                R2 += td;
+                R3 = fma(td, dv, R3);
+            }
+            dv += step;
+        }
+    }
+    double T[5] = {0.5 * R0, R1, (du * du) * R1, du * R2, R3};   // cost, sum rho f, its du^2, du dv, dv^2 moments
+    cta_sum<5, NWARPS>(T, scratch, buf);
+    // rebuild the reference's sums from the moments, then the chain rule:
+    //   sum.d_j = -(ms.d_j Sq + 2 ms (a11.d_j S2 + g2.d_j S3 + a22.d_j S4))
+    const double Sq = qa * M[1] + qb * M[2] + qc * M[3];
+    const double Sw1u = A11 * M[1] + G2 * M[2];
+    const double Sx = (A11 + A22) * M[2] + G2 * (M[1] + M[3]);
+    const double Sw2v = G2 * M[2] + A22 * M[3];
+    const double Tq = qa * T[2] + qb * T[3] + qc * T[4];
+    const double Tw1u = A11 * T[2] + G2 * T[3];
+    const double Tx = (A11 + A22) * T[3] + G2 * (T[2] + T[4]);
+    const double Tw2v = G2 * T[3] + A22 * T[4];
+    double g[3];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        const double a11d = s[4 + j], a22d = s[7 + j], g2d = s[10 + j], msd = s[13 + j];
+        const double dS = -(msd * Sq + 2.0 * MS * (a11d * Sw1u + g2d * Sx + a22d * Sw2v));
+        const double dA = -(A / M[0]) * dS;
+        const double dT = -(msd * Tq + 2.0 * MS * (a11d * Tw1u + g2d * Tx + a22d * Tw2v));
+        g[j] = dA * T[1] + A * dT;
+    }
+    out.f = T[0]; out.g0 = g[0]; out.g1 = g[1]; out.g2 = g[2];
+    // every thread stores the same bits; the barriers above order these writes against the other threads' reads
+    es.xl[0] = x0; es.xl[1] = x1; es.xl[2] = x2;
+    es.fl = out.f; es.gl[0] = g[0]; es.gl[1] = g[1]; es.gl[2] = g[2];
+    es.have_last = 1; es.scb = scb ^ 1; es.buf = buf;
+    return out;
+}
 
 // ---------------------------------------------------------------------------------------------
 // HagerZhang line search (LineSearches 7.2.0 defaults), value form: trial points are
@@ -340,23 +299,20 @@ __device__ __forceinline__ double eps_of(double b) {   // Julia eps(x::Float64)
 }
 __device__ __forceinline__ double nextfloat_(double x) { return nextafter(x, (double)INFINITY); }
 
-template <class Eval>
+template <int THREADS>
 struct LineSearch {
-    Eval &E;
     double x[3], s[3];
     double phi_0, dphi_0, phi_lim;
     int npts;
     bool err;
     int ntrials;
 
-    __device__ LineSearch(Eval &e) : E(e), npts(0), err(false), ntrials(0) {}
+    __device__ LineSearch() : npts(0), err(false), ntrials(0) {}
 
     __device__ __forceinline__ void phidphi(double alpha, double &phi, double &dphi) {
-        double xn[3], g[3];
-#pragma unroll
-        for (int i = 0; i < 3; i++) xn[i] = add_(x[i], mul_(alpha, s[i]));
-        E.fg(xn, phi, g);
-        dphi = add_(add_(mul_(g[0], s[0]), mul_(g[1], s[1])), mul_(g[2], s[2]));
+        const FG r = eval_fg<THREADS>(add_(x[0], mul_(alpha, s[0])), add_(x[1], mul_(alpha, s[1])), add_(x[2], mul_(alpha, s[2])));
+        phi = r.f;
+        dphi = add_(add_(mul_(r.g0, s[0]), mul_(r.g1, s[1])), mul_(r.g2, s[2]));
         ntrials++;
     }
     __device__ __forceinline__ Pt push(double a, double v, double sl) {
@@ -534,20 +490,22 @@ __device__ __forceinline__ double dot3(const double a[3], const double b[3]) {
 }
 __device__ __forceinline__ double maxabs3(const double a[3]) { return fmax(fmax(fabs(a[0]), fabs(a[1])), fabs(a[2])); }
 
-template <class Eval>
-__device__ int lbfgs_fit(Eval &E, const double x0[3], double g_tol, int max_iter, double out_p[3], int &iters_out) {
-    constexpr int M = 10;
+template <int THREADS>
+__device__ int lbfgs_fit(const double x0[3], double g_tol, int max_iter, double out_p[3], int &iters_out) {
+    constexpr int M = LBFGS_M;
     double x[3] = {x0[0], x0[1], x0[2]}, x_prev[3], g[3], g_prev[3], s[3], dx[3], dg[3];
-    double dxh[M][3], dgh[M][3], rho[M], tl_alpha[M];
+    EvalShared &es = eval_shared();
+    double (*dxh)[3] = es.hist_dx, (*dgh)[3] = es.hist_dg;
+    double *rho = es.hist_rho, *tl_alpha = es.hist_alpha;
     double f, f_prev = nan("");
     int pseudo = 0, iteration = 0, counter_f_tol = 0, status;
-    E.fg(x, f, g);
+    { const FG r0 = eval_fg<THREADS>(x[0], x[1], x[2]); f = r0.f; g[0] = r0.g0; g[1] = r0.g1; g[2] = r0.g2; }
     const bool g_conv0 = maxabs3(g) <= g_tol;
     const bool stopped0 = !isfinite(f) || !isfinite(g[0]) || !isfinite(g[1]) || !isfinite(g[2]);
     bool converged = g_conv0 || stopped0;
     status = stopped0 ? SHOPT_FIT_NONFINITE : SHOPT_FIT_CONVERGED;
     bool broke = false;
-    LineSearch<Eval> LS(E);
+    LineSearch<THREADS> LS;
     while (!converged && iteration < max_iter) {
         iteration++;
         pseudo++;
@@ -599,7 +557,7 @@ __device__ int lbfgs_fit(Eval &E, const double x0[3], double g_tol, int max_iter
 #pragma unroll
         for (int k = 0; k < 3; k++) { dx[k] = mul_(alpha, s[k]); x[k] = add_(x[k], dx[k]); }
         if (hz == HZ_LSEXC) { status = SHOPT_FIT_LS_FAILED; broke = true; break; }
-        E.fg(x, f, g);
+        { const FG r1 = eval_fg<THREADS>(x[0], x[1], x[2]); f = r1.f; g[0] = r1.g0; g[1] = r1.g1; g[2] = r1.g2; }
         // assess_convergence with x_abstol = x_reltol = f_abstol = f_reltol = 0
         const double xchg = fmax(fmax(fabs(sub_(x[0], x_prev[0])), fabs(sub_(x[1], x_prev[1]))), fabs(sub_(x[2], x_prev[2])));
         const bool x_conv = xchg <= 0.0;
@@ -647,7 +605,7 @@ struct FitArgs {
     double *s, *g1, *g2;
     int *status, *iters;
     unsigned long long *counter;   // device work counter, zeroed before launch
-    int nbuf, pitch;
+    int nbuf, pitch, plane;
     double *f_out, *g_out;         // non-null: evaluate cost / gradient at x0 only (cost, g! of analyticLBFGS.jl)
 };
 
@@ -690,17 +648,19 @@ __device__ __forceinline__ void load_edges(const FitArgs &a, long long star, dou
     }
 }
 
-template <int THREADS, int PPT, int MINB>
+template <int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NWARPS = THREADS / 32;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);
-    long long *next_star = reinterpret_cast<long long *>(smem_raw + 16);   // 2 slots
-    double *scratch = reinterpret_cast<double *>(smem_raw + 32);
-    unsigned char *coff_base = smem_raw + 32 + 2 * NWARPS * 6 * sizeof(double);
+    // [ EvalShared | scratch 2*NWARPS*6 | mbarriers 2 x 8 B | next_star 2 x 8 B | coff nbuf*stride | crop nbuf | f plane ]
+    EvalShared &es = eval_shared();
+    double *scratch = reinterpret_cast<double *>(smem_raw + ES_BYTES);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(scratch + 2 * NWARPS * 6);
+    long long *next_star = reinterpret_cast<long long *>(bars + 2);        // 2 slots
+    unsigned char *coff_base = reinterpret_cast<unsigned char *>(next_star + 2);
     const int coff_stride = (a.n_a + 15) & ~15;
     double *crop_base = reinterpret_cast<double *>(coff_base + (size_t)a.nbuf * coff_stride);
     const size_t crop_stride = (size_t)a.n_a * a.pitch;
+    double *fplane = crop_base + (size_t)a.nbuf * crop_stride;
 
     if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
@@ -713,7 +673,8 @@ __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
     long long cur = next_star[0];
     int b = 0, slot = 0;
     uint32_t phase[2] = {0u, 0u};
-    using EvalT = typename std::conditional<(PPT > 0), StarEval<THREADS, (PPT > 0 ? PPT : 1)>, StarEvalGeneric<THREADS>>::type;
+    const int r0 = (a.r - a.n_a) / 2, c0 = (a.c - a.n_a) / 2;
+    const int mis0 = (int)(((uintptr_t)a.stamps >> 3) & 1);
     while (cur < a.N) {
         // grab the next star and (double-buffered) start its copies before fitting the current one
         if (threadIdx.x == 0) {
@@ -721,37 +682,35 @@ __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
             next_star[slot ^ 1] = nx;
             if (a.nbuf == 2 && nx < a.N)
                 stage_issue(a, nx, crop_base + (b ^ 1) * crop_stride, coff_base + (b ^ 1) * coff_stride, &bars[b ^ 1]);
+            const long long base = cur * (long long)a.r * a.c + r0 + (long long)c0 * a.r;
+            es.crop_s = smem_u32(crop_base + b * crop_stride); es.fbuf_s = smem_u32(fplane);
+            es.n_a = a.n_a; es.pitch = a.pitch; es.TV = THREADS / a.n_a;      // n_a <= THREADS (checked at launch)
+            es.m0 = (int)((base + mis0) & 1); es.rodd = a.r & 1; es.plane = a.plane;
+            es.have_last = 0; es.scb = 0; es.buf = 0;
         }
         double *crop = crop_base + b * crop_stride;
-        unsigned char *coff = coff_base + b * coff_stride;
         mbar_wait(&bars[b], phase[b]);
         phase[b] ^= 1u;
         load_edges(a, cur, crop);
-        __syncthreads();   // coff + edge columns + next_star visible
+        __syncthreads();   // edge columns, next_star and the evaluator state visible
 
-        EvalT E;
-        E.crop = crop; E.coff = coff; E.n_a = a.n_a; E.pitch = a.pitch; E.npix = a.n_a * a.n_a;
-        E.magic = (a.n_a > 1) ? (unsigned)((0x100000000ULL + a.n_a - 1) / (unsigned)a.n_a) : 0u;
-        E.uc = a.n_a / 2.0;
-        E.scratch = scratch; E.buf = 0; E.have_last = false; E.nevals = 0;
         const double x0[3] = {a.x0[3 * cur + 0], a.x0[3 * cur + 1], a.x0[3 * cur + 2]};
         double p[3];
         int iters = 0;
         if (a.f_out) {   // cost(x0), g!(G, x0) only
-            double f, g[3];
-            E.fg(x0, f, g);
+            const FG r = eval_fg<THREADS>(x0[0], x0[1], x0[2]);
             if (threadIdx.x == 0) {
-                a.f_out[cur] = f;
-                a.g_out[3 * cur + 0] = g[0]; a.g_out[3 * cur + 1] = g[1]; a.g_out[3 * cur + 2] = g[2];
+                a.f_out[cur] = r.f;
+                a.g_out[3 * cur + 0] = r.g0; a.g_out[3 * cur + 1] = r.g1; a.g_out[3 * cur + 2] = r.g2;
             }
         }
-        const int st = a.f_out ? 0 : lbfgs_fit(E, x0, a.g_tol, a.max_iter, p, iters);
+        const int st = a.f_out ? 0 : lbfgs_fit<THREADS>(x0, a.g_tol, a.max_iter, p, iters);
         if (threadIdx.x == 0 && !a.f_out) {
             a.s[cur] = p[0]; a.g1[cur] = p[1]; a.g2[cur] = p[2];
             if (a.status) a.status[cur] = st;
             if (a.iters) a.iters[cur] = iters;
         }
-        __syncthreads();   // everyone is done with crop[b] and scratch
+        __syncthreads();   // everyone is done with crop[b], scratch and the evaluator state
         const long long nx = next_star[slot ^ 1];
         slot ^= 1;
         if (a.nbuf == 2) {
@@ -767,31 +726,38 @@ __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
 }
 
 // ---- launch ---------------------------------------------------------------------------------
-static size_t fit_smem_bytes(int nwarps, int n_a, int pitch, int nbuf) {
+static size_t fit_smem_bytes(int nwarps, int n_a, int pitch, int nbuf, int plane) {
     const size_t coff_stride = (size_t)((n_a + 15) & ~15);
-    return 32 + (size_t)2 * nwarps * 6 * sizeof(double) + nbuf * coff_stride + (size_t)nbuf * n_a * pitch * sizeof(double);
+    return ES_BYTES + 32 + (size_t)(2 * nwarps * 6) * sizeof(double) + nbuf * coff_stride +
+           (size_t)(nbuf + plane) * n_a * pitch * sizeof(double);
 }
 
-template <int THREADS, int PPT, int MINB>
+template <int THREADS, int MINB>
 static int launch_fit(FitArgs a, cudaStream_t stream) {
     const int nw = THREADS / 32;
+    if (a.n_a > THREADS) return SHOPT_E_UNSUPPORTED;
     a.pitch = (a.n_a + 2 + 1) & ~1;
-    a.nbuf = 2;
-    size_t smem = fit_smem_bytes(nw, a.n_a, a.pitch, 2);
-    if (smem > 110 * 1024) {   // keep two CTAs per SM where possible, else single-buffer
-        a.nbuf = 1;
-        smem = fit_smem_bytes(nw, a.n_a, a.pitch, 1);
+    auto kern = fit_kernel<THREADS, MINB>;
+    // double-buffer the crop only when that does not cost a resident CTA (the prefetch hides ~1 us of a ~50 us fit)
+    // the profile plane is dropped (pass B recomputes exp) when crop + plane do not fit one SM
+    a.plane = fit_smem_bytes(nw, a.n_a, a.pitch, 1, 1) <= 227 * 1024 ? 1 : 0;
+    int best_nbuf = 0, best_per_sm = 0;
+    size_t best_smem = 0;
+    for (int nbuf = 2; nbuf >= 1; nbuf--) {
+        const size_t smem = fit_smem_bytes(nw, a.n_a, a.pitch, nbuf, a.plane);
+        if (smem > 227 * 1024) continue;
+        SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS, smem));
+        if (per_sm > best_per_sm) { best_per_sm = per_sm; best_nbuf = nbuf; best_smem = smem; }
     }
-    if (smem > 227 * 1024) return SHOPT_E_UNSUPPORTED;
-    auto kern = fit_kernel<THREADS, PPT, MINB>;
-    SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 0;
-    SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS, smem));
-    if (per_sm < 1) return SHOPT_E_UNSUPPORTED;
-    long long grid = (long long)sm_count() * per_sm;
+    if (best_per_sm < 1) return SHOPT_E_UNSUPPORTED;
+    a.nbuf = best_nbuf;
+    SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)best_smem));
+    long long grid = (long long)sm_count() * best_per_sm;
     if (grid > a.N) grid = a.N;
     SHOPT_CUDA_TRY(cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream));
-    kern<<<(unsigned)grid, THREADS, smem, stream>>>(a);
+    kern<<<(unsigned)grid, THREADS, best_smem, stream>>>(a);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
@@ -806,13 +772,12 @@ int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n
     FitArgs a;
     a.stamps = d_stamps; a.r = r; a.c = c; a.n_a = n_a; a.N = N; a.x0 = d_x0; a.g_tol = g_tol; a.max_iter = max_iter;
     a.s = d_s; a.g1 = d_g1; a.g2 = d_g2; a.status = d_status; a.iters = d_iters; a.counter = d_counter;
-    a.nbuf = 2; a.pitch = 0; a.f_out = d_f; a.g_out = d_g;
+    a.nbuf = 2; a.pitch = 0; a.plane = 1; a.f_out = d_f; a.g_out = d_g;
     const int npix = n_a * n_a;
-    if (npix <= 1024) return launch_fit<128, 8, 4>(a, stream);
-    if (npix <= 4096) return launch_fit<256, 16, 2>(a, stream);
-    if (npix <= 6144) return launch_fit<256, 24, 2>(a, stream);
-    if (npix <= 16384) return launch_fit<512, 32, 1>(a, stream);
-    if (n_a <= 160) return launch_fit<512, 0, 1>(a, stream);
+    (void)npix;
+    if (n_a <= 32) return launch_fit<128, 6>(a, stream);
+    if (n_a <= 80) return launch_fit<256, 3>(a, stream);
+    if (n_a <= 160) return launch_fit<512, 1>(a, stream);
     return SHOPT_E_UNSUPPORTED;
 }
 
