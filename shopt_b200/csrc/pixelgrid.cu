@@ -40,6 +40,7 @@ struct PcaArgs {
     int kmax;             // min(ncomp, r, c)
     int fast;             // try the block subspace iteration first (0: always the full Jacobi SVD)
     double kern[15 * 15]; // normalised lanczos kernel (2a+1)^2, a <= 7, column-major like the reference's
+    double kz[15];        // its 1-D factor: kern = kz (x) kz / sum
 };
 
 __device__ __forceinline__ double nan_to_zero(double x) { return isnan(x) ? 0.001 : x; }   // masks.jl:43
@@ -262,6 +263,104 @@ __device__ void cholqr(const double *Qsrc, double *Qdst, int r, int ldq, double 
     __syncthreads();
 }
 
+// Symmetric 8 x 8 eigenproblem  G = V diag(theta) V'  by cyclic two-sided Jacobi inside ONE warp (Rayleigh-Ritz of the
+// block).  Lane l owns row (l & 7) of the working matrix and of V (the four groups of eight lanes run the same
+// computation).  A sweep is the 7-step round-robin tournament on 8 indices, 4 disjoint pairs per step; every lane
+// computes the four rotations of a step (they are independent, so the divisions and square roots overlap) and all
+// register indices are compile-time constants.  Gt: lower triangle, e = i(i+1)/2 + j;  Vout[a * 8 + b] = V_ab.
+__device__ void eig8_warp(const double *Gt, double *Vout) {
+    const int lane = threadIdx.x & 31, i = lane & 7;
+    double a[FB], v[FB], dg;
+#pragma unroll
+    for (int j = 0; j < FB; j++) {
+        a[j] = (j <= i) ? Gt[i * (i + 1) / 2 + j] : Gt[j * (j + 1) / 2 + i];
+        v[j] = (i == j) ? 1.0 : 0.0;
+    }
+    dg = Gt[i * (i + 1) / 2 + i];
+    for (int sweep = 0; sweep < 16; sweep++) {
+        int rotated = 0;
+#pragma unroll
+        for (int s = 0; s < 7; s++) {
+            double cs[4], sn[4], dnew = dg;
+            bool amP = false;
+            double myc = 1.0, mys = 0.0;
+#pragma unroll
+            for (int m = 0; m < 4; m++) {
+                const int x = (m == 0) ? 7 : (s + m) % 7, y = (m == 0) ? s : (s - m + 7) % 7;
+                const int P = x < y ? x : y, Q = x < y ? y : x;
+                const double apq = __shfl_sync(0xffffffffu, a[Q], P, 8);
+                const double app = __shfl_sync(0xffffffffu, dg, P, 8);
+                const double aqq = __shfl_sync(0xffffffffu, dg, Q, 8);
+                double c = 1.0, sg = 0.0, t = 0.0;
+                if (fabs(apq) > DBL_EPSILON * sqrt(fabs(app * aqq)) && apq != 0.0) {
+                    const double zeta = (aqq - app) / (2.0 * apq);
+                    t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                    c = rsqrt(1.0 + t * t);
+                    sg = c * t;
+                    rotated = 1;
+                }
+                cs[m] = c; sn[m] = sg;
+                if (i == P) { amP = true; myc = c; mys = sg; dnew = app - t * apq; }
+                if (i == Q) { myc = c; mys = sg; dnew = aqq + t * apq; }
+                // columns P, Q of this lane's rows (A J and V J)
+                const double ap = a[P], aq = a[Q], vp = v[P], vq = v[Q];
+                a[P] = cs[m] * ap - sn[m] * aq; a[Q] = sn[m] * ap + cs[m] * aq;
+                v[P] = cs[m] * vp - sn[m] * vq; v[Q] = sn[m] * vp + cs[m] * vq;
+            }
+            // rows: J' (A J); the partner of index i in step s of the tournament
+            const int partner = (i == 7) ? s : ((i == s) ? 7 : (2 * s - i + 14) % 7);
+#pragma unroll
+            for (int j = 0; j < FB; j++) {
+                const double th = __shfl_sync(0xffffffffu, a[j], partner, 8);
+                a[j] = amP ? (myc * a[j] - mys * th) : (mys * th + myc * a[j]);
+            }
+            dg = dnew;
+        }
+        if (!rotated) break;
+    }
+    if (lane < FB) {
+#pragma unroll
+        for (int j = 0; j < FB; j++) Vout[i * FB + j] = v[j];
+    }
+}
+
+// Rayleigh-Ritz on the block: G = T'T (= Q' Z Z' Q), V from eig8_warp, then T <- T V and Q <- Q V.
+// FGm: 36 doubles Gram + 64 doubles V.  Ends with a __syncthreads.
+template <int NW>
+__device__ void rayleigh_ritz(double *T, int c, double *Q, int r, int ldq, double *FGm) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
+    double *Gt = FGm, *V = FGm + 36;
+    for (int e = warp; e < FB * (FB + 1) / 2; e += NW) {
+        int i = 0;
+        while ((i + 1) * (i + 2) / 2 <= e) i++;
+        const int j = e - i * (i + 1) / 2;
+        const double *ci = T + i * c, *cj = T + j * c;
+        double s = 0.0;
+        for (int t = lane; t < c; t += 32) s = fma(ci[t], cj[t], s);
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) Gt[e] = s;
+    }
+    __syncthreads();
+    if (warp == 0) eig8_warp(Gt, V);
+    __syncthreads();
+    for (int u = tid; u < r + c; u += nthr) {
+        double *base = (u < r) ? Q + u : T + (u - r);
+        const int ld = (u < r) ? ldq : c;
+        double x[FB], y[FB];
+#pragma unroll
+        for (int b = 0; b < FB; b++) { x[b] = base[b * ld]; y[b] = 0.0; }
+#pragma unroll
+        for (int aa = 0; aa < FB; aa++) {
+#pragma unroll
+            for (int b = 0; b < FB; b++) y[b] = fma(x[aa], V[aa * FB + b], y[b]);
+        }
+#pragma unroll
+        for (int b = 0; b < FB; b++) base[b * ld] = y[b];
+    }
+    __syncthreads();
+}
+
 // returns k >= 1 on acceptance (ford[0..k) = block columns of the kept components, Q = Ritz vectors, T = Z'Q), else 0
 template <int NW, int RT>
 __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, double pratio, double *Q, double *Qn,
@@ -280,9 +379,8 @@ __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, do
         __syncthreads();
         const bool check = (it == 3 || it == 5 || it == 8 || it == 12);
         if (check) {
-            // Rayleigh-Ritz: orthogonalise the columns of T = Z'Q, co-rotating Q (T'T = V Theta V')
-            int sw;
-            (void)jacobi_columns<NW, RT>(T, c, FB, c, Q, r, ldq, fro * 1e-300, 30, sw);
+            // Rayleigh-Ritz: T'T = V Theta V' (8 x 8, one warp), then T <- T V and Q <- Q V
+            rayleigh_ritz<NW>(T, c, Q, r, ldq, G + 64);
             for (int b = warp; b < FB; b += NW) {
                 double s = 0.0;
                 for (int j = lane; j < c; j += 32) s = fma(T[b * c + j], T[b * c + j], s);
@@ -350,6 +448,81 @@ __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, do
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// smooth(data, a) (dataPreprocessing.jl:112-139) for a NaN-free image R (r x c, shared or global) -> out (global).
+// The reference's kernel is the outer product kz (x) kz / S, so the renormalised correlation factorises:
+//     out(i,j) = sum_dj kz(dj) [ sum_di kz(di) R(i+di, j+dj) ] / (A_i B_j),   A_i, B_j = sums of the taps inside the image.
+// One thread owns row i of a column segment [j0, j1) and slides along j: the 2 LA + 1 vertical sums it needs live in a
+// register window that rotates by full unrolling (no moves, no local memory), so a pixel costs 2 LA + 1 shared loads
+// and 2 (2 LA + 1) FMAs instead of (2 LA + 1)^2 loads.  Lanes run along i: conflict-free shared reads, coalesced stores.
+// ---------------------------------------------------------------------------------------------
+template <int LA>
+__device__ __noinline__ void smooth_sep(const double *R, double *out, int r, int c, const double *kz, int nthr) {
+    constexpr int KW = 2 * LA + 1;
+    int nseg = nthr / r;
+    if (nseg < 1) nseg = 1;
+    if (nseg > c) nseg = c;
+    const int seglen = (c + nseg - 1) / nseg;
+    double wz[KW], s1 = 0.0;
+#pragma unroll
+    for (int t = 0; t < KW; t++) { wz[t] = kz[t]; s1 += wz[t]; }
+    const double inv_s1 = 1.0 / s1;
+    for (int unit = threadIdx.x; unit < r * nseg; unit += nthr) {
+        const int seg = unit / r, i = unit - seg * r;
+        const int j0 = seg * seglen, j1 = (j0 + seglen < c) ? j0 + seglen : c;
+        double wv[KW], Ai = 0.0;
+        int ro[KW];                                   // clamped row offsets (out-of-image rows carry weight 0)
+#pragma unroll
+        for (int t = 0; t < KW; t++) {
+            const int ii = i + t - LA;
+            const bool ok = ii >= 0 && ii < r;
+            wv[t] = ok ? wz[t] : 0.0;
+            ro[t] = ok ? ii : i;
+            Ai += wv[t];
+        }
+        const double inv_ai = 1.0 / Ai;
+        double h[KW];
+#pragma unroll
+        for (int t = 0; t < KW - 1; t++) {            // prime the window with columns j0 - LA .. j0 + LA - 1
+            const int jj = j0 - LA + t;
+            double vs = 0.0;
+            if (jj >= 0 && jj < c) {
+                const double *col = R + (size_t)jj * r;
+#pragma unroll
+                for (int d = 0; d < KW; d++) vs = fma(wv[d], col[ro[d]], vs);
+            }
+            h[t] = vs;
+        }
+        h[KW - 1] = 0.0;
+        for (int jb = j0; jb < j1; jb += KW) {
+#pragma unroll
+            for (int u = 0; u < KW; u++) {
+                const int j = jb + u;
+                if (j < j1) {
+                    const int jn = j + LA;
+                    double vs = 0.0;
+                    if (jn < c) {
+                        const double *col = R + (size_t)jn * r;
+#pragma unroll
+                        for (int d = 0; d < KW; d++) vs = fma(wv[d], col[ro[d]], vs);
+                    }
+                    h[(u + KW - 1) % KW] = vs;
+                    double acc = 0.0;
+#pragma unroll
+                    for (int t = 0; t < KW; t++) acc = fma(wz[t], h[(u + t) % KW], acc);
+                    double inv_b = inv_s1;
+                    if (j < LA || j >= c - LA) {
+                        double Bj = 0.0;
+#pragma unroll
+                        for (int t = 0; t < KW; t++) { const int jj = j + t - LA; if (jj >= 0 && jj < c) Bj += wz[t]; }
+                        inv_b = 1.0 / Bj;
+                    }
+                    out[i + (size_t)j * r] = acc * inv_ai * inv_b;
+                }
+            }
+        }
+    }
+}
 // rows handled by one lane in the Jacobi kernels: i = lane + 32 t, t < RT  (32 RT >= max(r, c))
 template <int NW, int RT>
 __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
@@ -376,12 +549,15 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
     double *FQ = Y, *FQn = FQ + FB * ldq, *FT = FQn + FB * ldq, *FG = FT + FB * c;
     int buf = 0;
 
+    if (tid == 0) *s_next = (long long)atomicAdd(a.counter, 1ULL);
     for (;;) {
-        __syncthreads();
-        if (tid == 0) *s_next = (long long)atomicAdd(a.counter, 1ULL);
         __syncthreads();
         const long long star = *s_next;
         if (star >= a.N) break;
+        __syncthreads();                                         // everyone has read s_next before it is replaced
+        // the next star's index is fetched now and published at the end of this one: the atomic's latency is hidden
+        long long nxt = 0;
+        if (tid == 0) nxt = (long long)atomicAdd(a.counter, 1ULL);
         const double *X = a.stamps + star * rc;
         double *out = a.pgf + star * rc;
 
@@ -395,7 +571,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         bad = __syncthreads_or(bad);
         if (bad) {
             for (long long p = tid; p < rc; p += nthr) out[p] = 0.0;
-            if (tid == 0) { if (a.k_out) a.k_out[star] = 0; if (a.status) a.status[star] = SHOPT_PCA_FAILED; }
+            if (tid == 0) { if (a.k_out) a.k_out[star] = 0; if (a.status) a.status[star] = SHOPT_PCA_FAILED; *s_next = nxt; }
             continue;
         }
         // ---- mean over the columns (sequential in j like mean(X, dims=2)), centre ----
@@ -417,7 +593,8 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         int k = 0, status = SHOPT_PCA_OK;
         if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
             k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag);
-        if (k > 0) {
+        const bool fastk = k > 0;
+        if (fastk) {
             if (tid < k) {
                 uoff[tid] = (int)(FQ - W) + ford[tid] * ldq;
                 yoff[tid] = (int)(FT - W) + ford[tid] * c;
@@ -481,45 +658,89 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
             }
             __syncthreads();
         }
-        // ---- reconstruct: out = U_k Y + mean ----
+        // ---- reconstruct: R = U_k Y + mean.  Thread = (row i, column segment); the fast path leaves U and Y outside W,
+        //      so R goes straight into W when it is smoothed next; the Jacobi path (U inside W) goes through `out` ----
+        const bool smoothing = !a.unity_sum && a.lanczos_a > 0;
+        double *Rdst = (fastk && smoothing) ? W : out;
+        int nseg = nthr / r;
+        if (nseg < 1) nseg = 1;
+        if (nseg > c) nseg = c;
+        const int seglen = (c + nseg - 1) / nseg;
         double part = 0.0;
-        for (long long p = tid; p < rc; p += nthr) {
-            const int j = (int)(p / r), i = (int)(p - (long long)j * r);
-            double s = 0.0;
-            for (int aa = 0; aa < k; aa++) s = fma(W[uoff[aa] + i], W[yoff[aa] + j], s);
-            s += mu[i];
-            out[p] = s;
-            part += s;
+        int nonfinite = 0;
+        for (int unit = tid; unit < r * nseg; unit += nthr) {
+            const int seg = unit / r, i = unit - seg * r;
+            const int j0 = seg * seglen, j1 = (j0 + seglen < c) ? j0 + seglen : c;
+            const double mui = mu[i];
+            if (k <= FB_KMAX) {
+                double ua[FB_KMAX];
+#pragma unroll
+                for (int aa = 0; aa < FB_KMAX; aa++) ua[aa] = (aa < k) ? W[uoff[aa] + i] : 0.0;
+                for (int j = j0; j < j1; j++) {
+                    double sacc = 0.0;
+#pragma unroll
+                    for (int aa = 0; aa < FB_KMAX; aa++)
+                        if (aa < k) sacc = fma(ua[aa], W[yoff[aa] + j], sacc);
+                    sacc += mui;
+                    if (!isfinite(sacc)) nonfinite = 1;
+                    Rdst[i + (size_t)j * r] = sacc;
+                    part += sacc;
+                }
+            } else {
+                for (int j = j0; j < j1; j++) {
+                    double sacc = 0.0;
+                    for (int aa = 0; aa < k; aa++) sacc = fma(W[uoff[aa] + i], W[yoff[aa] + j], sacc);
+                    sacc += mui;
+                    if (!isfinite(sacc)) nonfinite = 1;
+                    Rdst[i + (size_t)j * r] = sacc;
+                    part += sacc;
+                }
+            }
         }
         if (a.unity_sum) {                                   // shopt.jl:295: pca ./ sum(pca), no smoothing
             const double tot = block_sum1<NW>(part, scratch, buf);
-            for (long long p = tid; p < rc; p += nthr) out[p] = out[p] / tot;   // same thread wrote it
-        } else if (a.lanczos_a > 0) {                        // shopt.jl:299: smooth(pca, lanczos)
-            __syncthreads();
-            for (long long p = tid; p < rc; p += nthr) W[p] = out[p];            // same thread wrote it
-            __syncthreads();
-            const int la = a.lanczos_a, kw = 2 * la + 1;
-            for (long long p = tid; p < rc; p += nthr) {
-                const int j = (int)(p / r), i = (int)(p - (long long)j * r);
-                if (isnan(W[p])) continue;
-                const int dlo = i - la < 0 ? 0 : i - la, dhi = i + la > r - 1 ? r - 1 : i + la;
-                const int elo = j - la < 0 ? 0 : j - la, ehi = j + la > c - 1 ? c - 1 : j + la;
-                double norm = 0.0, val = 0.0;
-                for (int di = dlo; di <= dhi; di++)
-                    for (int dj = elo; dj <= ehi; dj++) {
-                        const double d = W[di + (size_t)dj * r];
-                        if (!isnan(d)) {
-                            const double kk = a.kern[(di - i + la) + (dj - j + la) * kw];
-                            val += kk * d;
-                            norm += kk;
+            for (int unit = tid; unit < r * nseg; unit += nthr) {        // same thread wrote these pixels
+                const int seg = unit / r, i = unit - seg * r;
+                const int j0 = seg * seglen, j1 = (j0 + seglen < c) ? j0 + seglen : c;
+                for (int j = j0; j < j1; j++) out[i + (size_t)j * r] = out[i + (size_t)j * r] / tot;
+            }
+        } else if (smoothing) {                              // shopt.jl:299: smooth(pca, lanczos)
+            nonfinite = __syncthreads_or(nonfinite);         // also publishes R
+            if (!fastk) {
+                for (int unit = tid; unit < r * nseg; unit += nthr) {    // same thread wrote these pixels
+                    const int seg = unit / r, i = unit - seg * r;
+                    const int j0 = seg * seglen, j1 = (j0 + seglen < c) ? j0 + seglen : c;
+                    for (int j = j0; j < j1; j++) W[i + (size_t)j * r] = out[i + (size_t)j * r];
+                }
+                __syncthreads();
+            }
+            if (!nonfinite && a.lanczos_a == 3) {            // the shipped default (shopt.yml lanczos: 3)
+                smooth_sep<3>(W, out, r, c, a.kz, nthr);
+            } else {                                         // NaN-aware renormalisation, tap by tap like the reference
+                const int la = a.lanczos_a, kw = 2 * la + 1;
+                for (long long p = tid; p < rc; p += nthr) {
+                    const int j = (int)(p / r), i = (int)(p - (long long)j * r);
+                    if (isnan(W[p])) { out[p] = W[p]; continue; }
+                    const int dlo = i - la < 0 ? 0 : i - la, dhi = i + la > r - 1 ? r - 1 : i + la;
+                    const int elo = j - la < 0 ? 0 : j - la, ehi = j + la > c - 1 ? c - 1 : j + la;
+                    double norm = 0.0, val = 0.0;
+                    for (int di = dlo; di <= dhi; di++)
+                        for (int dj = elo; dj <= ehi; dj++) {
+                            const double d = W[di + (size_t)dj * r];
+                            if (!isnan(d)) {
+                                const double kk = a.kern[(di - i + la) + (dj - j + la) * kw];
+                                val += kk * d;
+                                norm += kk;
+                            }
                         }
-                    }
-                out[p] = val / norm;
+                    out[p] = val / norm;
+                }
             }
         }
         if (tid == 0) {
             if (a.k_out) a.k_out[star] = k;
             if (a.status) a.status[star] = status;
+            *s_next = nxt;
         }
     }
 }
@@ -562,7 +783,7 @@ __global__ void __launch_bounds__(256) smooth_kernel(const SmoothArgs a) {
 }
 
 // dataPreprocessing.jl:94-110: a*sinc(pi x)*sinc(pi x / a) at integer offsets, outer product, normalised by the sum
-static void lanczos_kernel2d(int a, double *kernel) {
+static void lanczos_kernel2d(int a, double *kernel, double *kz = nullptr) {
     const int w = 2 * a + 1;
     auto sinc = [](double x) { return x == 0 ? 1.0 : sin(x) / x; };
     auto lz = [&](double x) { return (fabs(x) >= a) ? 0.0 : (x == 0 ? 1.0 : a * sinc(M_PI * x) * sinc(M_PI * x / a)); };
@@ -571,6 +792,7 @@ static void lanczos_kernel2d(int a, double *kernel) {
         for (int i = 0; i < w; i++) kernel[i + j * w] = lz(i - a) * lz(j - a);
     for (int i = 0; i < w * w; i++) sum += kernel[i];
     for (int i = 0; i < w * w; i++) kernel[i] /= sum;
+    if (kz) for (int i = 0; i < w; i++) kz[i] = lz(i - a);
 }
 
 // ---- launch -----------------------------------------------------------------------------------
@@ -579,7 +801,7 @@ static size_t pca_fixed_smem(int nw, int r, int c, int kmax) {
            (size_t)2 * ((kmax + 1) & ~1) * 4 + FB * 4;
 }
 static size_t pca_w_doubles(int r, int c, int kmax) {      // W plus the region shared by Y and the fast-path buffers
-    const size_t y = (size_t)kmax * c, f = (size_t)2 * FB * ((r + 1) & ~1) + (size_t)FB * c + 64;
+    const size_t y = (size_t)kmax * c, f = (size_t)2 * FB * ((r + 1) & ~1) + (size_t)FB * c + 192;
     return (size_t)r * c + (y > f ? y : f);
 }
 size_t pca_scratch_bytes(int r, int c, int ncomp) {
@@ -631,7 +853,7 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
     a.counter = d_counter; a.wglobal = nullptr; a.wstride = 0;
     a.kmax = ncomp < r ? ncomp : r; if (c < a.kmax) a.kmax = c;
     a.fast = (getenv("SHOPT_PCA_NO_FAST") == nullptr);
-    if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern);
+    if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern, a.kz);
     const int rt = ((r > c ? r : c) + 31) / 32;
     switch (rt) {
         case 1: return pca_launch_nw<1>(a, scratch, scratch_bytes, st);
