@@ -152,16 +152,17 @@ __device__ __forceinline__ void sts_f64(uint32_t addr, double v) {
 
 constexpr int SC_DOUBLES = 16;   // one broadcast block of the scalar section
 constexpr int LBFGS_M = 10;
+enum { CMD_EVAL = 1, CMD_EXIT = 2 };
 
 // Per-CTA state in shared memory (offset 0 of the dynamic shared memory).  Everything the scalar optimiser code keeps
 // between evaluations lives here or in registers: the 126 KB of L1 left beside three CTAs' crops cannot hold
 // per-thread stacks, and local-memory traffic was what bounded the first version of this kernel (profiles/).
 struct EvalShared {
-    double sc[2][SC_DOUBLES];          // double-buffered broadcast of the dual-number scalar section
+    double sc[SC_DOUBLES];             // broadcast of the dual-number scalar section (master -> everyone)
     double xl[3], fl, gl[3];           // NLSolversBase caches the last evaluated point by value
     double hist_dx[LBFGS_M][3], hist_dg[LBFGS_M][3], hist_rho[LBFGS_M], hist_alpha[LBFGS_M];
     uint32_t crop_s, fbuf_s;           // shared-space byte addresses: staged crop, profile plane (same indexing)
-    int n_a, pitch, TV, m0, rodd, plane, have_last, scb, buf;
+    int n_a, pitch, TV, m0, rodd, plane, have_last, cmd;
 };
 struct FG {
     double f, g0, g1, g2;
@@ -170,34 +171,49 @@ extern __shared__ __align__(16) unsigned char smem_raw[];
 __device__ __forceinline__ EvalShared &eval_shared() { return *reinterpret_cast<EvalShared *>(smem_raw); }
 constexpr int ES_BYTES = (sizeof(EvalShared) + 15) & ~15;
 
-// value_gradient!(d, x): the reference runs g! (ForwardDiff over cost) and then cost(x); the value channel of the dual
-// pass is the same operation sequence, so one evaluation yields both.  Arguments and result travel in registers.
+// Barrier of one evaluation (id 1; the star loop uses __syncthreads = id 0).  The master warp and the worker warps
+// arrive from different code, which named barriers allow as long as every warp of the CTA arrives.
 template <int THREADS>
-__device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
+__device__ __forceinline__ void bar_eval() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }
+
+// Deterministic warp sums with a fixed tree that halves the number of live values at each step instead of carrying
+// every value through five butterflies: 6 (8) 64-bit shuffles for 4 (5) values instead of 20 (25).
+// Result: value i on lane 8 i (i < 4); the fifth value on lane 4.
+__device__ __forceinline__ double warp_reduce4(double v0, double v1, double v2, double v3) {
+    const int lane = threadIdx.x & 31;
+    const bool b4 = lane & 16, b3 = lane & 8;
+    double k0 = (b4 ? v2 : v0) + __shfl_xor_sync(0xffffffffu, b4 ? v0 : v2, 16);
+    double k1 = (b4 ? v3 : v1) + __shfl_xor_sync(0xffffffffu, b4 ? v1 : v3, 16);
+    double k = (b3 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, b3 ? k0 : k1, 8);
+    k += __shfl_xor_sync(0xffffffffu, k, 4);
+    k += __shfl_xor_sync(0xffffffffu, k, 2);
+    k += __shfl_xor_sync(0xffffffffu, k, 1);
+    return k;
+}
+__device__ __forceinline__ double warp_reduce5(double v0, double v1, double v2, double v3, double v4) {
+    const int lane = threadIdx.x & 31;
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+    double k0 = (b4 ? v2 : v0) + __shfl_xor_sync(0xffffffffu, b4 ? v0 : v2, 16);
+    double k1 = (b4 ? v3 : v1) + __shfl_xor_sync(0xffffffffu, b4 ? v1 : v3, 16);
+    double k4 = v4 + __shfl_xor_sync(0xffffffffu, v4, 16);
+    double k = (b3 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, b3 ? k0 : k1, 8);
+    k4 += __shfl_xor_sync(0xffffffffu, k4, 8);
+    k = (b2 ? k4 : k) + __shfl_xor_sync(0xffffffffu, b2 ? k : k4, 4);
+    k += __shfl_xor_sync(0xffffffffu, k, 2);
+    k += __shfl_xor_sync(0xffffffffu, k, 1);
+    return k;
+}
+
+// The pixel passes of one evaluation, executed by every warp between the evaluation's first barrier (scalar block
+// published) and its third.  Only the master warp needs the totals; a worker needs sum f alone (the normalisation).
+template <int THREADS, bool MASTER>
+__device__ __forceinline__ void eval_pixels(double (&M)[4], double (&T)[5]) {
     constexpr int NWARPS = THREADS / 32;
     EvalShared &es = eval_shared();
-    FG out;
-    if (es.have_last && x0 == es.xl[0] && x1 == es.xl[1] && x2 == es.xl[2]) {
-        out.f = es.fl; out.g0 = es.gl[0]; out.g1 = es.gl[1]; out.g2 = es.gl[2];
-        return out;
-    }
-    double *scratch = reinterpret_cast<double *>(smem_raw + ES_BYTES);
-    const int scb = es.scb;
-    int buf = es.buf;
-    double *s = es.sc[scb];
-    if (threadIdx.x < 32) {   // scalar section, warp 0
-        Dual sig = d_seed(x0, 0), e1 = d_seed(x1, 1), e2 = d_seed(x2, 2);
-        Dual sg = d_sq(sig);
-        Dual g1, g2;
-        e_to_g_dual(e1, e2, g1, g2);
-        Dual a11 = d_radd(1.0, g1), a22 = d_rsub(1.0, g1);
-        Dual ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
-        if (threadIdx.x == 0) {
-            s[0] = a11.v; s[1] = a22.v; s[2] = g2.v; s[3] = ms.v;
-#pragma unroll
-            for (int j = 0; j < 3; j++) { s[4 + j] = a11.d[j]; s[7 + j] = a22.d[j]; s[10 + j] = g2.d[j]; s[13 + j] = ms.d[j]; }
-        }
-    }
+    double *scrA = reinterpret_cast<double *>(smem_raw + ES_BYTES);   // NWARPS x 4
+    double *scrB = scrA + NWARPS * 4;                                  // NWARPS x 5
+    const double *s = es.sc;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_a = es.n_a, pitch = es.pitch, TV = es.TV, m0 = es.m0, rodd = es.rodd;
     const bool plane = es.plane != 0;
     const uint32_t crop_s = es.crop_s, fbuf_s = es.fbuf_s;
@@ -205,7 +221,6 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
     const bool active = tv < TV;
     const double du = (double)(tu + 1) - n_a / 2.0;    // analyticLBFGS.jl:28,41: the centre is (r/2, c/2) of the crop
     const double dv0 = (double)(tv + 1) - n_a / 2.0;
-    __syncthreads();
     const double A11 = s[0], A22 = s[1], G2 = s[2], MS = s[3];
     // q = qa du^2 + qb du dv + qc dv^2
     const double qa = A11 * A11 + G2 * G2, qb = 2.0 * (G2 * (A11 + A22)), qc = G2 * G2 + A22 * A22;
@@ -226,8 +241,18 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
             dv += step;
         }
     }
-    double M[4] = {S0, (du * du) * S0, du * S1, S2};   // sum f, sum f du^2, sum f du dv, sum f dv^2
-    cta_sum<4, NWARPS>(M, scratch, buf);
+    {   // sum f, sum f du^2, sum f du dv, sum f dv^2
+        const double k = warp_reduce4(S0, (du * du) * S0, du * S1, S2);
+        if ((lane & 7) == 0) scrA[warp * 4 + (lane >> 3)] = k;
+    }
+    bar_eval<THREADS>();
+#pragma unroll
+    for (int i = 0; i < (MASTER ? 4 : 1); i++) {
+        double t = scrA[i];
+#pragma unroll
+        for (int w = 1; w < NWARPS; w++) t += scrA[w * 4 + i];
+        M[i] = t;
+    }
     const double A = 1.0 / M[0];
     // pass B: residual moments over non-NaN pixels (analyticLBFGS.jl:36-44)
     double R0 = 0.0, R1 = 0.0, R2 = 0.0, R3 = 0.0;
@@ -248,8 +273,55 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
             dv += step;
         }
     }
-    double T[5] = {0.5 * R0, R1, (du * du) * R1, du * R2, R3};   // cost, sum rho f, its du^2, du dv, dv^2 moments
-    cta_sum<5, NWARPS>(T, scratch, buf);
+    {   // cost, sum rho f, its du^2, du dv, dv^2 moments
+        const double k = warp_reduce5(R1, (du * du) * R1, du * R2, R3, 0.5 * R0);
+        if ((lane & 7) == 0) scrB[warp * 5 + 1 + (lane >> 3)] = k;
+        else if (lane == 4) scrB[warp * 5] = k;
+    }
+    bar_eval<THREADS>();
+    if (MASTER) {
+#pragma unroll
+        for (int i = 0; i < 5; i++) {
+            double t = scrB[i];
+#pragma unroll
+            for (int w = 1; w < NWARPS; w++) t += scrB[w * 5 + i];
+            T[i] = t;
+        }
+    }
+}
+
+// value_gradient!(d, x): the reference runs g! (ForwardDiff over cost) and then cost(x); the value channel of the dual
+// pass is the same operation sequence, so one evaluation yields both.  MASTER WARP ONLY: it owns the optimiser state;
+// the other warps sit in worker_loop() and join the pixel passes of every evaluation.
+template <int THREADS>
+__device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
+    EvalShared &es = eval_shared();
+    FG out;
+    if (es.have_last && x0 == es.xl[0] && x1 == es.xl[1] && x2 == es.xl[2]) {
+        out.f = es.fl; out.g0 = es.gl[0]; out.g1 = es.gl[1]; out.g2 = es.gl[2];
+        return out;
+    }
+    double *s = es.sc;
+    {   // scalar section
+        Dual sig = d_seed(x0, 0), e1 = d_seed(x1, 1), e2 = d_seed(x2, 2);
+        Dual sg = d_sq(sig);
+        Dual g1, g2;
+        e_to_g_dual(e1, e2, g1, g2);
+        Dual a11 = d_radd(1.0, g1), a22 = d_rsub(1.0, g1);
+        Dual ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
+        if (threadIdx.x == 0) {
+            s[0] = a11.v; s[1] = a22.v; s[2] = g2.v; s[3] = ms.v;
+#pragma unroll
+            for (int j = 0; j < 3; j++) { s[4 + j] = a11.d[j]; s[7 + j] = a22.d[j]; s[10 + j] = g2.d[j]; s[13 + j] = ms.d[j]; }
+            es.cmd = CMD_EVAL;
+        }
+    }
+    bar_eval<THREADS>();
+    double M[4], T[5];
+    eval_pixels<THREADS, true>(M, T);
+    const double A11 = s[0], A22 = s[1], G2 = s[2], MS = s[3];
+    const double qa = A11 * A11 + G2 * G2, qb = 2.0 * (G2 * (A11 + A22)), qc = G2 * G2 + A22 * A22;
+    const double A = 1.0 / M[0];
     // rebuild the reference's sums from the moments, then the chain rule:
     //   sum.d_j = -(ms.d_j Sq + 2 ms (a11.d_j S2 + g2.d_j S3 + a22.d_j S4))
     const double Sq = qa * M[1] + qb * M[2] + qc * M[3];
@@ -270,11 +342,24 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
         g[j] = dA * T[1] + A * dT;
     }
     out.f = T[0]; out.g0 = g[0]; out.g1 = g[1]; out.g2 = g[2];
-    // every thread stores the same bits; the barriers above order these writes against the other threads' reads
+    // every lane of the master warp stores the same bits
     es.xl[0] = x0; es.xl[1] = x1; es.xl[2] = x2;
     es.fl = out.f; es.gl[0] = g[0]; es.gl[1] = g[1]; es.gl[2] = g[2];
-    es.have_last = 1; es.scb = scb ^ 1; es.buf = buf;
+    es.have_last = 1;
+    __syncwarp();
     return out;
+}
+
+// Worker warps: wait for the master's command, join the pixel passes, repeat until the star is done.
+template <int THREADS>
+__device__ __forceinline__ void worker_loop() {
+    EvalShared &es = eval_shared();
+    for (;;) {
+        bar_eval<THREADS>();
+        if (*reinterpret_cast<volatile int *>(&es.cmd) == CMD_EXIT) break;
+        double M[4], T[5];
+        eval_pixels<THREADS, false>(M, T);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -686,7 +771,7 @@ __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
             es.crop_s = smem_u32(crop_base + b * crop_stride); es.fbuf_s = smem_u32(fplane);
             es.n_a = a.n_a; es.pitch = a.pitch; es.TV = THREADS / a.n_a;      // n_a <= THREADS (checked at launch)
             es.m0 = (int)((base + mis0) & 1); es.rodd = a.r & 1; es.plane = a.plane;
-            es.have_last = 0; es.scb = 0; es.buf = 0;
+            es.have_last = 0; es.cmd = 0;
         }
         double *crop = crop_base + b * crop_stride;
         mbar_wait(&bars[b], phase[b]);
@@ -694,21 +779,29 @@ __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
         load_edges(a, cur, crop);
         __syncthreads();   // edge columns, next_star and the evaluator state visible
 
-        const double x0[3] = {a.x0[3 * cur + 0], a.x0[3 * cur + 1], a.x0[3 * cur + 2]};
-        double p[3];
-        int iters = 0;
-        if (a.f_out) {   // cost(x0), g!(G, x0) only
-            const FG r = eval_fg<THREADS>(x0[0], x0[1], x0[2]);
-            if (threadIdx.x == 0) {
-                a.f_out[cur] = r.f;
-                a.g_out[3 * cur + 0] = r.g0; a.g_out[3 * cur + 1] = r.g1; a.g_out[3 * cur + 2] = r.g2;
+        if (threadIdx.x >= 32) {
+            worker_loop<THREADS>();
+        } else {   // master warp: the scalar LBFGS / HagerZhang state machine, every lane redundantly
+            const double x0[3] = {a.x0[3 * cur + 0], a.x0[3 * cur + 1], a.x0[3 * cur + 2]};
+            double p[3];
+            int iters = 0;
+            if (a.f_out) {   // cost(x0), g!(G, x0) only
+                const FG r = eval_fg<THREADS>(x0[0], x0[1], x0[2]);
+                if (threadIdx.x == 0) {
+                    a.f_out[cur] = r.f;
+                    a.g_out[3 * cur + 0] = r.g0; a.g_out[3 * cur + 1] = r.g1; a.g_out[3 * cur + 2] = r.g2;
+                }
             }
-        }
-        const int st = a.f_out ? 0 : lbfgs_fit<THREADS>(x0, a.g_tol, a.max_iter, p, iters);
-        if (threadIdx.x == 0 && !a.f_out) {
-            a.s[cur] = p[0]; a.g1[cur] = p[1]; a.g2[cur] = p[2];
-            if (a.status) a.status[cur] = st;
-            if (a.iters) a.iters[cur] = iters;
+            const int st = a.f_out ? 0 : lbfgs_fit<THREADS>(x0, a.g_tol, a.max_iter, p, iters);
+            if (threadIdx.x == 0) {
+                if (!a.f_out) {
+                    a.s[cur] = p[0]; a.g1[cur] = p[1]; a.g2[cur] = p[2];
+                    if (a.status) a.status[cur] = st;
+                    if (a.iters) a.iters[cur] = iters;
+                }
+                eval_shared().cmd = CMD_EXIT;
+            }
+            bar_eval<THREADS>();   // releases the workers
         }
         __syncthreads();   // everyone is done with crop[b], scratch and the evaluator state
         const long long nx = next_star[slot ^ 1];

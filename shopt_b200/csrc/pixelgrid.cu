@@ -265,9 +265,8 @@ __device__ void cholqr(const double *Qsrc, double *Qdst, int r, int ldq, double 
 
 // Symmetric 8 x 8 eigenproblem  G = V diag(theta) V'  by cyclic two-sided Jacobi inside ONE warp (Rayleigh-Ritz of the
 // block).  Lane l owns row (l & 7) of the working matrix and of V (the four groups of eight lanes run the same
-// computation).  A sweep is the 7-step round-robin tournament on 8 indices, 4 disjoint pairs per step; every lane
-// computes the four rotations of a step (they are independent, so the divisions and square roots overlap) and all
-// register indices are compile-time constants.  Gt: lower triangle, e = i(i+1)/2 + j;  Vout[a * 8 + b] = V_ab.
+// computation).  A sweep is the 7-step round-robin tournament on 8 indices, 4 disjoint pairs per step; lane group m
+// computes the rotation of pair m and broadcasts it; all register indices are compile-time constants.  Gt: lower triangle, e = i(i+1)/2 + j;  Vout[a * 8 + b] = V_ab.
 __device__ void eig8_warp(const double *Gt, double *Vout) {
     const int lane = threadIdx.x & 31, i = lane & 7;
     double a[FB], v[FB], dg;
@@ -277,35 +276,52 @@ __device__ void eig8_warp(const double *Gt, double *Vout) {
         v[j] = (i == j) ? 1.0 : 0.0;
     }
     dg = Gt[i * (i + 1) / 2 + i];
+    const int grp = lane >> 3;                               // group m of eight lanes computes the rotation of pair m
     for (int sweep = 0; sweep < 16; sweep++) {
         int rotated = 0;
 #pragma unroll
         for (int s = 0; s < 7; s++) {
-            double cs[4], sn[4], dnew = dg;
-            bool amP = false;
-            double myc = 1.0, mys = 0.0;
+            // pair m of step s: (7, s) for m = 0, ((s + m) % 7, (s - m) % 7) otherwise, ordered P < Q
+            double apq = 0.0, app = 0.0, aqq = 0.0;
 #pragma unroll
             for (int m = 0; m < 4; m++) {
                 const int x = (m == 0) ? 7 : (s + m) % 7, y = (m == 0) ? s : (s - m + 7) % 7;
                 const int P = x < y ? x : y, Q = x < y ? y : x;
-                const double apq = __shfl_sync(0xffffffffu, a[Q], P, 8);
-                const double app = __shfl_sync(0xffffffffu, dg, P, 8);
-                const double aqq = __shfl_sync(0xffffffffu, dg, Q, 8);
-                double c = 1.0, sg = 0.0, t = 0.0;
-                if (fabs(apq) > DBL_EPSILON * sqrt(fabs(app * aqq)) && apq != 0.0) {
-                    const double zeta = (aqq - app) / (2.0 * apq);
-                    t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-                    c = rsqrt(1.0 + t * t);
-                    sg = c * t;
-                    rotated = 1;
-                }
-                cs[m] = c; sn[m] = sg;
-                if (i == P) { amP = true; myc = c; mys = sg; dnew = app - t * apq; }
-                if (i == Q) { myc = c; mys = sg; dnew = aqq + t * apq; }
+                const double e = __shfl_sync(0xffffffffu, a[Q], P, 8);
+                const double dp = __shfl_sync(0xffffffffu, dg, P, 8);
+                const double dq = __shfl_sync(0xffffffffu, dg, Q, 8);
+                if (grp == m) { apq = e; app = dp; aqq = dq; }
+            }
+            // t = tan(theta) from  t = h sgn(d) / (|d| + sqrt(d^2 + h^2)),  d = aqq - app, h = 2 apq.  Only c^2 + s^2 = 1
+            // needs full accuracy (c = rsqrt(1 + t^2), s = t c), so the quotient uses rsqrt instead of IEEE div/sqrt.
+            double c = 1.0, sg = 0.0, t = 0.0;
+            if (apq * apq > (DBL_EPSILON * DBL_EPSILON) * fabs(app * aqq) && apq != 0.0) {
+                const double d = aqq - app, h = 2.0 * apq;
+                const double w = fma(d, d, h * h);
+                const double den = fabs(d) + w * rsqrt(w);
+                const double ri = rsqrt(den);
+                t = copysign(h, h * d) * (ri * ri);
+                if (d == 0.0) t = copysign(1.0, apq);
+                if (isfinite(t)) { c = rsqrt(fma(t, t, 1.0)); sg = c * t; } else t = 0.0;
+            }
+            double myc = 1.0, mys = 0.0, dnew = dg;
+            bool amP = false;
+#pragma unroll
+            for (int m = 0; m < 4; m++) {
+                const int x = (m == 0) ? 7 : (s + m) % 7, y = (m == 0) ? s : (s - m + 7) % 7;
+                const int P = x < y ? x : y, Q = x < y ? y : x;
+                const double cm = __shfl_sync(0xffffffffu, c, 8 * m);
+                const double sm = __shfl_sync(0xffffffffu, sg, 8 * m);
+                const double tp = __shfl_sync(0xffffffffu, t * apq, 8 * m);
+                const double pp = __shfl_sync(0xffffffffu, app, 8 * m);
+                const double qq = __shfl_sync(0xffffffffu, aqq, 8 * m);
+                if (sm != 0.0) rotated = 1;
+                if (i == P) { amP = true; myc = cm; mys = sm; dnew = pp - tp; }
+                if (i == Q) { myc = cm; mys = sm; dnew = qq + tp; }
                 // columns P, Q of this lane's rows (A J and V J)
                 const double ap = a[P], aq = a[Q], vp = v[P], vq = v[Q];
-                a[P] = cs[m] * ap - sn[m] * aq; a[Q] = sn[m] * ap + cs[m] * aq;
-                v[P] = cs[m] * vp - sn[m] * vq; v[Q] = sn[m] * vp + cs[m] * vq;
+                a[P] = cm * ap - sm * aq; a[Q] = sm * ap + cm * aq;
+                v[P] = cm * vp - sm * vq; v[Q] = sm * vp + cm * vq;
             }
             // rows: J' (A J); the partner of index i in step s of the tournament
             const int partner = (i == 7) ? s : ((i == s) ? 7 : (2 * s - i + 14) % 7);
