@@ -52,7 +52,9 @@ int get_ctx(Ctx **out) {
     Ctx &c = g_ctx[dev];
     if (c.dev != dev) {
         SHOPT_CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+        SHOPT_CUDA_TRY(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
         for (int i = 0; i < 4; i++) SHOPT_CUDA_TRY(cudaEventCreate(&c.ev[i]));
+        for (int i = 0; i < Ctx::NCHUNK_EV; i++) SHOPT_CUDA_TRY(cudaEventCreateWithFlags(&c.chunk_ev[i], cudaEventDisableTiming));
         SHOPT_CUDA_TRY(cudaMalloc(&c.counter, 64));
         c.dev = dev;
     }

@@ -9,6 +9,9 @@ namespace shopt {
 struct Ctx {
     int dev = -1;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;      // H2D of the pipelined host entry points
+    static constexpr int NCHUNK_EV = 16;
+    cudaEvent_t chunk_ev[NCHUNK_EV] = {};
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     unsigned long long *counter = nullptr;   // 8 slots, rotated per launch so overlapping launches never share one
     unsigned slot = 0;

@@ -45,7 +45,33 @@ int64_t shopt_training_split(const int32_t *flags, int64_t n_global, const int64
     return m;
 }
 
-int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream) {
+}  // extern "C"
+
+namespace shopt {
+
+// Per-star phase on stars [first, first + count) of a device-resident shard: model fit, pixel-grid fit, learned fit
+// (shopt.jl:130-164, 281-314, 357-397).  Enqueues three launches on `st`; d_tmp = 3 ints per star of the shard.
+static int stage_per_star(const shopt_params *p, const shopt_stage_io *io, long long first, long long count, int *d_tmp,
+                          Ctx *ctx, cudaStream_t st) {
+    if (count <= 0) return SHOPT_OK;
+    const int r = io->r, c = io->c;
+    const long long n = io->n_local, rc = (long long)r * c;
+    const size_t nn = (size_t)std::max<long long>(n, 1);
+    int *d_fst = d_tmp + first, *d_fit = d_tmp + nn + first, *d_pst = d_tmp + 2 * nn + first;
+    double *m = io->model, *l = io->learned;
+    const double *stamps = io->stamps + first * rc;
+    double *pgf = io->pgf + first * rc;
+    TRY(fit_analytic_launch(stamps, r, c, count, p->n_a, io->x0_model + 3 * first, p->g_tol_model, p->max_iter, m + first,
+                            m + n + first, m + 2 * n + first, d_fst, d_fit, ctx->next_counter(), st));
+    TRY(pca_launch(stamps, r, c, count, p->pca_terms, p->pratio, p->lanczos, p->unity_sum, pgf,
+                   io->pca_k ? io->pca_k + first : nullptr, d_pst, ctx->next_counter(), (double *)ctx->scratch,
+                   ctx->scratch_bytes, st));
+    TRY(fit_analytic_launch(pgf, r, c, count, p->n_a, io->x0_learned + 3 * first, p->g_tol_learned, p->max_iter, l + first,
+                            l + n + first, l + 2 * n + first, d_fst, d_fit, ctx->next_counter(), st));
+    return SHOPT_OK;
+}
+
+static int stage_check_args(const shopt_params *p, const shopt_stage_io *io) {
     if (!p || !io || !io->stamps || !io->u || !io->v || !io->x0_model || !io->x0_learned || !io->model || !io->learned ||
         !io->pgf || !io->flags || !io->poly)
         return SHOPT_E_BADARG;
@@ -54,25 +80,29 @@ int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allredu
     if (r < 1 || c < 2 || n < 0 || NG < n || off < 0 || off + n > NG || (NG > 0 && !io->perm)) return SHOPT_E_BADARG;
     if (p->degree < 0 || p->degree > 8 || p->iterations < 0 || p->n_a < 1 || p->n_a > r || p->n_a > c) return SHOPT_E_BADARG;
     if (p->median_constraint) return SHOPT_E_UNSUPPORTED;
+    return SHOPT_OK;
+}
+static size_t stage_scratch_bytes(const shopt_params *p, const shopt_stage_io *io) {
+    return std::max(pca_scratch_bytes(io->r, io->c, p->pca_terms),
+                    polyfit_scratch_bytes((long long)io->r * io->c, io->n_local, p->degree));
+}
+
+// The stage on a device-resident shard.  d_tmp: 3 ints per star (fit status | fit iterations | pca status);
+// per_star_done: the caller has already enqueued stage_per_star() for every star on `st` (the pipelined host path).
+static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream,
+                          int *d_tmp, bool per_star_done) {
     Ctx *ctx; TRY(get_ctx(&ctx));
+    const int r = io->r, c = io->c;
+    const long long n = io->n_local, NG = io->n_global, off = io->offset;
     cudaStream_t st = (cudaStream_t)stream;
     const long long rc = (long long)r * c;
     const int K = (p->degree + 1) * (p->degree + 2) / 2;
     const size_t nn = (size_t)std::max<long long>(n, 1);
-    DevBuf dint, dacc, didx, dmse, dkeep, dinfo;
-    TRY(dint.alloc(nn * 12));                       // fit status | fit iters (reused) | pca status
-    int *d_fst = dint.as<int>(), *d_fit = d_fst + nn, *d_pst = d_fit + nn;
-    size_t scratch = std::max(pca_scratch_bytes(r, c, p->pca_terms), polyfit_scratch_bytes(rc, n, p->degree));
-    TRY(ctx->need_scratch(scratch));
-
-    // ---- model fit, pixel-grid fit, learned fit (every star of the shard; flags decide who counts) ----
+    DevBuf dacc, didx, dmse, dkeep, dinfo;
+    int *d_pst = d_tmp + 2 * nn;
     double *m = io->model, *l = io->learned;
-    TRY(fit_analytic_launch(io->stamps, r, c, n, p->n_a, io->x0_model, p->g_tol_model, p->max_iter, m, m + n, m + 2 * n,
-                            d_fst, d_fit, ctx->next_counter(), st));
-    TRY(pca_launch(io->stamps, r, c, n, p->pca_terms, p->pratio, p->lanczos, p->unity_sum, io->pgf, io->pca_k, d_pst,
-                   ctx->next_counter(), (double *)ctx->scratch, ctx->scratch_bytes, st));
-    TRY(fit_analytic_launch(io->pgf, r, c, n, p->n_a, io->x0_learned, p->g_tol_learned, p->max_iter, l, l + n, l + 2 * n,
-                            d_fst, d_fit, ctx->next_counter(), st));
+    // ---- model fit, pixel-grid fit, learned fit (every star of the shard; flags decide who counts) ----
+    if (!per_star_done) TRY(stage_per_star(p, io, 0, n, d_tmp, ctx, st));
     if (n > 0) flag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(m, d_pst, l, n, p->s_lo, p->s_hi, io->flags);
     SHOPT_CUDA_TRY(cudaGetLastError());
     std::vector<int> flags((size_t)n);
@@ -169,6 +199,21 @@ int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allredu
     return SHOPT_OK;
 }
 
+}  // namespace shopt
+
+extern "C" {
+
+int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream) {
+    TRY(stage_check_args(p, io));
+    Ctx *ctx; TRY(get_ctx(&ctx));
+    DevBuf dint;
+    TRY(dint.alloc((size_t)std::max<long long>(io->n_local, 1) * 12));
+    TRY(ctx->need_scratch(stage_scratch_bytes(p, io)));
+    return stage_run_impl(p, io, comm, comm_user, stream, dint.as<int>(), false);
+}
+
+// Host buffers, one GPU.  The stamps go up in chunks on a copy stream while the per-star kernels of the chunks that
+// have landed run on the compute stream, so the H2D transfer (13.7 GB at 100k x 131 x 131) hides behind the fits.
 int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) {
     if (!p || !io || !io->stamps || !io->u || !io->v || !io->x0_model || !io->x0_learned || !io->model || !io->learned ||
         !io->flags || !io->poly)
@@ -177,23 +222,39 @@ int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) {
     Ctx *ctx; TRY(get_ctx(&ctx));
     const size_t n = (size_t)io->n_local, rc = (size_t)io->r * io->c, nn = std::max<size_t>(n, 1);
     const size_t K = (size_t)(p->degree + 1) * (p->degree + 2) / 2;
-    DevBuf dst, dpgf, dsm, dout, dint, dpoly;
+    DevBuf dst, dpgf, dsm, dout, dint, dpoly, dtmp;
     TRY(dst.alloc(nn * rc * 8)); TRY(dpgf.alloc(nn * rc * 8)); TRY(dsm.alloc(nn * 8 * 8)); TRY(dout.alloc(nn * 6 * 8));
-    TRY(dint.alloc(nn * 8)); TRY(dpoly.alloc(K * rc * 8));
-    cudaStream_t st = ctx->stream;
+    TRY(dint.alloc(nn * 8)); TRY(dpoly.alloc(K * rc * 8)); TRY(dtmp.alloc(nn * 12));
+    cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
     double *small = dsm.as<double>();                // u | v | x0_model (3n) | x0_learned (3n)
-    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[0], st));
-    SHOPT_CUDA_TRY(cudaMemcpyAsync(dst.p, io->stamps, n * rc * 8, cudaMemcpyHostToDevice, st));
-    SHOPT_CUDA_TRY(cudaMemcpyAsync(small, io->u, n * 8, cudaMemcpyHostToDevice, st));
-    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + n, io->v, n * 8, cudaMemcpyHostToDevice, st));
-    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + 2 * n, io->x0_model, n * 24, cudaMemcpyHostToDevice, st));
-    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + 5 * n, io->x0_learned, n * 24, cudaMemcpyHostToDevice, st));
-    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[1], st));
     shopt_stage_io d = *io;
     d.stamps = dst.as<double>(); d.u = small; d.v = small + n; d.x0_model = small + 2 * n; d.x0_learned = small + 5 * n;
     d.model = dout.as<double>(); d.learned = dout.as<double>() + 3 * n; d.pgf = dpgf.as<double>();
     d.flags = dint.as<int32_t>(); d.pca_k = io->pca_k ? dint.as<int32_t>() + n : nullptr; d.poly = dpoly.as<double>();
-    TRY(shopt_stage_run_dev(p, &d, nullptr, nullptr, st));
+    TRY(stage_check_args(p, &d));
+    TRY(ctx->need_scratch(stage_scratch_bytes(p, &d)));
+    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[0], st));
+    SHOPT_CUDA_TRY(cudaStreamWaitEvent(cs, ctx->ev[0], 0));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(small, io->u, n * 8, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + n, io->v, n * 8, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + 2 * n, io->x0_model, n * 24, cudaMemcpyHostToDevice, st));
+    SHOPT_CUDA_TRY(cudaMemcpyAsync(small + 5 * n, io->x0_learned, n * 24, cudaMemcpyHostToDevice, st));
+    // chunks: at least ~16 stars per resident CTA so the persistent kernels keep their tail short; at most NCHUNK_EV
+    long long nchunks = (long long)n / (16LL * 3 * sm_count());
+    if (nchunks > Ctx::NCHUNK_EV) nchunks = Ctx::NCHUNK_EV;
+    if (nchunks < 1) nchunks = 1;
+    const long long per = ((long long)n + nchunks - 1) / nchunks;
+    for (long long ck = 0; ck < nchunks; ck++) {
+        const long long first = ck * per, count = std::min<long long>(per, (long long)n - first);
+        if (count <= 0) break;
+        SHOPT_CUDA_TRY(cudaMemcpyAsync(dst.as<double>() + first * rc, io->stamps + first * rc, (size_t)count * rc * 8,
+                                       cudaMemcpyHostToDevice, cs));
+        SHOPT_CUDA_TRY(cudaEventRecord(ctx->chunk_ev[ck], cs));
+        SHOPT_CUDA_TRY(cudaStreamWaitEvent(st, ctx->chunk_ev[ck], 0));
+        TRY(stage_per_star(p, &d, first, count, dtmp.as<int>(), ctx, st));
+    }
+    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[1], cs));    // last stamp on the device
+    TRY(stage_run_impl(p, &d, nullptr, nullptr, st, dtmp.as<int>(), true));
     SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[2], st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(io->model, d.model, n * 24, cudaMemcpyDeviceToHost, st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(io->learned, d.learned, n * 24, cudaMemcpyDeviceToHost, st));
