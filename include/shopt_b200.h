@@ -105,6 +105,25 @@ int shopt_smooth_batch(const double *stamps, int r, int c, int64_t N, int lanczo
 int shopt_smooth_batch_dev(const double *d_stamps, int r, int c, int64_t N, int lanczos_a,
                            int nan_to_zero, double *d_out, void *stream);
 
+/* The whole loop body of mode == "smooth" (shopt.jl:316-348) per star: data = nanToZero(star); unity_sum == 0 ->
+ * smooth(data, lanczos_a); unity_sum != 0 -> data ./ sum(data) (the reference's smooth(data) call with one argument
+ * raises, so its catch branch :330 runs and nothing is smoothed). */
+int shopt_smooth_mode_batch(const double *stamps, int r, int c, int64_t N, int lanczos_a, int unity_sum, double *pgf);
+int shopt_smooth_mode_batch_dev(const double *d_stamps, int r, int c, int64_t N, int lanczos_a, int unity_sum,
+                                double *d_pgf, void *stream);
+
+/* mode == "chisq" (shopt.jl:194-224 with chisq_cost / chisq_g!, chisq.jl:1-11): the reference minimises
+ *   sum_px isfinite(t) ? t : 0,  t = (p - star)^2 / weight     over the r*c pixel values p by LBFGS from rand(r*c).
+ * The objective is separable and quadratic per pixel, so the minimiser is written down directly: p = star wherever the
+ * term is a finite convex quadratic (star finite, weight finite and > 0); every other pixel has zero gradient and
+ * keeps its START value -- x0 (r,c,N), the reference's rand(r*c), an explicit input; x0 == NULL -> `fill`.
+ * (LBFGS stops at |2 (p - star) / weight| <= g_tol, i.e. within g_tol * weight / 2 of this answer.)
+ * unity_sum != 0 divides each fit by its sum (shopt.jl:216-218).  weights (r,c,N) = errVignets. */
+int shopt_chisq_batch(const double *stamps, const double *weights, const double *x0, double fill, int r, int c,
+                      int64_t N, int unity_sum, double *pgf);
+int shopt_chisq_batch_dev(const double *d_stamps, const double *d_weights, const double *d_x0, double fill, int r, int c,
+                          int64_t N, int unity_sum, double *d_pgf, void *stream);
+
 /* ---- (3) per-pixel polynomial interpolation with outlier-star rejection ----------------------
  * Replaces shopt/shopt.jl:492-577: `iterations` rounds of
  *   polynomial_optimizer(degree, u, v, z) per pixel (interpolate.jl:105-147; term order p outer,
@@ -168,7 +187,12 @@ typedef struct shopt_params {
     double training_ratio;      /* training_ratio                                                */
     int    median_constraint;   /* median_constraint                                             */
     int    sigma_clip;          /* outlier_sigma_clipping                                        */
+    int    mode;                /* mode: SHOPT_MODE_PCA / _SMOOTH / _CHISQ (pixel-grid fit)      */
+    double chisq_fill;          /* mode chisq without a start cube: value of the pixels that have no finite term */
 } shopt_params;
+#define SHOPT_MODE_PCA    0     /* shopt.jl:281-314 */
+#define SHOPT_MODE_SMOOTH 1     /* shopt.jl:316-348 (the shipped shopt.yml default) */
+#define SHOPT_MODE_CHISQ  2     /* shopt.jl:194-224 */
 void shopt_default_params(shopt_params *p);     /* README.md:300-330 documented defaults          */
 
 #define SHOPT_FLAG_BLACKLISTED 1   /* model s out of [s_lo, s_hi]            (shopt.jl:166-171)   */
@@ -204,6 +228,9 @@ typedef struct shopt_stage_io {
     double *poly;                /* (r, c, K) PolynomialMatrix                                    */
     int64_t *n_per_round;        /* HOST (iterations): training-set size of each round; may be NULL */
     int64_t counts[4];           /* HOST: blacklisted, failed, training stars, kept after the last applied rejection */
+    /* inputs of mode chisq only (same residence as stamps); may be NULL otherwise */
+    const double *weights;       /* (r, c, n_local) errVignets                                    */
+    const double *x0_pixels;     /* (r, c, n_local) start values (the reference's rand(r*c)); NULL -> chisq_fill */
 } shopt_stage_io;
 
 /* Host logic of the split, exposed for sharded hosts and tests (shopt.jl:472-478): flags (n_global) = SHOPT_FLAG_* of

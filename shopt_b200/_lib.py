@@ -36,7 +36,7 @@ class Params(C.Structure):
                 ("max_iter", C.c_int), ("s_lo", C.c_double), ("s_hi", C.c_double), ("pca_terms", C.c_int),
                 ("pratio", C.c_double), ("lanczos", C.c_int), ("unity_sum", C.c_int), ("degree", C.c_int),
                 ("iterations", C.c_int), ("training_ratio", C.c_double), ("median_constraint", C.c_int),
-                ("sigma_clip", C.c_int)]
+                ("sigma_clip", C.c_int), ("mode", C.c_int), ("chisq_fill", C.c_double)]
 
 
 class StageIO(C.Structure):
@@ -44,10 +44,11 @@ class StageIO(C.Structure):
     _fields_ = [("stamps", vp), ("r", C.c_int), ("c", C.c_int), ("n_local", C.c_int64), ("u", vp), ("v", vp),
                 ("x0_model", vp), ("x0_learned", vp), ("n_global", C.c_int64), ("offset", C.c_int64), ("perm", vp),
                 ("model", vp), ("learned", vp), ("pgf", vp), ("flags", vp), ("pca_k", vp), ("poly", vp),
-                ("n_per_round", vp), ("counts", C.c_int64 * 4)]
+                ("n_per_round", vp), ("counts", C.c_int64 * 4), ("weights", vp), ("x0_pixels", vp)]
 
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p)
+MODE_PCA, MODE_SMOOTH, MODE_CHISQ = 0, 1, 2
 FLAG_BLACKLISTED, FLAG_PCA_FAILED, FLAG_LEARNED_OOB, FLAG_TRAINING, FLAG_REJECTED = 1, 2, 4, 8, 16
 
 # name -> (restype, argtypes); every symbol include/shopt_b200.h declares
@@ -69,6 +70,10 @@ SIGNATURES = {
                                       vp, vp, vp, vp]),
     "shopt_smooth_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, dp]),
     "shopt_smooth_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, vp, vp]),
+    "shopt_smooth_mode_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, dp]),
+    "shopt_smooth_mode_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, vp, vp]),
+    "shopt_chisq_batch": (C.c_int, [dp, dp, dp, C.c_double, C.c_int, C.c_int, C.c_int64, C.c_int, dp]),
+    "shopt_chisq_batch_dev": (C.c_int, [vp, vp, vp, C.c_double, C.c_int, C.c_int, C.c_int64, C.c_int, vp, vp]),
     "shopt_polyfit": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, dp, dp, lp, C.c_int64, C.c_int, C.c_int, C.c_int,
                                 C.c_int, dp, dp, lp, lp, lp]),
     "shopt_polyfit_acc_len": (C.c_int64, [C.c_int, C.c_int, C.c_int]),

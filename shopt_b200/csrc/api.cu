@@ -104,6 +104,7 @@ void shopt_default_params(shopt_params *p) {
     p->n_a = 64; p->g_tol_model = 1e-6; p->g_tol_learned = 1e-6; p->max_iter = 1000;
     p->s_lo = 0.075; p->s_hi = 1.0; p->pca_terms = 50; p->pratio = 0.99; p->lanczos = 3; p->unity_sum = 0;
     p->degree = 3; p->iterations = 3; p->training_ratio = 0.8; p->median_constraint = 0; p->sigma_clip = 0;
+    p->mode = SHOPT_MODE_PCA; p->chisq_fill = 0.0;
 }
 
 // ---- (1) analytic fit ---------------------------------------------------------------------

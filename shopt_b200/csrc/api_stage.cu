@@ -63,9 +63,21 @@ static int stage_per_star(const shopt_params *p, const shopt_stage_io *io, long 
     double *pgf = io->pgf + first * rc;
     TRY(fit_analytic_launch(stamps, r, c, count, p->n_a, io->x0_model + 3 * first, p->g_tol_model, p->max_iter, m + first,
                             m + n + first, m + 2 * n + first, d_fst, d_fit, ctx->next_counter(), st));
-    TRY(pca_launch(stamps, r, c, count, p->pca_terms, p->pratio, p->lanczos, p->unity_sum, pgf,
-                   io->pca_k ? io->pca_k + first : nullptr, d_pst, ctx->next_counter(), (double *)ctx->scratch,
-                   ctx->scratch_bytes, st));
+    if (p->mode == SHOPT_MODE_PCA) {
+        TRY(pca_launch(stamps, r, c, count, p->pca_terms, p->pratio, p->lanczos, p->unity_sum, pgf,
+                       io->pca_k ? io->pca_k + first : nullptr, d_pst, ctx->next_counter(), (double *)ctx->scratch,
+                       ctx->scratch_bytes, st));
+    } else {   // element-wise modes never fail a star (shopt.jl:194-224, 316-348)
+        if (p->mode == SHOPT_MODE_SMOOTH && !p->unity_sum)
+            TRY(smooth_launch(stamps, r, c, count, p->lanczos, 1, pgf, st));
+        else if (p->mode == SHOPT_MODE_SMOOTH)
+            TRY(elem_pgf_launch(stamps, nullptr, nullptr, 0.0, rc, count, 0, 1, pgf, st));
+        else
+            TRY(elem_pgf_launch(stamps, io->weights + first * rc, io->x0_pixels ? io->x0_pixels + first * rc : nullptr,
+                                p->chisq_fill, rc, count, 1, p->unity_sum ? 1 : 0, pgf, st));
+        SHOPT_CUDA_TRY(cudaMemsetAsync(d_pst, 0, (size_t)count * 4, st));
+        if (io->pca_k) SHOPT_CUDA_TRY(cudaMemsetAsync(io->pca_k + first, 0, (size_t)count * 4, st));
+    }
     TRY(fit_analytic_launch(pgf, r, c, count, p->n_a, io->x0_learned + 3 * first, p->g_tol_learned, p->max_iter, l + first,
                             l + n + first, l + 2 * n + first, d_fst, d_fit, ctx->next_counter(), st));
     return SHOPT_OK;
@@ -80,10 +92,13 @@ static int stage_check_args(const shopt_params *p, const shopt_stage_io *io) {
     if (r < 1 || c < 2 || n < 0 || NG < n || off < 0 || off + n > NG || (NG > 0 && !io->perm)) return SHOPT_E_BADARG;
     if (p->degree < 0 || p->degree > 8 || p->iterations < 0 || p->n_a < 1 || p->n_a > r || p->n_a > c) return SHOPT_E_BADARG;
     if (p->median_constraint) return SHOPT_E_UNSUPPORTED;
+    if (p->mode < SHOPT_MODE_PCA || p->mode > SHOPT_MODE_CHISQ) return SHOPT_E_BADARG;
+    if (p->mode == SHOPT_MODE_CHISQ && !io->weights) return SHOPT_E_BADARG;
+    if (p->mode == SHOPT_MODE_SMOOTH && p->lanczos > 7) return SHOPT_E_BADARG;
     return SHOPT_OK;
 }
 static size_t stage_scratch_bytes(const shopt_params *p, const shopt_stage_io *io) {
-    return std::max(pca_scratch_bytes(io->r, io->c, p->pca_terms),
+    return std::max(p->mode == SHOPT_MODE_PCA ? pca_scratch_bytes(io->r, io->c, p->pca_terms) : (size_t)0,
                     polyfit_scratch_bytes((long long)io->r * io->c, io->n_local, p->degree));
 }
 
@@ -225,12 +240,18 @@ int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) {
     DevBuf dst, dpgf, dsm, dout, dint, dpoly, dtmp;
     TRY(dst.alloc(nn * rc * 8)); TRY(dpgf.alloc(nn * rc * 8)); TRY(dsm.alloc(nn * 8 * 8)); TRY(dout.alloc(nn * 6 * 8));
     TRY(dint.alloc(nn * 8)); TRY(dpoly.alloc(K * rc * 8)); TRY(dtmp.alloc(nn * 12));
+    DevBuf dw, dx0p;                                 // mode chisq only
+    const bool chisq = p->mode == SHOPT_MODE_CHISQ;
+    if (chisq && !io->weights) return SHOPT_E_BADARG;
+    if (chisq) TRY(dw.alloc(nn * rc * 8));
+    if (chisq && io->x0_pixels) TRY(dx0p.alloc(nn * rc * 8));
     cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
     double *small = dsm.as<double>();                // u | v | x0_model (3n) | x0_learned (3n)
     shopt_stage_io d = *io;
     d.stamps = dst.as<double>(); d.u = small; d.v = small + n; d.x0_model = small + 2 * n; d.x0_learned = small + 5 * n;
     d.model = dout.as<double>(); d.learned = dout.as<double>() + 3 * n; d.pgf = dpgf.as<double>();
     d.flags = dint.as<int32_t>(); d.pca_k = io->pca_k ? dint.as<int32_t>() + n : nullptr; d.poly = dpoly.as<double>();
+    d.weights = chisq ? dw.as<double>() : nullptr; d.x0_pixels = (chisq && io->x0_pixels) ? dx0p.as<double>() : nullptr;
     TRY(stage_check_args(p, &d));
     TRY(ctx->need_scratch(stage_scratch_bytes(p, &d)));
     SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[0], st));
@@ -249,6 +270,10 @@ int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) {
         if (count <= 0) break;
         SHOPT_CUDA_TRY(cudaMemcpyAsync(dst.as<double>() + first * rc, io->stamps + first * rc, (size_t)count * rc * 8,
                                        cudaMemcpyHostToDevice, cs));
+        if (chisq) SHOPT_CUDA_TRY(cudaMemcpyAsync(dw.as<double>() + first * rc, io->weights + first * rc,
+                                                  (size_t)count * rc * 8, cudaMemcpyHostToDevice, cs));
+        if (d.x0_pixels) SHOPT_CUDA_TRY(cudaMemcpyAsync(dx0p.as<double>() + first * rc, io->x0_pixels + first * rc,
+                                                        (size_t)count * rc * 8, cudaMemcpyHostToDevice, cs));
         SHOPT_CUDA_TRY(cudaEventRecord(ctx->chunk_ev[ck], cs));
         SHOPT_CUDA_TRY(cudaStreamWaitEvent(st, ctx->chunk_ev[ck], 0));
         TRY(stage_per_star(p, &d, first, count, dtmp.as<int>(), ctx, st));

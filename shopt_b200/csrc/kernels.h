@@ -28,6 +28,9 @@ size_t pca_scratch_bytes(int r, int c, int ncomp);
 int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, double pratio, int lanczos_a, int unity_sum,
                double *d_pgf, int *d_k, int *d_status, unsigned long long *d_counter, double *scratch,
                size_t scratch_bytes, cudaStream_t st);
+// element-wise pixel-grid fits: smooth mode with unity_sum (nanToZero ./ sum) and chisq mode (closed-form minimiser)
+int elem_pgf_launch(const double *d_in, const double *d_w, const double *d_x0, double fill, long long rc, long long N,
+                    int chisq, int unity, double *d_out, cudaStream_t st);
 int smooth_launch(const double *d_in, int r, int c, long long N, int lanczos_a, int nan_to_zero_flag, double *d_out,
                   cudaStream_t st);
 

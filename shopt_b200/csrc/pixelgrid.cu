@@ -768,34 +768,121 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
 struct SmoothArgs {
     const double *in;
     double *out;
-    int r, c, la, nan_to_zero;
+    long long N;
+    int r, c, la, nan_to_zero, use_smem;
     double kern[15 * 15];
+    double kz[15];
 };
-__global__ void __launch_bounds__(256) smooth_kernel(const SmoothArgs a) {
-    const long long rc = (long long)a.r * a.c;
-    const double *X = a.in + (size_t)blockIdx.x * rc;
-    double *out = a.out + (size_t)blockIdx.x * rc;
+// Persistent CTAs, grid-stride over stars.  When the stamp fits shared memory it is staged there (nanToZero applied on
+// the way); a stamp without NaN/Inf then takes the separable sliding-window path, anything else the NaN-aware
+// renormalised tap loop of the reference.  Larger stamps (301 x 301) read their taps from global memory (L1/L2).
+__global__ void __launch_bounds__(512) smooth_kernel(const SmoothArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *skern = reinterpret_cast<double *>(smem_raw);          // 225 + 15 doubles
+    double *skz = skern + 225;
+    double *R = skz + 15;
     const int r = a.r, c = a.c, la = a.la, kw = 2 * la + 1;
-    for (long long p = threadIdx.x; p < rc; p += 256) {
-        const int j = (int)(p / r), i = (int)(p - (long long)j * r);
-        double x = __ldg(X + p);
-        if (a.nan_to_zero) x = nan_to_zero(x);
-        if (isnan(x) || la <= 0) { out[p] = x; continue; }
-        const int dlo = i - la < 0 ? 0 : i - la, dhi = i + la > r - 1 ? r - 1 : i + la;
-        const int elo = j - la < 0 ? 0 : j - la, ehi = j + la > c - 1 ? c - 1 : j + la;
-        double norm = 0.0, val = 0.0;
-        for (int di = dlo; di <= dhi; di++)
-            for (int dj = elo; dj <= ehi; dj++) {
-                double d = __ldg(X + di + (size_t)dj * r);
-                if (a.nan_to_zero) d = nan_to_zero(d);
-                if (!isnan(d)) {
-                    const double kk = a.kern[(di - i + la) + (dj - j + la) * kw];
-                    val += kk * d;
-                    norm += kk;
-                }
+    const long long rc = (long long)r * c;
+    for (int t = threadIdx.x; t < 225; t += 512) skern[t] = (t < kw * kw) ? a.kern[t] : 0.0;
+    if (threadIdx.x < 15) skz[threadIdx.x] = a.kz[threadIdx.x];
+    for (long long star = blockIdx.x; star < a.N; star += gridDim.x) {
+        const double *X = a.in + star * rc;
+        double *out = a.out + star * rc;
+        __syncthreads();
+        int bad = 0;
+        if (a.use_smem) {
+            for (long long p = threadIdx.x; p < rc; p += 512) {
+                double x = __ldg(X + p);
+                if (a.nan_to_zero) x = nan_to_zero(x);
+                if (!isfinite(x)) bad = 1;
+                R[p] = x;
             }
-        out[p] = val / norm;
+            bad = __syncthreads_or(bad);
+            if (la <= 0) {
+                for (long long p = threadIdx.x; p < rc; p += 512) out[p] = R[p];
+                continue;
+            }
+            if (!bad && la == 3) { smooth_sep<3>(R, out, r, c, skz, 512); continue; }
+        }
+        const double *src = a.use_smem ? R : X;
+        const bool ntz = a.nan_to_zero && !a.use_smem;
+        for (long long p = threadIdx.x; p < rc; p += 512) {
+            const int j = (int)(p / r), i = (int)(p - (long long)j * r);
+            double x = src[p];
+            if (ntz) x = nan_to_zero(x);
+            if (isnan(x) || la <= 0) { out[p] = x; continue; }
+            const int dlo = i - la < 0 ? 0 : i - la, dhi = i + la > r - 1 ? r - 1 : i + la;
+            const int elo = j - la < 0 ? 0 : j - la, ehi = j + la > c - 1 ? c - 1 : j + la;
+            double norm = 0.0, val = 0.0;
+            for (int di = dlo; di <= dhi; di++)
+                for (int dj = elo; dj <= ehi; dj++) {
+                    double d = src[di + (size_t)dj * r];
+                    if (ntz) d = nan_to_zero(d);
+                    if (!isnan(d)) {
+                        const double kk = skern[(di - i + la) + (dj - j + la) * kw];
+                        val += kk * d;
+                        norm += kk;
+                    }
+                }
+            out[p] = val / norm;
+        }
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Pixel-grid fits that are element-wise per star (one CTA per star, grid-stride over stars):
+//   mode "smooth" with unity_sum (shopt.jl:325-331): the 1-argument smooth() call raises, so the catch branch gives
+//       nanToZero(star) ./ sum(nanToZero(star));
+//   mode "chisq" (chisq.jl:1-11, shopt.jl:194-224): LBFGS over the r c pixel values of
+//       sum(isfinite(t) ? t : 0),  t = (p - star)^2 / weight.  The objective is separable: a pixel whose term is a
+//       finite positive-definite quadratic has the unique minimiser p = star; a pixel whose term is never finite or
+//       has no curvature (weight 0, Inf or NaN, star not finite) has zero gradient and keeps its START value
+//       (rand(r*c) in the reference; an explicit input here, `fill` when no start cube is given).
+// ---------------------------------------------------------------------------------------------
+struct ElemArgs {
+    const double *in, *w, *x0;
+    double *out;
+    long long rc, N;
+    double fill;
+    int chisq, unity;
+};
+__global__ void __launch_bounds__(256) elem_pgf_kernel(const ElemArgs a) {
+    __shared__ double sred[2 * 8];
+    int buf = 0;
+    for (long long star = blockIdx.x; star < a.N; star += gridDim.x) {
+        const double *X = a.in + star * a.rc;
+        double *out = a.out + star * a.rc;
+        double part = 0.0;
+        for (long long p = threadIdx.x; p < a.rc; p += 256) {
+            double y;
+            if (a.chisq) {
+                const double d = __ldg(X + p), w = __ldg(a.w + star * a.rc + p);
+                const bool live = isfinite(d) && isfinite(w) && w > 0.0;
+                y = live ? d : (a.x0 ? __ldg(a.x0 + star * a.rc + p) : a.fill);
+            } else {
+                y = nan_to_zero(__ldg(X + p));
+            }
+            out[p] = y;
+            part += y;
+        }
+        if (a.unity) {
+            const double tot = block_sum1<8>(part, sred, buf);
+            for (long long p = threadIdx.x; p < a.rc; p += 256) out[p] = out[p] / tot;   // same thread wrote it
+        }
+    }
+}
+
+int elem_pgf_launch(const double *d_in, const double *d_w, const double *d_x0, double fill, long long rc, long long N,
+                    int chisq, int unity, double *d_out, cudaStream_t st) {
+    if (!d_in || !d_out || rc < 1 || N < 0 || (chisq && !d_w)) return SHOPT_E_BADARG;
+    if (N == 0) return SHOPT_OK;
+    ElemArgs a;
+    a.in = d_in; a.w = d_w; a.x0 = d_x0; a.out = d_out; a.rc = rc; a.N = N; a.fill = fill; a.chisq = chisq; a.unity = unity;
+    long long grid = (long long)sm_count() * 8;
+    if (grid > N) grid = N;
+    elem_pgf_kernel<<<(unsigned)grid, 256, 0, st>>>(a);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
 }
 
 // dataPreprocessing.jl:94-110: a*sinc(pi x)*sinc(pi x / a) at integer offsets, outer product, normalised by the sum
@@ -887,9 +974,20 @@ int smooth_launch(const double *d_in, int r, int c, long long N, int lanczos_a, 
     if (!d_in || !d_out || r < 1 || c < 1 || N < 0 || lanczos_a > 7) return SHOPT_E_BADARG;
     if (N == 0) return SHOPT_OK;
     SmoothArgs a;
-    a.in = d_in; a.out = d_out; a.r = r; a.c = c; a.la = lanczos_a; a.nan_to_zero = nan_to_zero_flag;
-    if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern);
-    smooth_kernel<<<(unsigned)N, 256, 0, st>>>(a);
+    a.in = d_in; a.out = d_out; a.N = N; a.r = r; a.c = c; a.la = lanczos_a; a.nan_to_zero = nan_to_zero_flag;
+    for (int i = 0; i < 225; i++) a.kern[i] = 0.0;
+    for (int i = 0; i < 15; i++) a.kz[i] = 0.0;
+    if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern, a.kz);
+    const size_t fixed = (225 + 15) * sizeof(double), stamp = (size_t)r * c * sizeof(double);
+    a.use_smem = (fixed + stamp <= 227 * 1024) ? 1 : 0;
+    const size_t smem = fixed + (a.use_smem ? stamp : 0);
+    SHOPT_CUDA_TRY(cudaFuncSetAttribute(smooth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, smooth_kernel, 512, smem));
+    if (per_sm < 1) per_sm = 1;
+    long long grid = (long long)sm_count() * per_sm;
+    if (grid > N) grid = N;
+    smooth_kernel<<<(unsigned)grid, 512, smem, st>>>(a);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }

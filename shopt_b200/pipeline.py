@@ -73,7 +73,8 @@ def make_allreduce(group=None):
     return _lib.ALLREDUCE_FN(_cb)
 
 
-def run_stage_dev(params, stamps, u, v, x0_model, x0_learned, perm, n_global=None, offset=0, group=None, pgf=None):
+def run_stage_dev(params, stamps, u, v, x0_model, x0_learned, perm, n_global=None, offset=0, group=None, pgf=None,
+                  weights=None, x0_pixels=None):
     """Device-resident shard (torch CUDA tensors, float64): stamps (n, c, r), u, v (n), x0_* (n, 3);
     perm: global permutation (host, int64).  `group`/torch.distributed initialised -> sharded run.
     Returns dict of torch tensors (model/learned (3, n), pgf, flags, pca_k, poly (K, c, r)) + host counts."""
@@ -97,7 +98,9 @@ def run_stage_dev(params, stamps, u, v, x0_model, x0_learned, perm, n_global=Non
                       x0_model=x0_model.data_ptr(), x0_learned=x0_learned.data_ptr(), n_global=n_global, offset=offset,
                       perm=perm.ctypes.data, model=out["model"].data_ptr(), learned=out["learned"].data_ptr(),
                       pgf=out["pgf"].data_ptr(), flags=out["flags"].data_ptr(), pca_k=out["pca_k"].data_ptr(),
-                      poly=out["poly"].data_ptr(), n_per_round=npr.ctypes.data)
+                      poly=out["poly"].data_ptr(), n_per_round=npr.ctypes.data,
+                      weights=weights.data_ptr() if weights is not None else None,
+                      x0_pixels=x0_pixels.data_ptr() if x0_pixels is not None else None)
     sharded = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
     cb = make_allreduce(group) if sharded else None
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -107,11 +110,13 @@ def run_stage_dev(params, stamps, u, v, x0_model, x0_learned, perm, n_global=Non
     return out
 
 
-def run_stage(params, stamps, u, v, x0_model, x0_learned, perm, want_pgf=True):
+def run_stage(params, stamps, u, v, x0_model, x0_learned, perm, want_pgf=True, weights=None, x0_pixels=None):
     """Host arrays, one GPU (H2D, stage, D2H inside the call): stamps (N, c, r), u, v (N), x0_* (N, 3), perm (N)."""
     f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
     stamps, u, v, x0_model, x0_learned = f(stamps), f(u), f(v), f(x0_model), f(x0_learned)
     perm = np.ascontiguousarray(perm, dtype=np.int64)
+    weights = None if weights is None else f(weights)
+    x0_pixels = None if x0_pixels is None else f(x0_pixels)
     N, c, r = stamps.shape
     K = num_terms(params.degree)
     out = dict(model=np.zeros((3, N)), learned=np.zeros((3, N)), pgf=np.zeros((N, c, r)) if want_pgf else None,
@@ -121,7 +126,9 @@ def run_stage(params, stamps, u, v, x0_model, x0_learned, perm, want_pgf=True):
                       x0_model=x0_model.ctypes.data, x0_learned=x0_learned.ctypes.data, n_global=N, offset=0,
                       perm=perm.ctypes.data, model=out["model"].ctypes.data, learned=out["learned"].ctypes.data,
                       pgf=out["pgf"].ctypes.data if want_pgf else None, flags=out["flags"].ctypes.data,
-                      pca_k=out["pca_k"].ctypes.data, poly=out["poly"].ctypes.data, n_per_round=npr.ctypes.data)
+                      pca_k=out["pca_k"].ctypes.data, poly=out["poly"].ctypes.data, n_per_round=npr.ctypes.data,
+                      weights=weights.ctypes.data if weights is not None else None,
+                      x0_pixels=x0_pixels.ctypes.data if x0_pixels is not None else None)
     check(_lib.lib().shopt_stage_run(C.byref(params), C.byref(io)))
     out["n_per_round"] = npr[:params.iterations].copy()
     out["counts"] = dict(zip(("blacklisted", "failed", "training", "kept"), list(io.counts)))

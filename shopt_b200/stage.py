@@ -185,3 +185,25 @@ def smooth_batch(stamps, lanczos_a=3, nan_to_zero=False):
     out = np.zeros_like(stamps)
     check(_lib.lib().shopt_smooth_batch(_ptr(stamps), r, c, N, lanczos_a, int(nan_to_zero), _ptr(out)))
     return out
+
+
+def smooth_mode_batch(stamps, lanczos_a=3, unity_sum=False):
+    """Loop body of mode "smooth" (shopt.jl:316-348): smooth(nanToZero(star), lanczos) or, with unity_sum,
+    nanToZero(star) ./ sum (the reference's 1-argument smooth() raises, so nothing is smoothed)."""
+    stamps = _f64(stamps)
+    N, c, r = stamps.shape
+    out = np.zeros_like(stamps)
+    check(_lib.lib().shopt_smooth_mode_batch(_ptr(stamps), r, c, N, lanczos_a, int(unity_sum), _ptr(out)))
+    return out
+
+
+def chisq_batch(stamps, weights, x0=None, fill=0.0, unity_sum=False):
+    """Mode "chisq" (chisq.jl:1-11, shopt.jl:194-224): the minimiser of sum(isfinite(t) ? t : 0), t = (p - star)^2 / w.
+    x0 (N, c, r): start values (the reference's rand(r*c)), kept by pixels without a finite convex term."""
+    stamps, weights = _f64(stamps), _f64(weights)
+    N, c, r = stamps.shape
+    out = np.zeros_like(stamps)
+    x0 = None if x0 is None else _f64(x0)
+    check(_lib.lib().shopt_chisq_batch(_ptr(stamps), _ptr(weights), _ptr(x0) if x0 is not None else None, float(fill),
+                                       r, c, N, int(unity_sum), _ptr(out)))
+    return out

@@ -94,3 +94,34 @@ def test_pixel_grid_pca_batch_modes(orc):
     pgf1, _, _ = orc.pixel_grid_pca_batch(st, 50, 0.99, 3, unity_sum=True)
     for i in range(3):
         assert np.isclose(pgf1[i].sum(), 1.0, rtol=1e-12)          # shopt.jl:295
+
+
+def test_chisq_mode_closed_form_is_what_lbfgs_converges_to():
+    """chisq.jl:1-11 minimised by a quasi-Newton method from a random start (scipy's L-BFGS here, Optim's in the
+    reference): pixels with a finite convex term end on the star, every other pixel keeps its start value."""
+    from scipy.optimize import minimize
+    from oracle import stage_oracle
+    rng = np.random.default_rng(2)
+    r = 6
+    star = rng.normal(size=(r, r)) + 1.0
+    w = rng.uniform(0.5, 2.0, size=(r, r))
+    star[1, 2] = np.nan
+    w[0, 0], w[3, 3], w[4, 1] = 0.0, np.inf, np.nan
+    x0 = rng.uniform(size=r * r)
+
+    def cost(p):
+        with np.errstate(divide="ignore", invalid="ignore"):
+            t = (p - star.ravel()) ** 2 / w.ravel()
+        return np.where(np.isfinite(t), t, 0.0).sum()
+
+    def grad(p):
+        with np.errstate(divide="ignore", invalid="ignore"):
+            t = (p - star.ravel()) ** 2 / w.ravel()
+            g = 2.0 * (p - star.ravel()) / w.ravel()
+        return np.where(np.isfinite(t) & np.isfinite(g), g, 0.0)
+
+    res = minimize(cost, x0, jac=grad, method="L-BFGS-B", options=dict(gtol=1e-12, ftol=1e-30, maxiter=500))
+    want = stage_oracle.pixel_grid_elementwise(2, star[None], 3, False, w[None], x0.reshape(1, r, r))[0]
+    assert np.allclose(res.x.reshape(r, r), want, atol=1e-9)
+    dead = ~(np.isfinite(star) & np.isfinite(w) & (w > 0))
+    assert dead.sum() == 4 and np.array_equal(want[dead], x0.reshape(r, r)[dead])
