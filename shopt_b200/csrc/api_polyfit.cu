@@ -81,14 +81,14 @@ int shopt_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, c
     if (!pgf || !u || !v || !poly_out || r < 1 || c < 1 || N < 0 || n_train < 0 || (n_train > 0 && !train_idx))
         return SHOPT_E_BADARG;
     if (degree < 0 || degree > 8 || iterations < 0) return SHOPT_E_BADARG;
-    if (median_constraint) return SHOPT_E_UNSUPPORTED;
     for (int64_t t = 0; t < n_train; t++) if (train_idx[t] < 0 || train_idx[t] >= N) return SHOPT_E_BADARG;
     Ctx *ctx; TRY(get_ctx(&ctx));
     const long long rc = (long long)r * c;
     const int K = (degree + 1) * (degree + 2) / 2;
     const size_t n0 = (size_t)n_train;
     // only the training stars travel to the device, compacted in training order
-    DevBuf dpgf, du, dv, didx, dacc, dpoly, dmse, dinfo;
+    DevBuf dpgf, du, dv, didx, dacc, dpoly, dmse, dinfo, dmed;
+    if (median_constraint) TRY(dmed.alloc((size_t)rc * 8));
     TRY(dpgf.alloc(std::max<size_t>(n0, 1) * rc * 8)); TRY(du.alloc(n0 * 8)); TRY(dv.alloc(n0 * 8)); TRY(didx.alloc(n0 * 8));
     TRY(dacc.alloc((size_t)shopt_polyfit_acc_len(r, c, degree) * 8)); TRY(dpoly.alloc((size_t)K * rc * 8));
     TRY(dmse.alloc(n0 * 8)); TRY(dinfo.alloc(16));
@@ -120,7 +120,15 @@ int shopt_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, c
         } else {
             TRY(polyfit_normal_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), idx, n, degree,
                                       dacc.as<double>(), (double *)ctx->scratch, ctx->scratch_bytes, st));
+            if (!median_constraint)            // NaN values -> median before the solve (interpolate.jl:126-130)
+                TRY(polyfit_median_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), idx, n, degree, 2,
+                                          dacc.as<double>(), nullptr, st));
             TRY(polyfit_solve_launch(dacc.as<double>(), rc, degree, dpoly.as<double>(), dinfo.as<int>(), st));
+            if (median_constraint) {           // interpolate.jl:118-124, 139-141
+                TRY(polyfit_median_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), idx, n, degree, 1,
+                                          nullptr, dmed.as<double>(), st));
+                TRY(polyfit_set_coef0_launch(dmed.as<double>(), rc, dpoly.as<double>(), st));
+            }
         }
         TRY(polyfit_mse_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), idx, n, degree, dpoly.as<double>(),
                                dmse.as<double>(), (double *)ctx->scratch, ctx->scratch_bytes, st));

@@ -91,7 +91,6 @@ static int stage_check_args(const shopt_params *p, const shopt_stage_io *io) {
     const long long n = io->n_local, NG = io->n_global, off = io->offset;
     if (r < 1 || c < 2 || n < 0 || NG < n || off < 0 || off + n > NG || (NG > 0 && !io->perm)) return SHOPT_E_BADARG;
     if (p->degree < 0 || p->degree > 8 || p->iterations < 0 || p->n_a < 1 || p->n_a > r || p->n_a > c) return SHOPT_E_BADARG;
-    if (p->median_constraint) return SHOPT_E_UNSUPPORTED;
     if (p->mode < SHOPT_MODE_PCA || p->mode > SHOPT_MODE_CHISQ) return SHOPT_E_BADARG;
     if (p->mode == SHOPT_MODE_CHISQ && !io->weights) return SHOPT_E_BADARG;
     if (p->mode == SHOPT_MODE_SMOOTH && p->lanczos > 7) return SHOPT_E_BADARG;
@@ -113,7 +112,9 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
     const long long rc = (long long)r * c;
     const int K = (p->degree + 1) * (p->degree + 2) / 2;
     const size_t nn = (size_t)std::max<long long>(n, 1);
-    DevBuf dacc, didx, dmse, dkeep, dinfo;
+    DevBuf dacc, didx, dmse, dkeep, dinfo, dmed;
+    if (p->median_constraint && comm) return SHOPT_E_UNSUPPORTED;
+    if (p->median_constraint) TRY(dmed.alloc((size_t)rc * 8));
     int *d_pst = d_tmp + 2 * nn;
     double *m = io->model, *l = io->learned;
     // ---- model fit, pixel-grid fit, learned fit (every star of the shard; flags decide who counts) ----
@@ -179,7 +180,17 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
             if (comm && comm(dacc.p, acc_len, 0, stream, comm_user) != 0) {
                 set_last_error_text("all-reduce callback failed"); return SHOPT_E_CUDA;
             }
+            // per-pixel medians over the training stars (median_constraint; NaN pixel-grid values) are selected on one
+            // GPU; a sharded run would need a histogram exchange per radix pass and is refused above
+            if (!comm && !p->median_constraint)
+                TRY(polyfit_median_launch(io->pgf, rc, io->u, io->v, didx.as<long long>(), nl, p->degree, 2,
+                                          dacc.as<double>(), nullptr, st));
             TRY(polyfit_solve_launch(dacc.as<double>(), rc, p->degree, io->poly, dinfo.as<int>(), st));
+            if (p->median_constraint) {
+                TRY(polyfit_median_launch(io->pgf, rc, io->u, io->v, didx.as<long long>(), nl, p->degree, 1, nullptr,
+                                          dmed.as<double>(), st));
+                TRY(polyfit_set_coef0_launch(dmed.as<double>(), rc, io->poly, st));
+            }
         }
         TRY(polyfit_mse_launch(io->pgf, rc, io->u, io->v, didx.as<long long>(), nl, p->degree, io->poly, dmse.as<double>(),
                                (double *)ctx->scratch, ctx->scratch_bytes, st));

@@ -18,6 +18,11 @@ int polyfit_solve_launch(const double *acc, long long rc, int degree, double *po
 int polyfit_mse_launch(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
                        long long n, int degree, const double *poly, double *mse, double *scratch, size_t scratch_bytes,
                        cudaStream_t st);
+// per-pixel median over the listed stars: mode 1 -> med[rc] (median_constraint); mode 2 -> re-accumulate V'P in `acc`
+// for the pixels whose sums are NaN, with NaN values replaced by the median (interpolate.jl:126-130)
+int polyfit_median_launch(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+                          long long n, int degree, int mode, double *acc, double *med, cudaStream_t st);
+int polyfit_set_coef0_launch(const double *med, long long rc, double *poly, cudaStream_t st);
 int psf_at_launch(const double *poly, long long rc, int degree, const double *u, const double *v, long long M,
                   double *out, cudaStream_t st);
 int small_median_launch(const double *pgf, long long rc, const long long *idx, int n, int degree, double *poly,

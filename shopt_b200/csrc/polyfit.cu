@@ -351,6 +351,156 @@ __global__ void small_median_kernel(const double *__restrict__ pgf, long long rc
     for (int k = 1; k < K; k++) poly[px + (size_t)k * rc] = 0.0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Per-pixel median over the training stars, median(filter(!isnan, z)) of interpolate.jl:119,128,140 -- the two places
+// the reference needs it at full training-set size:
+//   mode 1  median_constraint = true: coefficient 1 of every pixel is replaced by the median (:139-141).  With the
+//           first design column set to the constant m (:119) the least-squares solution is the standard one with
+//           coefficient 1 divided by m, so the other coefficients are those of the unconstrained fit (m != 0).
+//   mode 2  median_constraint = false and a pixel has NaN values (:126-130): the NaNs are replaced by the median
+//           before the solve.  Only pixels whose accumulated V'P is NaN are touched: their median is selected and
+//           their column of V'P is re-accumulated with the replacement, in place in `acc`.
+// Selection: MSB-first radix select on the order-preserving 64-bit key, 8 bits per pass, histograms in shared memory
+// (256 bins x 64 pixels), 64 pixels x 8 star lanes per CTA; coalesced 8-byte loads along the pixels.  Integer
+// arithmetic only, so the result is exact and deterministic.  An even count takes Statistics.middle = a/2 + b/2.
+// ---------------------------------------------------------------------------------------------
+constexpr int MED_PX = 64, MED_LANES = 8, MED_THREADS = MED_PX * MED_LANES;
+__device__ __forceinline__ unsigned long long order_key(double z) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(z);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ double key_value(unsigned long long k) {
+    const unsigned long long b = (k >> 63) ? (k & 0x7fffffffffffffffULL) : ~k;
+    return __longlong_as_double((long long)b);
+}
+template <int DEG>
+__global__ void __launch_bounds__(MED_THREADS) median_fix_kernel(const double *__restrict__ pgf, long long rc,
+                                                                 const double *__restrict__ u, const double *__restrict__ v,
+                                                                 const long long *__restrict__ idx, long long n, int mode,
+                                                                 double *__restrict__ acc, double *__restrict__ med_out) {
+    constexpr int K = PolyCfg<DEG>::K;
+    extern __shared__ __align__(16) unsigned char med_smem[];
+    unsigned int *hist = reinterpret_cast<unsigned int *>(med_smem);            // [256][MED_PX]
+    __shared__ unsigned long long s_prefix[MED_PX], s_next[MED_PX];
+    __shared__ unsigned int s_k[MED_PX], s_nvalid[MED_PX], s_cnt[MED_PX];
+    __shared__ double s_med[MED_PX];
+    __shared__ int s_need[MED_PX];
+    const int pl = threadIdx.x % MED_PX, lane = threadIdx.x / MED_PX;
+    const long long px = (long long)blockIdx.x * MED_PX + pl;
+    if (lane == 0) {
+        int need = px < rc;
+        if (need && mode == 2) need = isnan(acc[(size_t)K * K + px]);          // V'P of the constant term: NaN iff z has one
+        s_need[pl] = need; s_prefix[pl] = 0ULL; s_k[pl] = 0u; s_nvalid[pl] = 0u; s_cnt[pl] = 0u;
+        s_next[pl] = ~0ULL; s_med[pl] = nan("");
+    }
+    __syncthreads();
+    {
+        int any = 0;
+        for (int i = 0; i < MED_PX; i++) any |= s_need[i];
+        if (!any) return;
+    }
+    for (int pass = 0; pass < 8; pass++) {
+        const int shift = 56 - 8 * pass;
+        for (int e = threadIdx.x; e < 256 * MED_PX; e += MED_THREADS) hist[e] = 0u;
+        __syncthreads();
+        if (s_need[pl]) {
+            const unsigned long long prefix = s_prefix[pl];
+            for (long long t = lane; t < n; t += MED_LANES) {
+                const long long star = idx ? idx[t] : t;
+                const double z = __ldg(pgf + star * rc + px);
+                if (isnan(z)) continue;
+                const unsigned long long key = order_key(z);
+                if (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8)))
+                    atomicAdd(&hist[(unsigned)((key >> shift) & 255ULL) * MED_PX + pl], 1u);
+            }
+        }
+        __syncthreads();
+        if (lane == 0 && s_need[pl]) {
+            unsigned int k = s_k[pl];
+            if (pass == 0) {
+                unsigned int total = 0;
+                for (int b = 0; b < 256; b++) total += hist[b * MED_PX + pl];
+                s_nvalid[pl] = total;
+                k = total ? (total - 1) / 2 : 0;
+                if (!total) s_need[pl] = (mode == 2) ? 2 : 0;     // no finite value at all: median is NaN
+            }
+            unsigned int cum = 0;
+            for (int b = 0; b < 256; b++) {
+                const unsigned int h = hist[b * MED_PX + pl];
+                if (cum + h > k) { s_prefix[pl] |= (unsigned long long)b << shift; k -= cum; break; }
+                cum += h;
+            }
+            s_k[pl] = k;
+        }
+        __syncthreads();
+    }
+    // even count: the upper middle value is v1 again when enough copies of it exist, else the smallest value above it
+    const bool sel = s_need[pl] == 1;
+    if (sel && (s_nvalid[pl] & 1u) == 0u) {
+        const unsigned long long k1 = s_prefix[pl];
+        unsigned int cnt = 0;
+        unsigned long long nxt = ~0ULL;
+        for (long long t = lane; t < n; t += MED_LANES) {
+            const long long star = idx ? idx[t] : t;
+            const double z = __ldg(pgf + star * rc + px);
+            if (isnan(z)) continue;
+            const unsigned long long key = order_key(z);
+            if (key <= k1) cnt++;
+            else if (key < nxt) nxt = key;
+        }
+        atomicAdd(&s_cnt[pl], cnt);
+        atomicMin(&s_next[pl], nxt);
+    }
+    __syncthreads();
+    if (lane == 0 && sel) {
+        const double v1 = key_value(s_prefix[pl]);
+        double m = v1;
+        if ((s_nvalid[pl] & 1u) == 0u) {
+            const double v2 = (s_cnt[pl] >= s_nvalid[pl] / 2 + 1) ? v1 : key_value(s_next[pl]);
+            m = v1 / 2 + v2 / 2;
+        }
+        s_med[pl] = m;
+    }
+    __syncthreads();
+    if (mode == 1) {
+        if (lane == 0 && px < rc) med_out[px] = s_med[pl];
+        return;
+    }
+    // mode 2: V'P of the flagged pixels with NaN -> median
+    double a[K];
+#pragma unroll
+    for (int k = 0; k < K; k++) a[k] = 0.0;
+    const bool fix = s_need[pl] != 0;
+    if (fix) {
+        const double m = s_med[pl];
+        for (long long t = lane; t < n; t += MED_LANES) {
+            const long long star = idx ? idx[t] : t;
+            double z = __ldg(pgf + star * rc + px);
+            if (isnan(z)) z = m;
+            double b[K];
+            basis_eval<DEG>(u[star], v[star], b);
+#pragma unroll
+            for (int k = 0; k < K; k++) a[k] = fma(b[k], z, a[k]);
+        }
+    }
+    double *red = reinterpret_cast<double *>(med_smem);                         // [MED_LANES][MED_PX]
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        __syncthreads();
+        red[lane * MED_PX + pl] = a[k];
+        __syncthreads();
+        if (lane == 0 && fix) {
+            double sum = red[pl];
+            for (int l = 1; l < MED_LANES; l++) sum += red[l * MED_PX + pl];
+            acc[(size_t)K * K + (size_t)k * rc + px] = sum;
+        }
+    }
+}
+__global__ void set_coef0_kernel(const double *__restrict__ med, long long rc, double *__restrict__ poly) {
+    const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (px < rc) poly[px] = med[px];
+}
+
 // ---- launch -----------------------------------------------------------------------------------
 static int pick_chunks(long long n, int tiles) {
     long long want = ((long long)sm_count() * 16 + tiles - 1) / tiles;
@@ -459,6 +609,30 @@ int psf_at_launch(const double *poly, long long rc, int degree, const double *u,
 int small_median_launch(const double *pgf, long long rc, const long long *idx, int n, int degree, double *poly,
                         cudaStream_t st) {
     small_median_kernel<<<(unsigned)((rc + 127) / 128), 128, 0, st>>>(pgf, rc, idx, n, num_terms(degree), poly);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+
+template <int DEG>
+static int median_launch_t(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+                           long long n, int mode, double *acc, double *med, cudaStream_t st) {
+    if (n == 0) return SHOPT_OK;
+    const size_t smem = (size_t)256 * MED_PX * sizeof(unsigned int);
+    auto kern = median_fix_kernel<DEG>;
+    SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)((rc + MED_PX - 1) / MED_PX), MED_THREADS, smem, st>>>(pgf, rc, u, v, idx, n, mode, acc, med);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+int polyfit_median_launch(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+                          long long n, int degree, int mode, double *acc, double *med, cudaStream_t st) {
+    if ((mode == 1 && !med) || (mode == 2 && !acc) || mode < 1 || mode > 2) return SHOPT_E_BADARG;
+#define CALL(D) median_launch_t<D>(pgf, rc, u, v, idx, n, mode, acc, med, st)
+    DEG_SWITCH(degree, CALL)
+#undef CALL
+}
+int polyfit_set_coef0_launch(const double *med, long long rc, double *poly, cudaStream_t st) {
+    set_coef0_kernel<<<(unsigned)((rc + 255) / 256), 256, 0, st>>>(med, rc, poly);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }

@@ -88,3 +88,20 @@ def test_stage_in_elementwise_modes(orc, mode, unity):
     assert peak_close(got["pgf"], want["pgf"], 1e-12)
     if mode == _lib.MODE_CHISQ:
         assert got["pgf"][5, 20, 20] == x0p[5, 20, 20]
+
+
+def test_stage_with_median_constraint(orc):
+    from oracle import stage_oracle
+    from shopt_b200 import pipeline
+    from test_gpu_stage import check_against_oracle
+    N, r, n_a = 200, 33, 32
+    cat = synth.make_catalog(N, r, n_a)
+    a = {k: cat[k].numpy() for k in ("stamps", "u", "v", "x0_model", "x0_learned", "perm")}
+    p = pipeline.default_params(n_a=n_a, degree=2, iterations=2, training_ratio=0.8, median_constraint=1)
+    got = pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], a["perm"])
+    want = stage_oracle.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], a["perm"],
+                                  nthreads=orc.max_threads())
+    check_against_oracle(got, want, a["x0_model"], a["x0_learned"], strict_poly=False)
+    # coefficient 1 is the per-pixel median of pixel-grid fits that agree to ~1e-15: compare against the peak
+    scale = np.abs(want["poly"]).max(axis=(1, 2), keepdims=True)
+    assert np.max(np.abs(got["poly"] - want["poly"]) / scale) <= 1e-6

@@ -107,3 +107,37 @@ def test_building_blocks_shard_additively(stage):
     parts = acc_of(idx[:300]) + acc_of(idx[300:450]) + acc_of(idx[450:])
     assert torch.allclose(whole, parts, rtol=1e-12, atol=1e-12)
     assert torch.equal(acc_of(idx), whole)                            # deterministic: no floating-point atomics
+
+
+@pytest.mark.parametrize("degree,N,r,c", [(1, 301, 9, 7), (3, 500, 13, 13), (2, 1000, 21, 19)])
+def test_median_constraint(stage, orc, degree, N, r, c):
+    """interpolate.jl:118-124, 139-141: coefficient 1 = per-pixel median over the training stars (radix select on the
+    device); odd and even training-set sizes, ties."""
+    pgf, u, v, train, _ = make_case(degree * 5 + N, N, r, c, degree)
+    pgf[:, 0, 0] = np.round(pgf[:, 0, 0], 1)                        # many exact ties in one pixel
+    pgf[:, 1, 1] = -np.abs(pgf[:, 1, 1])                            # negative values exercise the key ordering
+    pgf[::2, 2, 2] *= -1.0                                           # mixed signs
+    got = stage.polyfit(pgf, u, v, train, degree, 3, median_constraint=True)
+    want = orc.polyfit(pgf, u, v, train, degree, 3, median_constraint=True, nthreads=orc.max_threads())
+    assert got["n_per_round"].tolist() == want["n_per_round"].tolist()
+    assert got["kept"].tolist() == want["kept"].tolist()
+    assert np.array_equal(got["poly"][0], want["poly"][0])          # the median itself is exact
+    assert coef_close(got["poly"], want["poly"])
+    assert np.allclose(got["mse"], want["mse"], rtol=1e-9)
+
+
+def test_nan_pixel_grid_values_are_replaced_by_the_median(stage, orc):
+    """interpolate.jl:126-130 (median_constraint = false): NaN values of a pixel become the median of its finite
+    values before the solve; the stars keep their NaNs, so their reconstruction error is NaN and they sort first."""
+    pgf, u, v, train, _ = make_case(3, 400, 9, 8, 2, n_out=0)
+    rng = np.random.default_rng(1)
+    for _ in range(25):
+        pgf[rng.integers(400), rng.integers(8), rng.integers(9)] = np.nan
+    pgf[train[:7], 3, 4] = np.nan
+    got = stage.polyfit(pgf, u, v, train, 2, 2)
+    want = orc.polyfit(pgf.copy(), u, v, train, 2, 2, nthreads=orc.max_threads())
+    assert got["n_per_round"].tolist() == want["n_per_round"].tolist()
+    assert got["kept"].tolist() == want["kept"].tolist()
+    assert np.all(np.isfinite(got["poly"])) and coef_close(got["poly"], want["poly"])
+    assert np.array_equal(np.isnan(got["mse"]), np.isnan(want["mse"]))
+    assert np.allclose(got["mse"], want["mse"], rtol=1e-9, equal_nan=True)
