@@ -167,6 +167,19 @@ int shopt_psf_at_batch(const double *poly, int r, int c, int degree, const doubl
 int shopt_psf_at_batch_dev(const double *d_poly, int r, int c, int degree, const double *d_u,
                            const double *d_v, int64_t M, double *d_stars_out, void *stream);
 
+/* ---- s(u,v), g1(u,v), g2(u,v) across the field of view --------------------------------------------
+ * Replaces interpolate.jl:7-87 and the three optimize(interpCost*, polyG_*!, rand(10), LBFGS()) calls of
+ * shopt.jl:422-466.  The cost  sum_i (I_p(u_i, v_i) - t_i)^2  with
+ *   I_p(u,v) = p1 u^3 + p2 v^3 + p3 u^2 v + p4 v^2 u + p5 u^2 + p6 v^2 + p7 u v + p8 u + p9 v + p10
+ * is a convex quadratic, so LBFGS's limit from any start is the least-squares solution; it is computed directly
+ * (Householder QR, host code, one factorisation for all `nvalues` right-hand sides).
+ *   values[j] (n): e.g. {s_data, g1_data, g2_data};  coef (10, nvalues): coef[10 j + k], the reference's order.
+ * Returns the numerical rank of the design matrix (10 = full; dependent coefficients are set to 0) or SHOPT_E_*. */
+int shopt_field_interp(const double *u, const double *v, const double *const *values, int nvalues, int64_t n,
+                       double *coef);
+/* s(u,v) etc. of shopt.jl:437 at n positions (host). */
+int shopt_field_eval(const double *coef, const double *u, const double *v, int64_t n, double *out);
+
 /* ---- the whole stage: what shopt.jl's loops :130-184, :281-314, :357-417, :472-577 become ---------
  * model fit -> s-blacklist -> PCA pixel-grid fit -> learned fit -> failed list -> training split -> polyfit rounds.
  * Parameters mirror shopt.yml (shopt_params).  Stars keep their ORIGINAL indices: instead of splicing arrays like the
@@ -231,6 +244,10 @@ typedef struct shopt_stage_io {
     /* inputs of mode chisq only (same residence as stamps); may be NULL otherwise */
     const double *weights;       /* (r, c, n_local) errVignets                                    */
     const double *x0_pixels;     /* (r, c, n_local) start values (the reference's rand(r*c)); NULL -> chisq_fill */
+    /* output, replicated: cubic s(u,v), g1(u,v), g2(u,v) over the surviving stars' learned fits (shopt.jl:422-466),
+     * field[10 j + k], j = s, g1, g2, the reference's coefficient order (see shopt_field_interp); HOST */
+    double field[30];
+    int32_t field_rank;          /* numerical rank of the cubic design matrix (10 = full)          */
 } shopt_stage_io;
 
 /* Host logic of the split, exposed for sharded hosts and tests (shopt.jl:472-478): flags (n_global) = SHOPT_FLAG_* of

@@ -12,6 +12,13 @@ from . import shopt_oracle as orc
 FLAG_BLACKLISTED, FLAG_PCA_FAILED, FLAG_LEARNED_OOB, FLAG_TRAINING, FLAG_REJECTED = 1, 2, 4, 8, 16
 
 
+def field_interp(u, v, *values):
+    """interpolate.jl:7-87: the minimiser of sum (I_p(u,v) - t)^2 over the 10 cubic coefficients, term order
+    [u^3, v^3, u^2 v, v^2 u, u^2, v^2, u v, u, v, 1] (numpy lstsq: SVD-based, independent of the product's QR)."""
+    A = np.stack([u ** 3, v ** 3, u * u * v, v * v * u, u * u, v * v, u * v, u, v, np.ones_like(u)], axis=1)
+    return np.stack([np.linalg.lstsq(A, t, rcond=None)[0] for t in values])
+
+
 def pixel_grid_elementwise(mode, stamps, lanczos, unity_sum, weights=None, x0_pixels=None, fill=0.0):
     """mode 1 = "smooth" (shopt.jl:316-348), mode 2 = "chisq" (shopt.jl:194-224 with chisq.jl:1-11; the minimiser of
     the separable objective: star where the term is a finite convex quadratic, the start value elsewhere)."""
@@ -49,6 +56,7 @@ def run_stage(p, stamps, u, v, x0_model, x0_learned, perm, nthreads=1, fit_only=
     sl, g1l, g2l, _, _ = orc.fit_analytic_batch(pgf, p.n_a, x0_learned, p.g_tol_learned, p.max_iter, nthreads)
     flags[(sl < p.s_lo) | (sl > p.s_hi)] |= FLAG_LEARNED_OOB                        # shopt.jl:384-386
     surv = flags == 0
+    field = field_interp(u[surv], v[surv], sl[surv], g1l[surv], g2l[surv])        # shopt.jl:422-466
     n_train = int(np.rint(p.training_ratio * surv.sum()))                            # round(Int, .): half to even
     train = np.array([g for g in perm if surv[g]][:n_train], dtype=np.int64)
     flags[train] |= FLAG_TRAINING
@@ -58,6 +66,6 @@ def run_stage(p, stamps, u, v, x0_model, x0_learned, perm, nthreads=1, fit_only=
     black = (flags & FLAG_BLACKLISTED) != 0
     failed = ~black & ((flags & (FLAG_PCA_FAILED | FLAG_LEARNED_OOB)) != 0)
     return dict(model=model, learned=np.stack([sl, g1l, g2l]), pgf=pgf, flags=flags, pca_k=k, poly=res["poly"],
-                n_per_round=res["n_per_round"][:p.iterations],
+                n_per_round=res["n_per_round"][:p.iterations], field=field,
                 counts=dict(blacklisted=int(black.sum()), failed=int(failed.sum()), training=len(train),
                             kept=len(res["kept"])))

@@ -44,7 +44,8 @@ class StageIO(C.Structure):
     _fields_ = [("stamps", vp), ("r", C.c_int), ("c", C.c_int), ("n_local", C.c_int64), ("u", vp), ("v", vp),
                 ("x0_model", vp), ("x0_learned", vp), ("n_global", C.c_int64), ("offset", C.c_int64), ("perm", vp),
                 ("model", vp), ("learned", vp), ("pgf", vp), ("flags", vp), ("pca_k", vp), ("poly", vp),
-                ("n_per_round", vp), ("counts", C.c_int64 * 4), ("weights", vp), ("x0_pixels", vp)]
+                ("n_per_round", vp), ("counts", C.c_int64 * 4), ("weights", vp), ("x0_pixels", vp),
+                ("field", C.c_double * 30), ("field_rank", C.c_int32)]
 
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p)
@@ -74,6 +75,8 @@ SIGNATURES = {
     "shopt_smooth_mode_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, vp, vp]),
     "shopt_chisq_batch": (C.c_int, [dp, dp, dp, C.c_double, C.c_int, C.c_int, C.c_int64, C.c_int, dp]),
     "shopt_chisq_batch_dev": (C.c_int, [vp, vp, vp, C.c_double, C.c_int, C.c_int, C.c_int64, C.c_int, vp, vp]),
+    "shopt_field_interp": (C.c_int, [dp, dp, C.POINTER(dp), C.c_int, C.c_int64, dp]),
+    "shopt_field_eval": (C.c_int, [dp, dp, dp, C.c_int64, dp]),
     "shopt_polyfit": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, dp, dp, lp, C.c_int64, C.c_int, C.c_int, C.c_int,
                                 C.c_int, dp, dp, lp, lp, lp]),
     "shopt_polyfit_acc_len": (C.c_int64, [C.c_int, C.c_int, C.c_int]),

@@ -61,14 +61,22 @@ int64_t shopt_worst_10_percent(const double *err, int64_t n, int sigma_clip, int
         for (int64_t i = 0; i < n; i++) if (err[i] > thr) idx_out[m++] = i;
         return m;
     }
+    // The stable descending sort keeps ties in index order, i.e. it sorts by the TOTAL order (error descending with NaN
+    // first, index ascending); its first m entries are therefore the m smallest under that order: select, then sort m.
     std::vector<int64_t> order((size_t)n);
     std::iota(order.begin(), order.end(), (int64_t)0);
-    std::stable_sort(order.begin(), order.end(), [err](int64_t a, int64_t b) {
-        const double x = err[a], y = err[b];          // "a before b" <=> isless(y, x)
-        if (std::isnan(y)) return false;
-        if (std::isnan(x)) return true;
-        return y < x;
-    });
+    auto before = [err](int64_t a, int64_t b) {
+        const double x = err[a], y = err[b];          // "a before b" <=> isless(y, x), ties by index
+        const bool nx = std::isnan(x), ny = std::isnan(y);
+        if (nx || ny) return (nx && ny) ? a < b : nx;
+        if (x != y) return y < x;
+        return a < b;
+    };
+    {
+        const int64_t m = (int64_t)std::ceil(0.10 * (double)n);
+        if (m < n) std::nth_element(order.begin(), order.begin() + m, order.end(), before);
+        std::sort(order.begin(), order.begin() + m, before);
+    }
     const int64_t m = (int64_t)std::ceil(0.10 * (double)n);
     for (int64_t i = 0; i < m; i++) idx_out[i] = order[(size_t)i];
     return m;

@@ -24,6 +24,44 @@ __global__ void flag_kernel(const double *__restrict__ s_model, const int *__res
     flags[i] = f;
 }
 
+
+// Normal equations of the cubic field fit (shopt.jl:422-466) over the surviving stars of a shard:
+// part[block][0..100) = T'T, [100..130) = T'[s g1 g2], T = the reference's ten terms.  Fixed-order sums: deterministic.
+constexpr int FIELD_LEN = 130, FIELD_CHUNK = 128;
+__global__ void __launch_bounds__(160) field_normal_kernel(const double *__restrict__ u, const double *__restrict__ v,
+                                                           const double *__restrict__ learned, const int *__restrict__ flags,
+                                                           long long n, long long per_block, double *__restrict__ part) {
+    __shared__ double st[FIELD_CHUNK][13];
+    const long long t0 = (long long)blockIdx.x * per_block, t1 = (t0 + per_block < n) ? t0 + per_block : n;
+    const int e = threadIdx.x;
+    const int i = (e < 100) ? e / 10 : (e - 100) % 10, j = (e < 100) ? e % 10 : 10 + (e - 100) / 10;
+    double acc = 0.0;
+    for (long long base = t0; base < t1; base += FIELD_CHUNK) {
+        const int m = (int)((t1 - base < FIELD_CHUNK) ? (t1 - base) : FIELD_CHUNK);
+        __syncthreads();
+        if (e < m) {
+            const long long g = base + e;
+            const bool live = (flags[g] & 7) == 0;
+            const double uu = u[g], vv = v[g];
+            const double t[13] = {uu * uu * uu, vv * vv * vv, uu * uu * vv, vv * vv * uu, uu * uu, vv * vv, uu * vv, uu, vv, 1.0,
+                                  learned[g], learned[n + g], learned[2 * n + g]};
+#pragma unroll
+            for (int k = 0; k < 13; k++) st[e][k] = live ? t[k] : 0.0;
+        }
+        __syncthreads();
+        if (e < FIELD_LEN)
+            for (int s = 0; s < m; s++) acc = fma(st[s][i], st[s][j], acc);
+    }
+    if (e < FIELD_LEN) part[(size_t)blockIdx.x * FIELD_LEN + e] = acc;
+}
+__global__ void field_reduce_kernel(const double *__restrict__ part, int nblocks, double *__restrict__ out) {
+    const int e = threadIdx.x;
+    if (e >= FIELD_LEN) return;
+    double s = 0.0;
+    for (int b = 0; b < nblocks; b++) s += part[(size_t)b * FIELD_LEN + e];
+    out[e] = s;
+}
+
 }  // namespace shopt
 
 using namespace shopt;
@@ -141,6 +179,23 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
         if (f & SHOPT_FLAG_BLACKLISTED) n_black++;
         else if (f & (SHOPT_FLAG_PCA_FAILED | SHOPT_FLAG_LEARNED_OOB)) n_failed++;
         else n_surv++;
+    }
+    // ---- s(u,v), g1(u,v), g2(u,v) over the survivors' learned fits (shopt.jl:422-466): normal equations of the cubic
+    //      accumulated on the device (additive over shards -> one 130-double all-reduce), solved on the host ----
+    {
+        DevBuf dfield;
+        const int nb = (int)std::min<long long>(64, std::max<long long>(1, (n + FIELD_CHUNK - 1) / FIELD_CHUNK));
+        TRY(dfield.alloc((size_t)(nb + 1) * FIELD_LEN * 8));
+        double *d_part = dfield.as<double>() + FIELD_LEN, *d_sum = dfield.as<double>();
+        const long long per_block = (n + nb - 1) / nb;
+        field_normal_kernel<<<nb, 160, 0, st>>>(io->u, io->v, l, io->flags, n, per_block, d_part);
+        field_reduce_kernel<<<1, 160, 0, st>>>(d_part, nb, d_sum);
+        SHOPT_CUDA_TRY(cudaGetLastError());
+        if (comm && comm(d_sum, FIELD_LEN, 0, stream, comm_user) != 0) { set_last_error_text("all-reduce callback failed"); return SHOPT_E_CUDA; }
+        double h[FIELD_LEN];
+        SHOPT_CUDA_TRY(cudaMemcpyAsync(h, d_sum, sizeof h, cudaMemcpyDeviceToHost, st));
+        SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+        io->field_rank = field_solve_normal(h, h + 100, 3, io->field);
     }
     // ---- training split: first round(training_ratio * n_surv) survivors in perm order (shopt.jl:472-478) ----
     for (auto &f : gflag) f &= 31;
@@ -300,6 +355,8 @@ int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) {
     SHOPT_CUDA_TRY(cudaMemcpyAsync(io->poly, d.poly, K * rc * 8, cudaMemcpyDeviceToHost, st));
     SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[3], st));
     for (int i = 0; i < 4; i++) io->counts[i] = d.counts[i];
+    for (int i = 0; i < 30; i++) io->field[i] = d.field[i];
+    io->field_rank = d.field_rank;
     return finish_timing(ctx);
 }
 

@@ -1,8 +1,14 @@
 // kernels.h -- internal launch functions (one per .cu); all enqueue on `stream` and return SHOPT_* codes.
 #pragma once
 #include <cuda_runtime.h>
+#include <vector>
 
 namespace shopt {
+
+// api_field.cu (host): min |A x - b_j|, A n x 10 column-major, B n x nrhs; both overwritten; returns the rank
+int field_lstsq(std::vector<double> &A, std::vector<double> &B, long long n, int nrhs, double *coef);
+// the same from the normal equations (G 10 x 10, b [nrhs][10]); pivoted Cholesky; returns the rank
+int field_solve_normal(const double *G, const double *b, int nrhs, double *coef);
 
 // lbfgs_fit.cu
 int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n_a, const double *d_x0, double g_tol,

@@ -173,8 +173,9 @@ constexpr int ES_BYTES = (sizeof(EvalShared) + 15) & ~15;
 
 // Barrier of one evaluation (id 1; the star loop uses __syncthreads = id 0).  The master warp and the worker warps
 // arrive from different code, which named barriers allow as long as every warp of the CTA arrives.
+// THREADS counts the WORKER threads (warps 0 .. THREADS/32 - 1); the master warp is the extra, last warp of the CTA.
 template <int THREADS>
-__device__ __forceinline__ void bar_eval() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }
+__device__ __forceinline__ void bar_eval() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS + 32) : "memory"); }
 
 // Deterministic warp sums with a fixed tree that halves the number of live values at each step instead of carrying
 // every value through five butterflies: 6 (8) 64-bit shuffles for 4 (5) values instead of 20 (25).
@@ -204,10 +205,11 @@ __device__ __forceinline__ double warp_reduce5(double v0, double v1, double v2, 
     return k;
 }
 
-// The pixel passes of one evaluation, executed by every warp between the evaluation's first barrier (scalar block
-// published) and its third.  Only the master warp needs the totals; a worker needs sum f alone (the normalisation).
-template <int THREADS, bool MASTER>
-__device__ __forceinline__ void eval_pixels(double (&M)[4], double (&T)[5]) {
+// The pixel passes of one evaluation, executed by the worker warps between the evaluation's first barrier (value block
+// published by the master) and its third.  The totals are needed by the master alone; a worker needs sum f (the
+// normalisation) for the second pass.
+template <int THREADS>
+__device__ __forceinline__ void eval_pixels() {
     constexpr int NWARPS = THREADS / 32;
     EvalShared &es = eval_shared();
     double *scrA = reinterpret_cast<double *>(smem_raw + ES_BYTES);   // NWARPS x 4
@@ -246,14 +248,10 @@ __device__ __forceinline__ void eval_pixels(double (&M)[4], double (&T)[5]) {
         if ((lane & 7) == 0) scrA[warp * 4 + (lane >> 3)] = k;
     }
     bar_eval<THREADS>();
+    double sumf = scrA[0];
 #pragma unroll
-    for (int i = 0; i < (MASTER ? 4 : 1); i++) {
-        double t = scrA[i];
-#pragma unroll
-        for (int w = 1; w < NWARPS; w++) t += scrA[w * 4 + i];
-        M[i] = t;
-    }
-    const double A = 1.0 / M[0];
+    for (int w = 1; w < NWARPS; w++) sumf += scrA[w * 4];
+    const double A = 1.0 / sumf;
     // pass B: residual moments over non-NaN pixels (analyticLBFGS.jl:36-44)
     double R0 = 0.0, R1 = 0.0, R2 = 0.0, R3 = 0.0;
     if (active) {
@@ -279,22 +277,15 @@ __device__ __forceinline__ void eval_pixels(double (&M)[4], double (&T)[5]) {
         else if (lane == 4) scrB[warp * 5] = k;
     }
     bar_eval<THREADS>();
-    if (MASTER) {
-#pragma unroll
-        for (int i = 0; i < 5; i++) {
-            double t = scrB[i];
-#pragma unroll
-            for (int w = 1; w < NWARPS; w++) t += scrB[w * 5 + i];
-            T[i] = t;
-        }
-    }
 }
 
 // value_gradient!(d, x): the reference runs g! (ForwardDiff over cost) and then cost(x); the value channel of the dual
-// pass is the same operation sequence, so one evaluation yields both.  MASTER WARP ONLY: it owns the optimiser state;
-// the other warps sit in worker_loop() and join the pixel passes of every evaluation.
+// pass is the same operation sequence, so one evaluation yields both.  MASTER WARP ONLY: it owns the optimiser state
+// and does no pixel work.  It publishes the VALUES of the scalar section (all the pixel passes need), releases the
+// workers, and evaluates the dual-number partials (a dozen dependent IEEE divisions and square roots) while they run.
 template <int THREADS>
 __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
+    constexpr int NWARPS = THREADS / 32;
     EvalShared &es = eval_shared();
     FG out;
     if (es.have_last && x0 == es.xl[0] && x1 == es.xl[1] && x2 == es.xl[2]) {
@@ -302,24 +293,38 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
         return out;
     }
     double *s = es.sc;
-    {   // scalar section
-        Dual sig = d_seed(x0, 0), e1 = d_seed(x1, 1), e2 = d_seed(x2, 2);
-        Dual sg = d_sq(sig);
-        Dual g1, g2;
-        e_to_g_dual(e1, e2, g1, g2);
-        Dual a11 = d_radd(1.0, g1), a22 = d_rsub(1.0, g1);
-        Dual ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
-        if (threadIdx.x == 0) {
-            s[0] = a11.v; s[1] = a22.v; s[2] = g2.v; s[3] = ms.v;
-#pragma unroll
-            for (int j = 0; j < 3; j++) { s[4 + j] = a11.d[j]; s[7 + j] = a22.d[j]; s[10 + j] = g2.d[j]; s[13 + j] = ms.d[j]; }
+    {   // value channel of the scalar section, op for op the .v of the dual evaluation below
+        double g1v, g2v;
+        e_to_g(x1, x2, g1v, g2v);
+        const double sgv = mul_(x0, x0);
+        const double msv = div_(mul_(sgv, sgv), sub_(sub_(1.0, mul_(g1v, g1v)), mul_(g2v, g2v)));
+        if ((threadIdx.x & 31) == 0) {
+            s[0] = add_(1.0, g1v); s[1] = sub_(1.0, g1v); s[2] = g2v; s[3] = msv;
             es.cmd = CMD_EVAL;
         }
     }
-    bar_eval<THREADS>();
+    bar_eval<THREADS>();                                   // workers start the pixel passes
+    Dual a11, a22, g2, ms;
+    {   // dual-number scalar section (analyticLBFGS.jl:10-18 under ForwardDiff), overlapped with pass A
+        Dual sig = d_seed(x0, 0), e1 = d_seed(x1, 1), e2 = d_seed(x2, 2);
+        Dual sg = d_sq(sig);
+        Dual g1;
+        e_to_g_dual(e1, e2, g1, g2);
+        a11 = d_radd(1.0, g1); a22 = d_rsub(1.0, g1);
+        ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
+    }
+    const double *scrA = reinterpret_cast<const double *>(smem_raw + ES_BYTES);
+    const double *scrB = scrA + NWARPS * 4;
     double M[4], T[5];
-    eval_pixels<THREADS, true>(M, T);
-    const double A11 = s[0], A22 = s[1], G2 = s[2], MS = s[3];
+    bar_eval<THREADS>();                                   // pass A partials are in
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        double t = scrA[i];
+#pragma unroll
+        for (int w = 1; w < NWARPS; w++) t += scrA[w * 4 + i];
+        M[i] = t;
+    }
+    const double A11 = a11.v, A22 = a22.v, G2 = g2.v, MS = ms.v;
     const double qa = A11 * A11 + G2 * G2, qb = 2.0 * (G2 * (A11 + A22)), qc = G2 * G2 + A22 * A22;
     const double A = 1.0 / M[0];
     // rebuild the reference's sums from the moments, then the chain rule:
@@ -328,6 +333,20 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
     const double Sw1u = A11 * M[1] + G2 * M[2];
     const double Sx = (A11 + A22) * M[2] + G2 * (M[1] + M[3]);
     const double Sw2v = G2 * M[2] + A22 * M[3];
+    double dA[3];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        const double dS = -(ms.d[j] * Sq + 2.0 * MS * (a11.d[j] * Sw1u + g2.d[j] * Sx + a22.d[j] * Sw2v));
+        dA[j] = -(A / M[0]) * dS;
+    }
+    bar_eval<THREADS>();                                   // pass B partials are in
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        double t = scrB[i];
+#pragma unroll
+        for (int w = 1; w < NWARPS; w++) t += scrB[w * 5 + i];
+        T[i] = t;
+    }
     const double Tq = qa * T[2] + qb * T[3] + qc * T[4];
     const double Tw1u = A11 * T[2] + G2 * T[3];
     const double Tx = (A11 + A22) * T[3] + G2 * (T[2] + T[4]);
@@ -335,11 +354,8 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
     double g[3];
 #pragma unroll
     for (int j = 0; j < 3; j++) {
-        const double a11d = s[4 + j], a22d = s[7 + j], g2d = s[10 + j], msd = s[13 + j];
-        const double dS = -(msd * Sq + 2.0 * MS * (a11d * Sw1u + g2d * Sx + a22d * Sw2v));
-        const double dA = -(A / M[0]) * dS;
-        const double dT = -(msd * Tq + 2.0 * MS * (a11d * Tw1u + g2d * Tx + a22d * Tw2v));
-        g[j] = dA * T[1] + A * dT;
+        const double dT = -(ms.d[j] * Tq + 2.0 * MS * (a11.d[j] * Tw1u + g2.d[j] * Tx + a22.d[j] * Tw2v));
+        g[j] = dA[j] * T[1] + A * dT;
     }
     out.f = T[0]; out.g0 = g[0]; out.g1 = g[1]; out.g2 = g[2];
     // every lane of the master warp stores the same bits
@@ -357,8 +373,7 @@ __device__ __forceinline__ void worker_loop() {
     for (;;) {
         bar_eval<THREADS>();
         if (*reinterpret_cast<volatile int *>(&es.cmd) == CMD_EXIT) break;
-        double M[4], T[5];
-        eval_pixels<THREADS, false>(M, T);
+        eval_pixels<THREADS>();
     }
 }
 
@@ -734,7 +749,7 @@ __device__ __forceinline__ void load_edges(const FitArgs &a, long long star, dou
 }
 
 template <int THREADS, int MINB>
-__global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
+__global__ void __launch_bounds__(THREADS + 32, MINB) fit_kernel(const FitArgs a) {
     constexpr int NWARPS = THREADS / 32;
     // [ EvalShared | scratch 2*NWARPS*6 | mbarriers 2 x 8 B | next_star 2 x 8 B | coff nbuf*stride | crop nbuf | f plane ]
     EvalShared &es = eval_shared();
@@ -779,7 +794,7 @@ __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
         load_edges(a, cur, crop);
         __syncthreads();   // edge columns, next_star and the evaluator state visible
 
-        if (threadIdx.x >= 32) {
+        if (threadIdx.x < THREADS) {
             worker_loop<THREADS>();
         } else {   // master warp: the scalar LBFGS / HagerZhang state machine, every lane redundantly
             const double x0[3] = {a.x0[3 * cur + 0], a.x0[3 * cur + 1], a.x0[3 * cur + 2]};
@@ -787,13 +802,13 @@ __global__ void __launch_bounds__(THREADS, MINB) fit_kernel(const FitArgs a) {
             int iters = 0;
             if (a.f_out) {   // cost(x0), g!(G, x0) only
                 const FG r = eval_fg<THREADS>(x0[0], x0[1], x0[2]);
-                if (threadIdx.x == 0) {
+                if (threadIdx.x == THREADS) {
                     a.f_out[cur] = r.f;
                     a.g_out[3 * cur + 0] = r.g0; a.g_out[3 * cur + 1] = r.g1; a.g_out[3 * cur + 2] = r.g2;
                 }
             }
             const int st = a.f_out ? 0 : lbfgs_fit<THREADS>(x0, a.g_tol, a.max_iter, p, iters);
-            if (threadIdx.x == 0) {
+            if (threadIdx.x == THREADS) {
                 if (!a.f_out) {
                     a.s[cur] = p[0]; a.g1[cur] = p[1]; a.g2[cur] = p[2];
                     if (a.status) a.status[cur] = st;
@@ -841,7 +856,7 @@ static int launch_fit(FitArgs a, cudaStream_t stream) {
         if (smem > 227 * 1024) continue;
         SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = 0;
-        SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS, smem));
+        SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS + 32, smem));
         if (per_sm > best_per_sm) { best_per_sm = per_sm; best_nbuf = nbuf; best_smem = smem; }
     }
     if (best_per_sm < 1) return SHOPT_E_UNSUPPORTED;
@@ -850,7 +865,7 @@ static int launch_fit(FitArgs a, cudaStream_t stream) {
     long long grid = (long long)sm_count() * best_per_sm;
     if (grid > a.N) grid = a.N;
     SHOPT_CUDA_TRY(cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream));
-    kern<<<(unsigned)grid, THREADS, best_smem, stream>>>(a);
+    kern<<<(unsigned)grid, THREADS + 32, best_smem, stream>>>(a);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }

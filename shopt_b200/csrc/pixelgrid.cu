@@ -39,6 +39,7 @@ struct PcaArgs {
     size_t wstride;
     int kmax;             // min(ncomp, r, c)
     int fast;             // try the block subspace iteration first (0: always the full Jacobi SVD)
+    int debug;            // status |= (subspace iterations used by the fast path) << 8
     double kern[15 * 15]; // normalised lanczos kernel (2a+1)^2, a <= 7, column-major like the reference's
     double kz[15];        // its 1-D factor: kern = kz (x) kz / sum
 };
@@ -172,10 +173,12 @@ __device__ __forceinline__ void mul_zt_q(const double *Z, int r, int c, const do
     }
 }
 // Qn = Z T : lanes = (row ii = lane & 7, column-part = lane >> 3); eight rows of Z per warp
+// executed by warps w0 .. NW-1 only (w0 = 1 while warp 0 solves the Rayleigh-Ritz eigenproblem)
 template <int NW>
-__device__ __forceinline__ void mul_z_t(const double *Z, int r, int c, const double *T, double *Qn, int ldq) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, ii = lane & 7, part = lane >> 3;
-    for (int i0 = warp * 8; i0 < r; i0 += NW * 8) {
+__device__ __forceinline__ void mul_z_t(const double *Z, int r, int c, const double *T, double *Qn, int ldq, int w0 = 0) {
+    const int warp = (threadIdx.x >> 5) - w0, lane = threadIdx.x & 31, ii = lane & 7, part = lane >> 3;
+    if (warp < 0) return;
+    for (int i0 = warp * 8; i0 < r; i0 += (NW - w0) * 8) {
         const int i = i0 + ii;
         const bool live = i < r;
         const double *zr = Z + (live ? i : 0);
@@ -266,8 +269,12 @@ __device__ void cholqr(const double *Qsrc, double *Qdst, int r, int ldq, double 
 // Symmetric 8 x 8 eigenproblem  G = V diag(theta) V'  by cyclic two-sided Jacobi inside ONE warp (Rayleigh-Ritz of the
 // block).  Lane l owns row (l & 7) of the working matrix and of V (the four groups of eight lanes run the same
 // computation).  A sweep is the 7-step round-robin tournament on 8 indices, 4 disjoint pairs per step; lane group m
-// computes the rotation of pair m and broadcasts it; all register indices are compile-time constants.  Gt: lower triangle, e = i(i+1)/2 + j;  Vout[a * 8 + b] = V_ab.
-__device__ void eig8_warp(const double *Gt, double *Vout) {
+// computes the rotation of pair m and broadcasts it; all register indices are compile-time constants.
+// Pairs whose diagonal entries are BOTH below `cut` are left alone: pca_image keeps component k only while the
+// cumulative variance is below pratio of the total, so a kept component carries at least (1 - pratio) total / min(r,c);
+// with cut an eighth of that, the principal block of the "small" indices has trace < 7 cut and cannot hide a component
+// that would be kept, and the sum of the Ritz values (all that is used of the small ones) is rotation-invariant.  Gt: lower triangle, e = i(i+1)/2 + j;  Vout[a * 8 + b] = V_ab.
+__device__ void eig8_warp(const double *Gt, double *Vout, double cut) {
     const int lane = threadIdx.x & 31, i = lane & 7;
     double a[FB], v[FB], dg;
 #pragma unroll
@@ -295,7 +302,7 @@ __device__ void eig8_warp(const double *Gt, double *Vout) {
             // t = tan(theta) from  t = h sgn(d) / (|d| + sqrt(d^2 + h^2)),  d = aqq - app, h = 2 apq.  Only c^2 + s^2 = 1
             // needs full accuracy (c = rsqrt(1 + t^2), s = t c), so the quotient uses rsqrt instead of IEEE div/sqrt.
             double c = 1.0, sg = 0.0, t = 0.0;
-            if (apq * apq > (DBL_EPSILON * DBL_EPSILON) * fabs(app * aqq) && apq != 0.0) {
+            if (apq * apq > (DBL_EPSILON * DBL_EPSILON) * fabs(app * aqq) && apq != 0.0 && (app >= cut || aqq >= cut)) {
                 const double d = aqq - app, h = 2.0 * apq;
                 const double w = fma(d, d, h * h);
                 const double den = fabs(d) + w * rsqrt(w);
@@ -340,10 +347,10 @@ __device__ void eig8_warp(const double *Gt, double *Vout) {
     }
 }
 
-// Rayleigh-Ritz on the block: G = T'T (= Q' Z Z' Q), V from eig8_warp, then T <- T V and Q <- Q V.
+// Rayleigh-Ritz on the block: G = T'T (= Q' Z Z' Q), V from eig8_warp, then T <- T V, Q <- Q V and Qn <- (Z T) V.
 // FGm: 36 doubles Gram + 64 doubles V.  Ends with a __syncthreads.
 template <int NW>
-__device__ void rayleigh_ritz(double *T, int c, double *Q, int r, int ldq, double *FGm) {
+__device__ void rayleigh_ritz(const double *Z, double *T, int c, double *Q, double *Qn, int r, int ldq, double *FGm, double cut) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
     double *Gt = FGm, *V = FGm + 36;
     for (int e = warp; e < FB * (FB + 1) / 2; e += NW) {
@@ -358,11 +365,14 @@ __device__ void rayleigh_ritz(double *T, int c, double *Q, int r, int ldq, doubl
         if (lane == 0) Gt[e] = s;
     }
     __syncthreads();
-    if (warp == 0) eig8_warp(Gt, V);
+    // warp 0 solves the 8 x 8 eigenproblem; the other warps meanwhile form Qn = Z T = Z Z' Q with the UNrotated block
+    // (rotating afterwards commutes: Z Z' (Q V) = (Z Z' Q) V), which the residual test of the caller needs
+    if (warp == 0) eig8_warp(Gt, V, cut);
+    else mul_z_t<NW>(Z, r, c, T, Qn, ldq, 1);
     __syncthreads();
-    for (int u = tid; u < r + c; u += nthr) {
-        double *base = (u < r) ? Q + u : T + (u - r);
-        const int ld = (u < r) ? ldq : c;
+    for (int u = tid; u < 2 * r + c; u += nthr) {
+        double *base = (u < r) ? Q + u : (u < r + c ? T + (u - r) : Qn + (u - r - c));
+        const int ld = (u < r || u >= r + c) ? ldq : c;
         double x[FB], y[FB];
 #pragma unroll
         for (int b = 0; b < FB; b++) { x[b] = base[b * ld]; y[b] = 0.0; }
@@ -380,7 +390,7 @@ __device__ void rayleigh_ritz(double *T, int c, double *Q, int r, int ldq, doubl
 // returns k >= 1 on acceptance (ford[0..k) = block columns of the kept components, Q = Ritz vectors, T = Z'Q), else 0
 template <int NW, int RT>
 __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, double pratio, double *Q, double *Qn,
-                        double *T, int ldq, double *G, double *fth, int *ford, int *s_flag) {
+                        double *T, int ldq, double *G, double *fth, int *ford, int *s_flag, int *dbg_it, int usecut) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
     const int j0 = c / 2 - FB / 2;
     for (int e = tid; e < FB * r; e += nthr) {
@@ -390,13 +400,15 @@ __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, do
     __syncthreads();
     cholqr<NW>(Qn, Q, r, ldq, G);
     cholqr<NW>(Q, Q, r, ldq, G);
+    // the small-pair cut of eig8_warp measured SLOWER on the bench catalogue (profiles/README.md); off unless debug & 4
+    const double rr_cut = usecut ? (1.0 - pratio) * fro / (8.0 * (double)(r < c ? r : c)) : 0.0;
     for (int it = 1; it <= 12; it++) {
         mul_zt_q<NW>(Z, r, c, Q, ldq, T);
         __syncthreads();
         const bool check = (it == 3 || it == 5 || it == 8 || it == 12);
         if (check) {
             // Rayleigh-Ritz: T'T = V Theta V' (8 x 8, one warp), then T <- T V and Q <- Q V
-            rayleigh_ritz<NW>(T, c, Q, r, ldq, G + 64);
+            rayleigh_ritz<NW>(Z, T, c, Q, Qn, r, ldq, G + 64, rr_cut);
             for (int b = warp; b < FB; b += NW) {
                 double s = 0.0;
                 for (int j = lane; j < c; j += 32) s = fma(T[b * c + j], T[b * c + j], s);
@@ -428,15 +440,13 @@ __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, do
                     k++;
                 }
                 const double thk = fth[ford[k - 1]];
-                if (!(thk > 0.0) || !(E <= 0.25 * thk) || !isfinite(fro)) ok = 0;
+                if (!(thk > 0.0) || !(E <= 0.25 * thk) || !isfinite(fro) || !(thk >= 8.0 * rr_cut)) ok = 0;
                 *s_flag = ok ? k : 0;
             }
             __syncthreads();
             const int k = *s_flag;
             if (k == 0) return 0;
-            mul_z_t<NW>(Z, r, c, T, Qn, ldq);
-            __syncthreads();
-            for (int a = warp; a < k; a += NW) {                 // residual |Z Z'u - theta u|^2
+            for (int a = warp; a < k; a += NW) {                 // residual |Z Z'u - theta u|^2 (Qn = Z Z' Q from rayleigh_ritz)
                 const int b = ford[a];
                 const double th = fth[b];
                 double s = 0.0;
@@ -452,7 +462,7 @@ __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, do
             const double tol = 1e-13 * fro;
             bool conv = true;
             for (int a = 0; a < k; a++) conv = conv && (G[48 + a] <= tol * tol);
-            if (conv) return k;
+            if (conv) { if (dbg_it) *dbg_it = it; return k; }
             __syncthreads();
         } else {
             mul_z_t<NW>(Z, r, c, T, Qn, ldq);
@@ -606,9 +616,9 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         fro = block_sum1<NW>(fro, scratch, buf);                // |Z|_F^2; the block sum also publishes W
 
         // ---- fast path: block subspace iteration with a-posteriori acceptance ----
-        int k = 0, status = SHOPT_PCA_OK;
+        int k = 0, status = SHOPT_PCA_OK, dbg_it = 0;
         if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
-            k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag);
+            k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag, &dbg_it, a.debug & 4);
         const bool fastk = k > 0;
         if (fastk) {
             if (tid < k) {
@@ -673,6 +683,13 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
                 }
             }
             __syncthreads();
+        }
+        // the next star's stamp starts its way into L2 now (one bulk prefetch); its load phase then hits L2
+        if (tid == 0 && nxt < a.N && !(a.debug & 2)) {
+            const uintptr_t p0 = (uintptr_t)(a.stamps + nxt * rc), p1 = (uintptr_t)(a.stamps + (nxt + 1) * rc);
+            const uintptr_t lo = p0 & ~(uintptr_t)15, hi = p1 & ~(uintptr_t)15;      // stays inside the batch
+            if (hi > lo)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(lo), "r"((uint32_t)(hi - lo)) : "memory");
         }
         // ---- reconstruct: R = U_k Y + mean.  Thread = (row i, column segment); the fast path leaves U and Y outside W,
         //      so R goes straight into W when it is smoothed next; the Jacobi path (U inside W) goes through `out` ----
@@ -755,7 +772,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         }
         if (tid == 0) {
             if (a.k_out) a.k_out[star] = k;
-            if (a.status) a.status[star] = status;
+            if (a.status) a.status[star] = (a.debug & 1) ? (status | (dbg_it << 8)) : status;
             *s_next = nxt;
         }
     }
@@ -956,6 +973,7 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
     a.counter = d_counter; a.wglobal = nullptr; a.wstride = 0;
     a.kmax = ncomp < r ? ncomp : r; if (c < a.kmax) a.kmax = c;
     a.fast = (getenv("SHOPT_PCA_NO_FAST") == nullptr);
+    a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on
     if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern, a.kz);
     const int rt = ((r > c ? r : c) + 31) / 32;
     switch (rt) {

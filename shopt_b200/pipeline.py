@@ -107,6 +107,8 @@ def run_stage_dev(params, stamps, u, v, x0_model, x0_learned, perm, n_global=Non
     check(_lib.lib().shopt_stage_run_dev(C.byref(params), C.byref(io), C.cast(cb, C.c_void_p) if cb else None, None, stream))
     out["n_per_round"] = npr[:params.iterations].copy()
     out["counts"] = dict(zip(("blacklisted", "failed", "training", "kept"), list(io.counts)))
+    out["field"] = np.array(io.field).reshape(3, 10)     # s(u,v), g1(u,v), g2(u,v): shopt.jl:422-466
+    out["field_rank"] = int(io.field_rank)
     return out
 
 
@@ -132,4 +134,6 @@ def run_stage(params, stamps, u, v, x0_model, x0_learned, perm, want_pgf=True, w
     check(_lib.lib().shopt_stage_run(C.byref(params), C.byref(io)))
     out["n_per_round"] = npr[:params.iterations].copy()
     out["counts"] = dict(zip(("blacklisted", "failed", "training", "kept"), list(io.counts)))
+    out["field"] = np.array(io.field).reshape(3, 10)     # s(u,v), g1(u,v), g2(u,v): shopt.jl:422-466
+    out["field_rank"] = int(io.field_rank)
     return out

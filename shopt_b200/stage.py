@@ -207,3 +207,25 @@ def chisq_batch(stamps, weights, x0=None, fill=0.0, unity_sum=False):
     check(_lib.lib().shopt_chisq_batch(_ptr(stamps), _ptr(weights), _ptr(x0) if x0 is not None else None, float(fill),
                                        r, c, N, int(unity_sum), _ptr(out)))
     return out
+
+
+def field_interp(u, v, *values):
+    """s(u,v), g1(u,v), g2(u,v): cubic least squares in the reference's coefficient order
+    [u^3, v^3, u^2 v, v^2 u, u^2, v^2, u v, u, v, 1] (interpolate.jl:7-87, shopt.jl:422-466).
+    Returns coef (len(values), 10) and the numerical rank."""
+    import ctypes as C
+    u, v = _f64(u), _f64(v)
+    vals = [_f64(x) for x in values]
+    arr = (dp * len(vals))(*[_ptr(x) for x in vals])
+    coef = np.zeros((len(vals), 10))
+    rank = _lib.lib().shopt_field_interp(_ptr(u), _ptr(v), arr, len(vals), len(u), _ptr(coef))
+    if rank < 0:
+        check(rank)
+    return coef, rank
+
+
+def field_eval(coef, u, v):
+    coef, u, v = _f64(coef), _f64(u), _f64(v)
+    out = np.zeros(len(u))
+    check(_lib.lib().shopt_field_eval(_ptr(coef), _ptr(u), _ptr(v), len(u), _ptr(out)))
+    return out

@@ -112,3 +112,32 @@ def test_psf_at(orc):
     star = orc.psf_at(poly, 3, 0.3, -0.7)
     want = np.einsum("k,kcr->cr", design(3, np.array([0.3]), np.array([-0.7]))[0], poly)
     assert np.allclose(star, want / want.sum(), rtol=1e-12)                        # reader.jl:40-68
+
+
+def test_field_interpolation_is_the_least_squares_solution(stage):
+    """shopt.jl:422-466 minimises interpCostS (interpolate.jl:7-19) by LBFGS from rand(10); the cost is a convex
+    quadratic, so the product's direct QR solution, numpy's SVD-based lstsq and a quasi-Newton run from a random
+    start must all land on the same coefficients.  Host code: runs without a device."""
+    from scipy.optimize import minimize
+    from oracle import stage_oracle
+    rng = np.random.default_rng(12)
+    n = 500
+    u, v = rng.uniform(-1, 1, n), rng.uniform(-1, 1, n)
+    s = 0.30 + 0.05 * u - 0.03 * v + 0.02 * u * v + 0.01 * u ** 3 + 1e-3 * rng.normal(size=n)
+    g1 = 0.08 + 0.03 * u - 0.02 * v * v + 1e-3 * rng.normal(size=n)
+    g2 = -0.03 + 0.03 * v + 0.02 * u * u + 1e-3 * rng.normal(size=n)
+    coef, rank = stage.field_interp(u, v, s, g1, g2)
+    want = stage_oracle.field_interp(u, v, s, g1, g2)
+    assert rank == 10 and np.allclose(coef, want, rtol=1e-9, atol=1e-12)
+
+    def cost(p):                                   # interpolate.jl:8-18 as written
+        I = p[0]*u**3 + p[1]*v**3 + p[2]*u**2*v + p[3]*v**2*u + p[4]*u**2 + p[5]*v**2 + p[6]*u*v + p[7]*u + p[8]*v + p[9]
+        return np.sum((I - s) ** 2)
+    res = minimize(cost, rng.uniform(size=10), method="L-BFGS-B", options=dict(gtol=1e-12, ftol=1e-30, maxiter=5000))
+    assert np.allclose(res.x, coef[0], atol=2e-5)
+    assert np.allclose(stage.field_eval(coef[0], u[:7], v[:7]),
+                       [np.dot(want[0], [a**3, b**3, a*a*b, b*b*a, a*a, b*b, a*b, a, b, 1.0])
+                        for a, b in zip(u[:7], v[:7])], rtol=1e-12)
+    # rank-deficient input (all stars on one line): the dependent coefficients are zeroed, the fit is still exact
+    coef, rank = stage.field_interp(u, u, 2.0 + 3.0 * u)
+    assert rank < 10 and np.allclose(stage.field_eval(coef[0], u, u), 2.0 + 3.0 * u, atol=1e-9)
