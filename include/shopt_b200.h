@@ -56,6 +56,22 @@ const char *shopt_last_error(void);            /* text of the last CUDA error on
  * [0]=H2D [1]=kernels [2]=D2H (CUDA events on the library's stream) */
 int         shopt_last_timing(double ms[3]);
 
+/* ---- (0) ingest: the per-star work of cataloging() that precedes the stage --------------------------
+ * Replaces, in dataPreprocessing.jl:342-397 (FITS decoding stays with astropy / CFITSIO):
+ *   nanMask (masks.jl:5-17: x < -1000 -> NaN);  unity_sum: ./ sum(nanToZero(nanMask(.))) (:344-346);
+ *   new_dim < r0: get_middle_nxn crop (:207-216, :384);  new_dim > r0: bilinear oversample_image (:141-162, :391);
+ *   a resized stamp is ALWAYS renormalised, nm(.) / sum(nz(nm(.))), and smoothed, smooth(., lanczos_a) (quirk B.9).
+ * vignets (r0, c0, N): the raw VIGNET cube, float32 when dtype_f32 != 0 (what SExtractor writes) else float64;
+ * stamps_out (new_dim, new_dim, N) float64 (new_dim == r0: (r0, c0, N), no resize).  Resizing needs r0 == c0. */
+int shopt_ingest_batch(const void *vignets, int dtype_f32, int r0, int c0, int64_t N, int unity_sum, int new_dim,
+                       int lanczos_a, double *stamps_out);
+int shopt_ingest_batch_dev(const void *d_vignets, int dtype_f32, int r0, int c0, int64_t N, int unity_sum, int new_dim,
+                           int lanczos_a, double *d_stamps_out, void *stream);
+/* outliers_filter (outliers.jl:16-34) on the Float32 SNR_WIN column: q1 = quantile(snr, k) (SnRPercentile), returns
+ * the count of stars with snr < q1 and their 0-based indices (ascending); SHOPT_E_BADARG when snr holds a NaN
+ * (Statistics.quantile raises).  Host function.  q1_out may be NULL. */
+int64_t shopt_snr_cut(const float *snr, int64_t N, double k, int64_t *idx_out, double *q1_out);
+
 /* ---- (1) analytic profile fit ------------------------------------------------------------
  * Replaces the loops  shopt/shopt.jl:130-164  (model stars, cost/g!)  and  :357-397  (learned
  * stars, costD/gD!):  Optim.optimize(cost, g!, x0, LBFGS(), Options(g_tol))  per star, with

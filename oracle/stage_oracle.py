@@ -12,6 +12,67 @@ from . import shopt_oracle as orc
 FLAG_BLACKLISTED, FLAG_PCA_FAILED, FLAG_LEARNED_OOB, FLAG_TRAINING, FLAG_REJECTED = 1, 2, 4, 8, 16
 
 
+def nan_mask(a):
+    """masks.jl:5-17"""
+    out = np.array(a, dtype=np.float64)
+    out[out < -1000] = np.nan
+    return out
+
+
+def get_middle_nxn(a, n):
+    """dataPreprocessing.jl:207-216 on an array stored (c, r): both starts are div(size - n, 2) (0-based)."""
+    cs, rs = (a.shape[0] - n) // 2, (a.shape[1] - n) // 2
+    return a[cs:cs + n, rs:rs + n]
+
+
+def oversample_image(img, nd):
+    """dataPreprocessing.jl:141-162 (bilinear); img stored (c, r) = img[col, row], so image[y, x] of the reference
+    (y = row index, first) is img[x-1, y-1]."""
+    size1, size2 = img.shape[1], img.shape[0]
+    scale = 1 / (nd / size1)
+    out = np.zeros((nd, nd))
+    for y in range(1, nd + 1):
+        for x in range(1, nd + 1):
+            sx, sy = (x - 0.5) * scale + 0.5, (y - 0.5) * scale + 0.5
+            x0 = max(1, int(np.floor(sx))); x1 = min(size1, x0 + 1)
+            y0 = max(1, int(np.floor(sy))); y1 = min(size2, y0 + 1)
+            dx, dy = sx - x0, sy - y0
+            I = lambda yy, xx: img[xx - 1, yy - 1]
+            out[x - 1, y - 1] = ((1 - dx) * (1 - dy) * I(y0, x0) + dx * (1 - dy) * I(y0, x1) + (1 - dx) * dy * I(y1, x0)
+                                 + dx * dy * I(y1, x1))
+    return out
+
+
+def ingest(vignets, unity_sum=False, new_dim=None, lanczos=3):
+    """The per-star part of cataloging() (dataPreprocessing.jl:342-397): nanMask, optional unity sum, and for
+    new_dim != size the crop / oversample followed by nm(.)/sum(nz(nm(.))) and smooth(., lanczos)."""
+    out = []
+    for img in vignets:
+        a = nan_mask(img)
+        if unity_sum:
+            a = a / orc.nan_to_zero(a).sum()
+        r0 = a.shape[1]
+        if new_dim is not None and new_dim != r0:
+            b = get_middle_nxn(a, new_dim) if new_dim < r0 else oversample_image(a, new_dim)
+            b = nan_mask(b)
+            b = b / orc.nan_to_zero(b).sum()
+            a = orc.smooth(np.ascontiguousarray(b), lanczos) if lanczos > 0 else b
+        out.append(a)
+    return np.stack(out)
+
+
+def snr_cut(snr, k):
+    """outliers.jl:16-34: indices with snr < quantile(snr, k) (Statistics' type-7 quantile of a Float32 vector)."""
+    v = np.sort(np.asarray(snr, dtype=np.float32))
+    n = len(v)
+    aleph = n * k + (1.0 - k)
+    j = int(min(max(np.trunc(aleph), 1), max(n - 1, 1)))
+    gamma = min(max(aleph - j, 0.0), 1.0)
+    a, b = v[j - 1], v[j] if n > 1 else v[0]
+    q1 = float(a) + gamma * float(np.float32(b - a))
+    return np.nonzero(np.asarray(snr, dtype=np.float32).astype(np.float64) < q1)[0], q1
+
+
 def field_interp(u, v, *values):
     """interpolate.jl:7-87: the minimiser of sum (I_p(u,v) - t)^2 over the 10 cubic coefficients, term order
     [u^3, v^3, u^2 v, v^2 u, u^2, v^2, u v, u, v, 1] (numpy lstsq: SVD-based, independent of the product's QR)."""

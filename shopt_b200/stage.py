@@ -229,3 +229,32 @@ def field_eval(coef, u, v):
     out = np.zeros(len(u))
     check(_lib.lib().shopt_field_eval(_ptr(coef), _ptr(u), _ptr(v), len(u), _ptr(out)))
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# (0) ingest: cataloging() of dataPreprocessing.jl:342-397 without the FITS decoding
+# ------------------------------------------------------------------------------------------------
+def ingest_batch(vignets, unity_sum=False, new_dim=None, lanczos_a=3):
+    """vignets (N, c0, r0) float32 or float64 raw VIGNET cube -> stamps (N, nd, nd) float64: nanMask, optional
+    unity-sum, crop / bilinear resample to new_dim with renormalisation + smooth (see include/shopt_b200.h)."""
+    v = np.ascontiguousarray(vignets)
+    if v.dtype != np.float32:
+        v = np.ascontiguousarray(v, dtype=np.float64)
+    N, c0, r0 = v.shape
+    nd = r0 if new_dim is None else int(new_dim)
+    out = np.zeros((N, nd, nd) if nd != r0 else (N, c0, r0))
+    check(_lib.lib().shopt_ingest_batch(v.ctypes.data, int(v.dtype == np.float32), r0, c0, N, int(unity_sum), nd,
+                                        lanczos_a, _ptr(out)))
+    return out
+
+
+def snr_cut(snr, k):
+    """outliers_filter of outliers.jl:16-34: (0-based indices with snr < quantile(snr, k), the quantile)."""
+    import ctypes as C
+    snr = np.ascontiguousarray(snr, dtype=np.float32)
+    idx = np.zeros(max(len(snr), 1), np.int64)
+    q1 = C.c_double()
+    n = _lib.lib().shopt_snr_cut(snr.ctypes.data_as(C.POINTER(C.c_float)), len(snr), float(k), _ptr(idx, lp), C.byref(q1))
+    if n < 0:
+        check(int(n))
+    return idx[:n].copy(), q1.value

@@ -66,3 +66,19 @@ def test_no_device_fails_loudly(stage):
     with pytest.raises(_lib.ShoptError) as e:
         stage.fit_analytic_batch(st, 8, x0)
     assert e.value.code == _lib.E_NODEVICE
+
+
+def test_snr_cut_is_the_reference_quantile_rule(stage):
+    """outliers_filter (outliers.jl:16-34): host code, runs without a device."""
+    from oracle import stage_oracle
+    from shopt_b200 import _lib
+    rng = np.random.default_rng(7)
+    for n, k in [(1, 0.33), (2, 0.33), (10, 0.33), (291, 0.33), (1000, 0.05), (1000, 0.0), (1000, 1.0), (57, 0.5)]:
+        snr = rng.normal(30, 10, n).astype(np.float32)
+        snr[: n // 5] = np.round(snr[: n // 5])                        # ties
+        idx, q1 = stage.snr_cut(snr, k)
+        widx, wq1 = stage_oracle.snr_cut(snr, k)
+        assert q1 == wq1 and idx.tolist() == widx.tolist()
+        assert np.isclose(q1, np.quantile(snr.astype(np.float64), k), rtol=1e-6)
+    with pytest.raises(_lib.ShoptError):
+        stage.snr_cut(np.array([1.0, np.nan, 2.0], np.float32), 0.33)
