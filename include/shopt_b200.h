@@ -196,6 +196,20 @@ int shopt_field_interp(const double *u, const double *v, const double *const *va
 /* s(u,v) etc. of shopt.jl:437 at n positions (host). */
 int shopt_field_eval(const double *coef, const double *u, const double *v, int64_t n, double *out);
 
+/* ---- summary.shopt: the stage's on-disk product ---------------------------------------------------
+ * Writer for the truncated summary file (truncate_summary_file: true, the shipped default) of
+ * dataOutprocessing.jl:52-84 and reader for read_shopt of reader.jl:13-38, as a self-contained FITS implementation
+ * (astropy is what the reference calls through PyCall):
+ *   HDU 0 image POLYNOMIAL_MATRIX  float64, numpy shape (r, c, K);  HDU 1 BINTABLE SUMMARY_STATISTICS, column
+ *   POLYNOMIAL_DEGREE;  HDU 2 BINTABLE ANALYTIC_PROFILE, columns s_MATRIX, g1_MATRIX, g2_MATRIX (10 rows each, the
+ *   cubic field coefficients in the reference's order).
+ * poly is (r, c, K) column-major as everywhere in this interface.  The reader finds the columns by name in any HDU,
+ * so the reference's full layout (ANALYTIC_PROFILE = HDU 6) reads too; poly may be NULL to query r, c, degree. */
+int shopt_summary_write(const char *path, const double *poly, int r, int c, int degree, const double *sC,
+                        const double *g1C, const double *g2C);
+int shopt_summary_read(const char *path, double *poly, int64_t poly_capacity, int *r, int *c, int *degree, double *sC,
+                       double *g1C, double *g2C);
+
 /* ---- the whole stage: what shopt.jl's loops :130-184, :281-314, :357-417, :472-577 become ---------
  * model fit -> s-blacklist -> PCA pixel-grid fit -> learned fit -> failed list -> training split -> polyfit rounds.
  * Parameters mirror shopt.yml (shopt_params).  Stars keep their ORIGINAL indices: instead of splicing arrays like the

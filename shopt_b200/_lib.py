@@ -78,6 +78,9 @@ SIGNATURES = {
     "shopt_ingest_batch": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, dp]),
     "shopt_ingest_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, vp, vp]),
     "shopt_snr_cut": (C.c_int64, [C.POINTER(C.c_float), C.c_int64, C.c_double, lp, dp]),
+    "shopt_summary_write": (C.c_int, [C.c_char_p, dp, C.c_int, C.c_int, C.c_int, dp, dp, dp]),
+    "shopt_summary_read": (C.c_int, [C.c_char_p, dp, C.c_int64, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                     C.POINTER(C.c_int), dp, dp, dp]),
     "shopt_field_interp": (C.c_int, [dp, dp, C.POINTER(dp), C.c_int, C.c_int64, dp]),
     "shopt_field_eval": (C.c_int, [dp, dp, dp, C.c_int64, dp]),
     "shopt_polyfit": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, dp, dp, lp, C.c_int64, C.c_int, C.c_int, C.c_int,

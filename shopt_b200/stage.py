@@ -258,3 +258,28 @@ def snr_cut(snr, k):
     if n < 0:
         check(int(n))
     return idx[:n].copy(), q1.value
+
+
+# ------------------------------------------------------------------------------------------------
+# summary.shopt (dataOutprocessing.jl:52-84, reader.jl:13-38)
+# ------------------------------------------------------------------------------------------------
+def write_summary(path, poly, degree, field):
+    """poly (K, c, r); field (3, 10) = s, g1, g2 cubic coefficients.  Writes the truncated summary.shopt."""
+    poly, field = _f64(poly), _f64(field)
+    K, c, r = poly.shape
+    check(_lib.lib().shopt_summary_write(str(path).encode(), _ptr(poly), r, c, degree, _ptr(field[0]), _ptr(field[1]),
+                                         _ptr(field[2])))
+
+
+def read_summary(path):
+    """read_shopt of reader.jl:13-38: (poly (K, c, r), degree, field (3, 10))."""
+    import ctypes as C
+    r, c, deg = C.c_int(), C.c_int(), C.c_int()
+    L = _lib.lib()
+    check(L.shopt_summary_read(str(path).encode(), None, 0, C.byref(r), C.byref(c), C.byref(deg), None, None, None))
+    K = num_terms(deg.value)
+    poly = np.zeros((K, c.value, r.value))
+    field = np.zeros((3, 10))
+    check(L.shopt_summary_read(str(path).encode(), _ptr(poly), poly.size, C.byref(r), C.byref(c), C.byref(deg),
+                               _ptr(field[0]), _ptr(field[1]), _ptr(field[2])))
+    return poly, deg.value, field
