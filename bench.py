@@ -155,7 +155,7 @@ def run_reference(args):
 # --------------------------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------------------------
-KERNELS_PER_STEP = 4 + 3 * 6   # fit, pca, fit, flags + 3 rounds x (normal, gram, reduce, solve, mse, mse_reduce)
+KERNELS_PER_STEP = 4 + 2 + 3 * 7   # fit, pca, fit, flags; field normal + reduce; 3 rounds x (normal, gram, reduce, median_fix, solve, mse, mse_reduce)
 
 
 def run_ours(args):

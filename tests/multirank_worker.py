@@ -39,6 +39,9 @@ def main():
     scale = np.abs(ref).max(axis=(1, 2), keepdims=True)
     err = np.max(np.abs(poly - ref) / scale)
     assert err < 1e-10, err
+    # s(u,v), g1(u,v), g2(u,v): the normal equations add over the shards (one 130-double all-reduce)
+    assert got["field_rank"] == io_one["field_rank"] == 10
+    assert np.allclose(got["field"], io_one["field"], rtol=1e-9, atol=1e-12), np.abs(got["field"] - io_one["field"]).max()
     # every rank holds the same replicated result
     gathered = [torch.empty_like(got["poly"]) for _ in range(world)]
     dist.all_gather(gathered, got["poly"])
