@@ -64,16 +64,43 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.rows, self.stop, self.t = index, [], threading.Event(), None
+        self.nvml = None
+        try:   # in-process NVML: a query costs microseconds; spawning nvidia-smi stalls the driver for ~100 ms per call,
+            import pynvml   # which at 2+ ranks showed up as +70 % step time
+            pynvml.nvmlInit()
+            try:
+                import torch
+                uuid = str(torch.cuda.get_device_properties(index).uuid)
+                h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nvml = (pynvml, h)
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        nv, h = self.nvml
+        sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        try:
+            bits = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+        except Exception:
+            bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+        act = lambda m: "Active" if bits & m else "Not Active"
+        return [str(sm), str(mx), act(0x8), act(0x40), act(0x20), act(0x4)]
 
     def _run(self):
         while not self.stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([x.strip() for x in out.strip().split(",")])
+                if self.nvml:
+                    self.rows.append(self._sample_nvml())
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                    self.rows.append([x.strip() for x in out.strip().split(",")])
             except Exception:
                 pass
-            self.stop.wait(0.2)
+            self.stop.wait(0.05 if self.nvml else 0.5)
 
     def __enter__(self):
         self.t = threading.Thread(target=self._run, daemon=True)
@@ -302,8 +329,9 @@ def stage_breakdown(args, p, cat, pgf, out):
 
 def run_e2e(args, p, cat, perm, world, n_global, offset, pgf, barrier):
     """The same step through the public API with HOST buffers: pinned inputs -> H2D -> stage -> D2H of the results
-    (model/learned parameters, flags, polynomial cube).  N = 1 goes through the C ABI host entry point
-    shopt_stage_run (copies inside the library); N > 1 copies explicitly around shopt_stage_run_dev."""
+    (model/learned parameters, flags, polynomial cube) through the C ABI host entry points: shopt_stage_run at N = 1,
+    shopt_stage_run_comm (this rank's shard + the all-reduce callback) at N > 1; the copies happen inside the library,
+    chunked and overlapped with the per-star kernels."""
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -320,15 +348,11 @@ def run_e2e(args, p, cat, perm, world, n_global, offset, pgf, barrier):
     steps = max(1, min(args.steps, 2))
 
     def once():
+        a = {k: host[k].numpy() for k in names}
         if world == 1:
-            a = {k: host[k].numpy() for k in names}
             return pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], perm, want_pgf=False)
-        d = {k: cat[k].copy_(host[k], non_blocking=True) for k in names}
-        o = pipeline.run_stage_dev(p, d["stamps"], d["u"], d["v"], d["x0_model"], d["x0_learned"], perm,
-                                   n_global=n_global, offset=offset, pgf=pgf)
-        res = {k: o[k].cpu() for k in ("model", "learned", "flags", "pca_k", "poly")}
-        torch.cuda.synchronize()
-        return res
+        return pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], perm, want_pgf=False,
+                                  n_global=n_global, offset=offset)
     once()
     barrier()
     t0 = time.perf_counter()
@@ -340,15 +364,22 @@ def run_e2e(args, p, cat, perm, world, n_global, offset, pgf, barrier):
         dist.all_reduce(sec, op=dist.ReduceOp.MAX)
     return {"value": n_global / float(sec.item()), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "ms_per_step": 1e3 * float(sec.item()), "steps": steps,
-            "api": "shopt_stage_run (C ABI, host buffers)" if world == 1 else "pipeline.run_stage_dev + explicit pinned copies"}
+            "api": "shopt_stage_run (C ABI, host buffers)" if world == 1 else
+            "shopt_stage_run_comm (C ABI, host buffers of the shard, torch.distributed all-reduce callback)"}
 
 
 def main():
     args = parse_args()
+    # stdout carries exactly one JSON line: anything libraries print to fd 1 meanwhile (NCCL's version banner, ...) is
+    # sent to stderr, and print() keeps the real stdout
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real
     if args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
+    real.flush()
 
 
 if __name__ == "__main__":

@@ -55,6 +55,9 @@ const char *shopt_last_error(void);            /* text of the last CUDA error on
 /* wall-clock-free device timing of the last host call, milliseconds, per stage:
  * [0]=H2D [1]=kernels [2]=D2H (CUDA events on the library's stream) */
 int         shopt_last_timing(double ms[3]);
+/* The host entry points keep their large device blocks (stamp cube, pixel-grid cube, scratch) between calls on the
+ * calling thread's context; this frees them. */
+int         shopt_release_buffers(void);
 
 /* ---- (0) ingest: the per-star work of cataloging() that precedes the stage --------------------------
  * Replaces, in dataPreprocessing.jl:342-397 (FITS decoding stays with astropy / CFITSIO):
@@ -289,8 +292,11 @@ int64_t shopt_training_split(const int32_t *flags, int64_t n_global, const int64
 /* device-resident shard; comm == NULL runs a single GPU.  Blocks until the stage is done (the outlier selection
  * between rounds runs on the host). */
 int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream);
-/* host buffers, one GPU: H2D, stage, D2H */
+/* host buffers, one GPU: H2D (chunked on a copy stream, overlapped with the per-star kernels), stage, D2H */
 int shopt_stage_run(const shopt_params *p, shopt_stage_io *io);
+/* host buffers of ONE SHARD of a sharded run (one process per GPU): as shopt_stage_run, with the all-reduce callback of
+ * shopt_stage_run_dev (enqueued on the library's stream, which is what `stream` of the callback carries). */
+int shopt_stage_run_comm(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user);
 
 #ifdef __cplusplus
 }

@@ -59,6 +59,7 @@ SIGNATURES = {
     "shopt_set_device": (C.c_int, [C.c_int]),
     "shopt_last_error": (C.c_char_p, []),
     "shopt_last_timing": (C.c_int, [dp]),
+    "shopt_release_buffers": (C.c_int, []),
     "shopt_fit_analytic_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, dp, C.c_double, C.c_int,
                                            dp, dp, dp, ip, ip]),
     "shopt_fit_analytic_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, C.c_double, C.c_int,
@@ -96,6 +97,7 @@ SIGNATURES = {
     "shopt_training_split": (C.c_int64, [ip, C.c_int64, lp, C.c_double, lp]),
     "shopt_stage_run_dev": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO), C.c_void_p, C.c_void_p, C.c_void_p]),
     "shopt_stage_run": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO)]),
+    "shopt_stage_run_comm": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO), C.c_void_p, C.c_void_p]),
 }
 
 _LIB = None

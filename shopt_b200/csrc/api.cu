@@ -37,6 +37,23 @@ int Ctx::need_scratch(size_t bytes) {
     scratch_bytes = bytes;
     return SHOPT_OK;
 }
+int Ctx::need_cache(int i, size_t bytes, void **out) {
+    if (i < 0 || i >= NCACHE) return SHOPT_E_BADARG;
+    if (bytes == 0) bytes = 16;
+    if (bytes > cache_bytes[i]) {
+        if (cache[i]) { cudaDeviceSynchronize(); cudaFree(cache[i]); cache[i] = nullptr; cache_bytes[i] = 0; }
+        cudaError_t e = cudaMalloc(&cache[i], bytes);
+        if (e != cudaSuccess) { cache[i] = nullptr; set_last_error("cudaMalloc(cache)", e); (void)cudaGetLastError(); return SHOPT_E_NOMEM; }
+        cache_bytes[i] = bytes;
+    }
+    *out = cache[i];
+    return SHOPT_OK;
+}
+void Ctx::release_cache() {
+    cudaDeviceSynchronize();
+    for (int i = 0; i < NCACHE; i++) { if (cache[i]) cudaFree(cache[i]); cache[i] = nullptr; cache_bytes[i] = 0; }
+    if (scratch) { cudaFree(scratch); scratch = nullptr; scratch_bytes = 0; }
+}
 static thread_local Ctx g_ctx[16];
 
 int get_ctx(Ctx **out) {
@@ -96,6 +113,13 @@ int shopt_last_timing(double ms[3]) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) { (void)cudaGetLastError(); return SHOPT_E_NODEVICE; }
     for (int i = 0; i < 3; i++) ms[i] = g_ctx[dev].ms[i];
+    return SHOPT_OK;
+}
+
+int shopt_release_buffers(void) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) { (void)cudaGetLastError(); return SHOPT_E_NODEVICE; }
+    if (g_ctx[dev].dev == dev) g_ctx[dev].release_cache();
     return SHOPT_OK;
 }
 

@@ -18,6 +18,13 @@ struct Ctx {
     double ms[3] = {0, 0, 0};
     void *scratch = nullptr;                 // grow-only device scratch of the _dev building blocks
     size_t scratch_bytes = 0;
+    // grow-only device blocks of the host entry points (stamp cube, pixel-grid cube, ...): allocating and freeing tens
+    // of GB per call costs tens of milliseconds; shopt_release_buffers() gives them back
+    static constexpr int NCACHE = 4;
+    void *cache[NCACHE] = {};
+    size_t cache_bytes[NCACHE] = {};
+    int need_cache(int i, size_t bytes, void **out);
+    void release_cache();
     unsigned long long *next_counter() { return counter + (slot++ & 7u); }
     // Work on a context is stream-ordered by the caller; growing frees the old block only after the device is idle.
     int need_scratch(size_t bytes);
@@ -36,6 +43,11 @@ struct DevBuf {
         if (e != cudaSuccess) { p = nullptr; set_last_error("cudaMalloc", e); (void)cudaGetLastError(); return SHOPT_E_NOMEM; }
         return SHOPT_OK;
     }
+    template <class T> T *as() const { return static_cast<T *>(p); }
+};
+// non-owning view with DevBuf's accessor (blocks that live in the context's cache)
+struct RawBuf {
+    void *p = nullptr;
     template <class T> T *as() const { return static_cast<T *>(p); }
 };
 #define TRY(expr) do { int _rc = (expr); if (_rc != SHOPT_OK) return _rc; } while (0)

@@ -2,7 +2,10 @@
 // control flow of shopt/shopt.jl:130-184, 281-314, 357-417, 472-577 around the kernels, for one GPU or one shard of a
 // multi-GPU run (the caller supplies the all-reduce).
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <numeric>
 #include <vector>
 
@@ -139,6 +142,21 @@ static size_t stage_scratch_bytes(const shopt_params *p, const shopt_stage_io *i
                     polyfit_scratch_bytes((long long)io->r * io->c, io->n_local, p->degree));
 }
 
+// SHOPT_TRACE=1: host wall-clock milestones of one stage call on stderr (tracing aid; off by default)
+struct StageTrace {
+    bool on = getenv("SHOPT_TRACE") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now(), last = t0;
+    void mark(const char *what, cudaStream_t st) {
+        if (!on) return;
+        cudaStreamSynchronize(st);
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[shopt trace] %-28s +%8.3f ms  (total %8.3f ms)\n", what,
+                std::chrono::duration<double, std::milli>(now - last).count(),
+                std::chrono::duration<double, std::milli>(now - t0).count());
+        last = now;
+    }
+};
+
 // The stage on a device-resident shard.  d_tmp: 3 ints per star (fit status | fit iterations | pca status);
 // per_star_done: the caller has already enqueued stage_per_star() for every star on `st` (the pipelined host path).
 static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream,
@@ -159,6 +177,8 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
     if (!per_star_done) TRY(stage_per_star(p, io, 0, n, d_tmp, ctx, st));
     if (n > 0) flag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(m, d_pst, l, n, p->s_lo, p->s_hi, io->flags);
     SHOPT_CUDA_TRY(cudaGetLastError());
+    StageTrace tr;
+    tr.mark("per-star kernels + flags", st);
     std::vector<int> flags((size_t)n);
     SHOPT_CUDA_TRY(cudaMemcpyAsync(flags.data(), io->flags, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
@@ -173,6 +193,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
         SHOPT_CUDA_TRY(cudaMemcpyAsync(gflag.data(), dkeep.p, (size_t)NG * 4, cudaMemcpyDeviceToHost, st));
         SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
     }
+    tr.mark("flag gather", st);
     long long n_black = 0, n_failed = 0, n_surv = 0;
     for (long long g = 0; g < NG; g++) {
         const int f = gflag[(size_t)g] & 31;
@@ -197,6 +218,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
         SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
         io->field_rank = field_solve_normal(h, h + 100, 3, io->field);
     }
+    tr.mark("field fit", st);
     // ---- training split: first round(training_ratio * n_surv) survivors in perm order (shopt.jl:472-478) ----
     for (auto &f : gflag) f &= 31;
     std::vector<int64_t> train((size_t)std::max<long long>(n_surv, 1));   // global star ids, training order
@@ -205,6 +227,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
     train.resize((size_t)n_train);
     for (int64_t g : train) if (g >= off && g < off + n) flags[(size_t)(g - off)] |= SHOPT_FLAG_TRAINING;
 
+    tr.mark("training split", st);
     // ---- polyfit rounds (shopt.jl:534-577) ----
     const long long acc_len = (long long)K * K + (long long)K * rc;
     TRY(dacc.alloc((size_t)acc_len * 8)); TRY(didx.alloc((size_t)std::max<long long>(n, 1) * 8));
@@ -240,6 +263,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
             if (!comm && !p->median_constraint)
                 TRY(polyfit_median_launch(io->pgf, rc, io->u, io->v, didx.as<long long>(), nl, p->degree, 2,
                                           dacc.as<double>(), nullptr, st));
+            tr.mark("  normal + all-reduce", st);
             TRY(polyfit_solve_launch(dacc.as<double>(), rc, p->degree, io->poly, dinfo.as<int>(), st));
             if (p->median_constraint) {
                 TRY(polyfit_median_launch(io->pgf, rc, io->u, io->v, didx.as<long long>(), nl, p->degree, 1, nullptr,
@@ -252,6 +276,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
         lerr.resize((size_t)nl);
         SHOPT_CUDA_TRY(cudaMemcpyAsync(lerr.data(), dmse.p, (size_t)nl * 8, cudaMemcpyDeviceToHost, st));
         SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+        tr.mark("  solve + mse", st);
         err.assign((size_t)nc, 0.0);
         for (long long i = 0; i < nl; i++) err[(size_t)lpos[(size_t)i]] = lerr[(size_t)i];
         if (comm && nc > 0) {                        // zero-padded gather of the per-star errors
@@ -260,6 +285,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
             SHOPT_CUDA_TRY(cudaMemcpyAsync(err.data(), dmse.p, (size_t)nc * 8, cudaMemcpyDeviceToHost, st));
             SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
         }
+        tr.mark("  error gather", st);
         if (loop < p->iterations) {                  // shopt.jl:557-575; the last round's selection is not applied
             bad.resize((size_t)std::max<long long>(nc, 1));
             const int64_t nbad = shopt_worst_10_percent(err.data(), nc, p->sigma_clip, bad.data());
@@ -274,6 +300,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, shopt_allre
             cur.resize(mkeep);
         }
     }
+    tr.mark("rounds done", st);
     SHOPT_CUDA_TRY(cudaMemcpyAsync(io->flags, flags.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
     SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
     io->counts[0] = n_black; io->counts[1] = n_failed; io->counts[2] = (int64_t)train.size(); io->counts[3] = (int64_t)cur.size();
@@ -295,16 +322,21 @@ int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allredu
 
 // Host buffers, one GPU.  The stamps go up in chunks on a copy stream while the per-star kernels of the chunks that
 // have landed run on the compute stream, so the H2D transfer (13.7 GB at 100k x 131 x 131) hides behind the fits.
-int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) {
+int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) { return shopt_stage_run_comm(p, io, nullptr, nullptr); }
+
+int shopt_stage_run_comm(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user) {
     if (!p || !io || !io->stamps || !io->u || !io->v || !io->x0_model || !io->x0_learned || !io->model || !io->learned ||
         !io->flags || !io->poly)
         return SHOPT_E_BADARG;
-    if (io->r < 1 || io->c < 2 || io->n_local < 0 || io->n_global != io->n_local || io->offset != 0) return SHOPT_E_BADARG;
+    if (io->r < 1 || io->c < 2 || io->n_local < 0) return SHOPT_E_BADARG;
+    if (!comm && (io->n_global != io->n_local || io->offset != 0)) return SHOPT_E_BADARG;
     Ctx *ctx; TRY(get_ctx(&ctx));
     const size_t n = (size_t)io->n_local, rc = (size_t)io->r * io->c, nn = std::max<size_t>(n, 1);
     const size_t K = (size_t)(p->degree + 1) * (p->degree + 2) / 2;
-    DevBuf dst, dpgf, dsm, dout, dint, dpoly, dtmp;
-    TRY(dst.alloc(nn * rc * 8)); TRY(dpgf.alloc(nn * rc * 8)); TRY(dsm.alloc(nn * 8 * 8)); TRY(dout.alloc(nn * 6 * 8));
+    DevBuf dsm, dout, dint, dpoly, dtmp;
+    RawBuf dst, dpgf;
+    TRY(ctx->need_cache(0, nn * rc * 8, &dst.p)); TRY(ctx->need_cache(1, nn * rc * 8, &dpgf.p));
+    TRY(dsm.alloc(nn * 8 * 8)); TRY(dout.alloc(nn * 6 * 8));
     TRY(dint.alloc(nn * 8)); TRY(dpoly.alloc(K * rc * 8)); TRY(dtmp.alloc(nn * 12));
     DevBuf dw, dx0p;                                 // mode chisq only
     const bool chisq = p->mode == SHOPT_MODE_CHISQ;
@@ -345,7 +377,7 @@ int shopt_stage_run(const shopt_params *p, shopt_stage_io *io) {
         TRY(stage_per_star(p, &d, first, count, dtmp.as<int>(), ctx, st));
     }
     SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[1], cs));    // last stamp on the device
-    TRY(stage_run_impl(p, &d, nullptr, nullptr, st, dtmp.as<int>(), true));
+    TRY(stage_run_impl(p, &d, comm, comm_user, st, dtmp.as<int>(), true));
     SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[2], st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(io->model, d.model, n * 24, cudaMemcpyDeviceToHost, st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(io->learned, d.learned, n * 24, cudaMemcpyDeviceToHost, st));

@@ -65,7 +65,12 @@ def make_allreduce(group=None):
     def _cb(ptr, count, dtype, stream, user):
         try:
             t = torch.as_tensor(_DevView(ptr, count, dtype), device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+            cur = torch.cuda.current_stream()
+            if stream and int(stream) != cur.cuda_stream:    # the library's own stream (host entry points)
+                with torch.cuda.stream(torch.cuda.ExternalStream(int(stream))):
+                    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+            else:
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
             return 0
         except Exception as e:      # never let an exception cross the C boundary
             print("shopt_b200 all-reduce failed:", e)
@@ -112,8 +117,12 @@ def run_stage_dev(params, stamps, u, v, x0_model, x0_learned, perm, n_global=Non
     return out
 
 
-def run_stage(params, stamps, u, v, x0_model, x0_learned, perm, want_pgf=True, weights=None, x0_pixels=None):
-    """Host arrays, one GPU (H2D, stage, D2H inside the call): stamps (N, c, r), u, v (N), x0_* (N, 3), perm (N)."""
+def run_stage(params, stamps, u, v, x0_model, x0_learned, perm, want_pgf=True, weights=None, x0_pixels=None,
+              n_global=None, offset=0, group=None):
+    """Host arrays (H2D, stage, D2H inside the call): stamps (N, c, r), u, v (N), x0_* (N, 3), perm (n_global).
+    One GPU by default; with torch.distributed initialised and n_global / offset given, the arrays are this rank's
+    shard of a sharded run (shopt_stage_run_comm)."""
+    import ctypes as C
     f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
     stamps, u, v, x0_model, x0_learned = f(stamps), f(u), f(v), f(x0_model), f(x0_learned)
     perm = np.ascontiguousarray(perm, dtype=np.int64)
@@ -131,7 +140,14 @@ def run_stage(params, stamps, u, v, x0_model, x0_learned, perm, want_pgf=True, w
                       pca_k=out["pca_k"].ctypes.data, poly=out["poly"].ctypes.data, n_per_round=npr.ctypes.data,
                       weights=weights.ctypes.data if weights is not None else None,
                       x0_pixels=x0_pixels.ctypes.data if x0_pixels is not None else None)
-    check(_lib.lib().shopt_stage_run(C.byref(params), C.byref(io)))
+    if n_global is not None and n_global != N:
+        import torch.distributed as dist
+        assert dist.is_initialized() and len(perm) == n_global
+        io.n_global, io.offset = n_global, offset
+        cb = make_allreduce(group)
+        check(_lib.lib().shopt_stage_run_comm(C.byref(params), C.byref(io), C.cast(cb, C.c_void_p), None))
+    else:
+        check(_lib.lib().shopt_stage_run(C.byref(params), C.byref(io)))
     out["n_per_round"] = npr[:params.iterations].copy()
     out["counts"] = dict(zip(("blacklisted", "failed", "training", "kept"), list(io.counts)))
     out["field"] = np.array(io.field).reshape(3, 10)     # s(u,v), g1(u,v), g2(u,v): shopt.jl:422-466
