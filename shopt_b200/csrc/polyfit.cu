@@ -19,6 +19,8 @@
 //   solve_kernel   equilibrated Cholesky of G in shared memory, then one thread per pixel back-substitutes;
 //   mse_kernel     same tiling as normal_kernel with the K*PX coefficients of the thread's pixels in registers;
 //                  per-star partial sums per pixel tile, reduced in tile order by mse_reduce_kernel.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -44,6 +46,7 @@ __device__ __forceinline__ void basis_eval(double u, double v, double *b) {
 }
 
 constexpr int POLY_THREADS = 128;
+constexpr int POLY_CFG_DEFAULT = 2;   // 4 pixels per thread (K <= 10), star loop unrolled by 4: normal_kernel 2.98 -> 2.71 ms
 constexpr int SCHUNK = 64;   // stars staged per shared-memory refill
 
 template <int DEG> struct PolyCfg {
@@ -56,17 +59,17 @@ template <int DEG> struct PolyCfg {
 // G = V'V and B = V'P partials
 // part layout: [chunk][K*K + K*rc]
 // ---------------------------------------------------------------------------------------------
-template <int DEG>
+template <int DEG, int PX, int UNR>
 __global__ void __launch_bounds__(POLY_THREADS) normal_kernel(const double *__restrict__ pgf, long long rc,
                                                               const double *__restrict__ u, const double *__restrict__ v,
                                                               const long long *__restrict__ idx, long long n,
                                                               long long per_chunk, double *__restrict__ part) {
-    constexpr int K = PolyCfg<DEG>::K, PX = PolyCfg<DEG>::PX;
+    constexpr int K = PolyCfg<DEG>::K;
     __shared__ double sV[SCHUNK][K];
     __shared__ long long sOff[SCHUNK];
     const long long t0 = (long long)blockIdx.y * per_chunk;
     const long long t1 = (t0 + per_chunk < n) ? t0 + per_chunk : n;
-    const long long px0 = (long long)blockIdx.x * PolyCfg<DEG>::TILE + threadIdx.x;
+    const long long px0 = (long long)blockIdx.x * (POLY_THREADS * PX) + threadIdx.x;
     double acc[K][PX];
 #pragma unroll
     for (int k = 0; k < K; k++)
@@ -84,7 +87,7 @@ __global__ void __launch_bounds__(POLY_THREADS) normal_kernel(const double *__re
             sOff[threadIdx.x] = star * rc;
         }
         __syncthreads();
-#pragma unroll 2
+#pragma unroll UNR
         for (int s = 0; s < m; s++) {
             const double *row = pgf + sOff[s];
             double z[PX];
@@ -224,19 +227,19 @@ __global__ void __launch_bounds__(128) solve_kernel(const double *__restrict__ a
 // ---------------------------------------------------------------------------------------------
 // per-star reconstruction error: part[tile][t] = sum over the tile's pixels of (sum_k poly[px,k] V[t,k] - pgf[t,px])^2
 // ---------------------------------------------------------------------------------------------
-template <int DEG>
+template <int DEG, int PX, int UNR>
 __global__ void __launch_bounds__(POLY_THREADS) mse_kernel(const double *__restrict__ pgf, long long rc,
                                                            const double *__restrict__ u, const double *__restrict__ v,
                                                            const long long *__restrict__ idx, long long n,
                                                            long long per_chunk, const double *__restrict__ poly,
                                                            double *__restrict__ part) {
-    constexpr int K = PolyCfg<DEG>::K, PX = PolyCfg<DEG>::PX, NW = POLY_THREADS / 32;
+    constexpr int K = PolyCfg<DEG>::K, NW = POLY_THREADS / 32;
     __shared__ double sV[SCHUNK][K];
     __shared__ long long sOff[SCHUNK];
     __shared__ double sE[SCHUNK][NW];
     const long long t0 = (long long)blockIdx.y * per_chunk;
     const long long t1 = (t0 + per_chunk < n) ? t0 + per_chunk : n;
-    const long long px0 = (long long)blockIdx.x * PolyCfg<DEG>::TILE + threadIdx.x;
+    const long long px0 = (long long)blockIdx.x * (POLY_THREADS * PX) + threadIdx.x;
     double cf[K][PX];
     bool live[PX];
 #pragma unroll
@@ -259,27 +262,45 @@ __global__ void __launch_bounds__(POLY_THREADS) mse_kernel(const double *__restr
             sOff[threadIdx.x] = star * rc;
         }
         __syncthreads();
-#pragma unroll 2
-        for (int s = 0; s < m; s++) {
-            const double *row = pgf + sOff[s];
-            double val[PX];
+        // eight stars at a time: their per-thread partial errors are reduced across the warp by ONE halving tree
+        // (9 shuffles per 8 stars instead of 40), value q landing on lane 4 q
+        for (int s0 = 0; s0 < m; s0 += 8) {
+            double e8[8];
 #pragma unroll
-            for (int j = 0; j < PX; j++) {
-                const long long px = px0 + (long long)j * POLY_THREADS;
-                val[j] = live[j] ? -__ldg(row + px) : 0.0;
+            for (int q = 0; q < 8; q++) {
+                const int s = (s0 + q < m) ? s0 + q : m - 1;   // a ragged tail re-reads the last star (result unused)
+                double e = 0.0;
+                {
+                    const double *row = pgf + sOff[s];
+                    double val[PX];
+#pragma unroll
+                    for (int j = 0; j < PX; j++) {
+                        const long long px = px0 + (long long)j * POLY_THREADS;
+                        val[j] = live[j] ? -__ldg(row + px) : 0.0;
+                    }
+#pragma unroll
+                    for (int k = 0; k < K; k++) {
+                        const double vk = sV[s][k];
+#pragma unroll
+                        for (int j = 0; j < PX; j++) val[j] = fma(cf[k][j], vk, val[j]);
+                    }
+#pragma unroll
+                    for (int j = 0; j < PX; j++) e = fma(val[j], val[j], e);
+                }
+                e8[q] = e;
             }
+            const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+            double k4[4], k2[2];
 #pragma unroll
-            for (int k = 0; k < K; k++) {
-                const double vk = sV[s][k];
+            for (int i = 0; i < 4; i++)
+                k4[i] = (b4 ? e8[i + 4] : e8[i]) + __shfl_xor_sync(0xffffffffu, b4 ? e8[i] : e8[i + 4], 16);
 #pragma unroll
-                for (int j = 0; j < PX; j++) val[j] = fma(cf[k][j], vk, val[j]);
-            }
-            double e = 0.0;
-#pragma unroll
-            for (int j = 0; j < PX; j++) e = fma(val[j], val[j], e);
-#pragma unroll
-            for (int o = 16; o >= 1; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
-            if (lane == 0) sE[s][warp] = e;
+            for (int i = 0; i < 2; i++)
+                k2[i] = (b3 ? k4[i + 2] : k4[i]) + __shfl_xor_sync(0xffffffffu, b3 ? k4[i] : k4[i + 2], 8);
+            double tot = (b2 ? k2[1] : k2[0]) + __shfl_xor_sync(0xffffffffu, b2 ? k2[0] : k2[1], 4);
+            tot += __shfl_xor_sync(0xffffffffu, tot, 2);
+            tot += __shfl_xor_sync(0xffffffffu, tot, 1);
+            if ((lane & 3) == 0 && s0 + (lane >> 2) < m) sE[s0 + (lane >> 2)][warp] = tot;
         }
         __syncthreads();
         if (threadIdx.x < m) {
@@ -510,23 +531,45 @@ static int pick_chunks(long long n, int tiles) {
     return (int)want;
 }
 
-template <int DEG>
-static int normal_launch_t(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+// Tiling variants of the two streaming kernels: pixels per thread x star-loop unroll.  SHOPT_POLY_CFG (0..3) selects one
+// for measurements; the default is the fastest measured on B200 (profiles/README.md).
+static int poly_cfg() {
+    static int cfg = -1;
+    if (cfg < 0) { const char *e = getenv("SHOPT_POLY_CFG"); cfg = e ? atoi(e) & 3 : POLY_CFG_DEFAULT; }
+    return cfg;
+}
+static int poly_px(int K, int cfg) {
+    const int base = (K <= 10) ? 4 : (K <= 21 ? 2 : 1);
+    return (cfg & 1) ? (base > 1 ? base / 2 : 1) : base;
+}
+template <int DEG, int PX, int UNR>
+static int normal_launch_v(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
                            long long n, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
     constexpr int K = PolyCfg<DEG>::K;
     const long long len = (long long)K * K + (long long)K * rc;
     if (n == 0) { SHOPT_CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)len * 8, st)); return SHOPT_OK; }
-    const int tiles = (int)((rc + PolyCfg<DEG>::TILE - 1) / PolyCfg<DEG>::TILE);
+    const int tiles = (int)((rc + POLY_THREADS * PX - 1) / (POLY_THREADS * PX));
     int nchunk = pick_chunks(n, tiles);
     while (nchunk > 1 && (size_t)nchunk * len * 8 > scratch_bytes) nchunk--;
     if ((size_t)nchunk * len * 8 > scratch_bytes) return SHOPT_E_NOMEM;
     const long long per_chunk = (n + nchunk - 1) / nchunk;
     nchunk = (int)((n + per_chunk - 1) / per_chunk);
-    normal_kernel<DEG><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, idx, n, per_chunk, scratch);
+    normal_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, idx, n, per_chunk, scratch);
     gram_kernel<DEG><<<nchunk, POLY_THREADS, 0, st>>>(u, v, idx, n, per_chunk, rc, scratch);
     reduce_kernel<<<(unsigned)((len + 255) / 256), 256, 0, st>>>(scratch, len, nchunk, acc);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
+}
+template <int DEG>
+static int normal_launch_t(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+                           long long n, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
+    constexpr int P0 = PolyCfg<DEG>::PX, P1 = (P0 > 1 ? P0 / 2 : 1);
+    switch (poly_cfg()) {
+        case 0: return normal_launch_v<DEG, P0, 2>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st);
+        case 1: return normal_launch_v<DEG, P1, 2>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st);
+        case 2: return normal_launch_v<DEG, P0, 4>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st);
+        default: return normal_launch_v<DEG, P1, 4>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st);
+    }
 }
 template <int DEG>
 static int solve_launch_t(const double *acc, long long rc, double *poly, int *info, cudaStream_t st) {
@@ -535,20 +578,32 @@ static int solve_launch_t(const double *acc, long long rc, double *poly, int *in
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
-template <int DEG>
-static int mse_launch_t(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+template <int DEG, int PX, int UNR>
+static int mse_launch_v(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
                         long long n, const double *poly, double *mse, double *scratch, size_t scratch_bytes,
                         cudaStream_t st) {
     if (n == 0) return SHOPT_OK;
-    const int tiles = (int)((rc + PolyCfg<DEG>::TILE - 1) / PolyCfg<DEG>::TILE);
+    const int tiles = (int)((rc + POLY_THREADS * PX - 1) / (POLY_THREADS * PX));
     if ((size_t)tiles * n * 8 > scratch_bytes) return SHOPT_E_NOMEM;
     int nchunk = pick_chunks(n, tiles);
     const long long per_chunk = ((n + nchunk - 1) / nchunk + SCHUNK - 1) / SCHUNK * SCHUNK;
     nchunk = (int)((n + per_chunk - 1) / per_chunk);
-    mse_kernel<DEG><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, idx, n, per_chunk, poly, scratch);
+    mse_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, idx, n, per_chunk, poly, scratch);
     mse_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(scratch, n, tiles, 1.0 / (double)rc, mse);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
+}
+template <int DEG>
+static int mse_launch_t(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
+                        long long n, const double *poly, double *mse, double *scratch, size_t scratch_bytes,
+                        cudaStream_t st) {
+    constexpr int P0 = PolyCfg<DEG>::PX, P1 = (P0 > 1 ? P0 / 2 : 1);
+    switch (poly_cfg()) {
+        case 0: return mse_launch_v<DEG, P0, 2>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st);
+        case 1: return mse_launch_v<DEG, P1, 2>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st);
+        case 2: return mse_launch_v<DEG, P0, 4>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st);
+        default: return mse_launch_v<DEG, P1, 4>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st);
+    }
 }
 template <int DEG>
 static int psf_launch_t(const double *poly, long long rc, const double *u, const double *v, long long M, double *out,
@@ -576,7 +631,7 @@ static int psf_launch_t(const double *poly, long long rc, const double *u, const
 size_t polyfit_scratch_bytes(long long rc, long long n, int degree) {
     const long long K = num_terms(degree);
     const long long len = K * K + K * rc;
-    const int px = (K <= 10) ? 4 : (K <= 21 ? 2 : 1);
+    const int px = poly_px((int)K, 1);                      // the smaller tile of the variants: the larger scratch
     const int tiles = (int)((rc + POLY_THREADS * px - 1) / (POLY_THREADS * px));
     const size_t a = (size_t)pick_chunks(n > 0 ? n : 1, tiles) * len * 8;
     const size_t b = (size_t)tiles * (n > 0 ? n : 1) * 8;
