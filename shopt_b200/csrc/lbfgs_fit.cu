@@ -16,6 +16,7 @@
 // control flow stays uniform.  The manifold reparameterisation [sigma,e1,e2] -> [s,g1,g2] is evaluated with
 // explicitly rounded operations (no FMA contraction) in the same operation order as the reference's
 // expression, because that expression amplifies round-off by 1/|e|^4.
+#include <cstdlib>
 #include <type_traits>
 #include "common.cuh"
 
@@ -154,6 +155,18 @@ constexpr int SC_DOUBLES = 16;   // one broadcast block of the scalar section
 constexpr int LBFGS_M = 10;
 enum { CMD_EVAL = 1, CMD_EXIT = 2 };
 
+// one trial point of the line search: step, value, slope, serial number
+struct Pt {
+    double a, v, s;
+    int id;
+};
+enum { S_P0 = 0, S_LAST, S_PREVOK, S_IA, S_IB, S_A, S_B, S_C, S_NA, S_NB, S_U, S_V, S_W, S_JA, S_JB, S_T1, S_T2, S_NSLOT };
+struct LsShared {
+    Pt pt[S_NSLOT];
+    double x[3], s[3], phi_0, dphi_0, phi_lim;
+    int npts, err, ntrials;
+};
+
 // Per-CTA state in shared memory (offset 0 of the dynamic shared memory).  Everything the scalar optimiser code keeps
 // between evaluations lives here or in registers: the 126 KB of L1 left beside three CTAs' crops cannot hold
 // per-thread stacks, and local-memory traffic was what bounded the first version of this kernel (profiles/).
@@ -161,6 +174,8 @@ struct EvalShared {
     double sc[SC_DOUBLES];             // broadcast of the dual-number scalar section (master -> everyone)
     double xl[3], fl, gl[3];           // NLSolversBase caches the last evaluated point by value
     double hist_dx[LBFGS_M][3], hist_dg[LBFGS_M][3], hist_rho[LBFGS_M], hist_alpha[LBFGS_M];
+    double vx[3], vxp[3], vg[3], vgp[3], vs[3], vdx[3], vdg[3];   // LBFGS iterate, gradient, direction, differences
+    LsShared ls;                       // line-search points and base point / direction
     uint32_t crop_s, fbuf_s;           // shared-space byte addresses: staged crop, profile plane (same indexing)
     int n_a, pitch, TV, m0, rodd, plane, have_last, cmd;
 };
@@ -383,10 +398,6 @@ __device__ __forceinline__ void worker_loop() {
 // algorithm makes of older history is "the most recent earlier point with phi <= phi_lim" during
 // bracketing, which is tracked incrementally.
 // ---------------------------------------------------------------------------------------------
-struct Pt {
-    double a, v, s;
-    int id;
-};
 enum { HZ_OK = 0, HZ_LSEXC = 1, HZ_ERROR = 2 };
 
 __device__ __forceinline__ double eps_of(double b) {   // Julia eps(x::Float64)
@@ -399,184 +410,183 @@ __device__ __forceinline__ double eps_of(double b) {   // Julia eps(x::Float64)
 }
 __device__ __forceinline__ double nextfloat_(double x) { return nextafter(x, (double)INFINITY); }
 
+// The trial points live in SHARED memory slots and the routines pass slot numbers, like the index-into-history style
+// of LineSearches.jl itself.  eval_fg is a real call (one copy of the evaluator instead of one per call site), and every
+// value that is live in registers across a call is saved to the local stack by the ABI: with the points in registers
+// that was 20 % of the master's instructions, each an L1 miss (the L1 left beside three CTAs' crops is a few KB).
+
 template <int THREADS>
 struct LineSearch {
-    double x[3], s[3];
-    double phi_0, dphi_0, phi_lim;
-    int npts;
-    bool err;
-    int ntrials;
-
-    __device__ LineSearch() : npts(0), err(false), ntrials(0) {}
-
-    __device__ __forceinline__ void phidphi(double alpha, double &phi, double &dphi) {
-        const FG r = eval_fg<THREADS>(add_(x[0], mul_(alpha, s[0])), add_(x[1], mul_(alpha, s[1])), add_(x[2], mul_(alpha, s[2])));
+    __device__ __forceinline__ static void phidphi(LsShared &L, double alpha, double &phi, double &dphi) {
+        const FG r = eval_fg<THREADS>(add_(L.x[0], mul_(alpha, L.s[0])), add_(L.x[1], mul_(alpha, L.s[1])),
+                                      add_(L.x[2], mul_(alpha, L.s[2])));
         phi = r.f;
-        dphi = add_(add_(mul_(r.g0, s[0]), mul_(r.g1, s[1])), mul_(r.g2, s[2]));
-        ntrials++;
+        dphi = add_(add_(mul_(r.g0, L.s[0]), mul_(r.g1, L.s[1])), mul_(r.g2, L.s[2]));
+        L.ntrials++;
     }
-    __device__ __forceinline__ Pt push(double a, double v, double sl) {
-        Pt p = {a, v, sl, npts};
-        npts++;
-        return p;
+    __device__ __forceinline__ static void push(LsShared &L, int slot, double a, double v, double sl) {
+        L.pt[slot].a = a; L.pt[slot].v = v; L.pt[slot].s = sl; L.pt[slot].id = L.npts;
+        L.npts++;
     }
-    __device__ __forceinline__ bool wolfe(double c, double phi_c, double dphi_c) const {
+    __device__ __forceinline__ static void copy(LsShared &L, int dst, int src) {
+        if (dst != src) L.pt[dst] = L.pt[src];
+    }
+    __device__ __forceinline__ static bool wolfe(const LsShared &L, double c, double phi_c, double dphi_c) {
         const double delta = 0.1, sigma = 0.9;
-        bool w1 = (mul_(delta, dphi_0) >= div_(sub_(phi_c, phi_0), c)) && (dphi_c >= mul_(sigma, dphi_0));
-        bool w2 = (mul_(sub_(mul_(2.0, delta), 1.0), dphi_0) >= dphi_c) && (dphi_c >= mul_(sigma, dphi_0)) &&
-                  (phi_c <= phi_lim);
+        bool w1 = (mul_(delta, L.dphi_0) >= div_(sub_(phi_c, L.phi_0), c)) && (dphi_c >= mul_(sigma, L.dphi_0));
+        bool w2 = (mul_(sub_(mul_(2.0, delta), 1.0), L.dphi_0) >= dphi_c) && (dphi_c >= mul_(sigma, L.dphi_0)) &&
+                  (phi_c <= L.phi_lim);
         return w1 || w2;
     }
-    // HZ stage U3 (theta = 1/2)
-    __device__ void bisect(Pt ia, Pt ib, Pt &oa, Pt &ob) {
-        double a = ia.a, b = ib.a;
-        if (!(ia.s < 0.0) || !(ia.v <= phi_lim) || !(ib.s < 0.0) || !(ib.v > phi_lim) || !(b > a)) {
-            err = true; oa = ia; ob = ib; return;
+    // HZ stage U3 (theta = 1/2); inputs ia, ib, outputs oa, ob (slots; outputs may alias inputs)
+    __device__ static void bisect(LsShared &L, int ia, int ib, int oa, int ob) {
+        copy(L, S_T1, ia); copy(L, S_T2, ib);
+        {
+            const Pt &A = L.pt[S_T1], &B = L.pt[S_T2];
+            if (!(A.s < 0.0) || !(A.v <= L.phi_lim) || !(B.s < 0.0) || !(B.v > L.phi_lim) || !(B.a > A.a)) {
+                L.err = 1; copy(L, oa, S_T1); copy(L, ob, S_T2); return;
+            }
         }
-        while (sub_(b, a) > eps_of(b)) {
-            double d = div_(add_(a, b), 2.0), phi_d, g;
-            phidphi(d, phi_d, g);
-            if (!(isfinite(phi_d) && isfinite(g))) { err = true; break; }
-            Pt id = push(d, phi_d, g);
-            if (g >= 0.0) { oa = ia; ob = id; return; }
-            if (phi_d <= phi_lim) { a = d; ia = id; } else { b = d; ib = id; }
+        while (sub_(L.pt[S_T2].a, L.pt[S_T1].a) > eps_of(L.pt[S_T2].a)) {
+            const double d = div_(add_(L.pt[S_T1].a, L.pt[S_T2].a), 2.0);
+            double phi_d, g;
+            phidphi(L, d, phi_d, g);
+            if (!(isfinite(phi_d) && isfinite(g))) { L.err = 1; break; }
+            if (g >= 0.0) { copy(L, oa, S_T1); push(L, ob, d, phi_d, g); return; }
+            if (phi_d <= L.phi_lim) push(L, S_T1, d, phi_d, g); else push(L, S_T2, d, phi_d, g);
         }
-        oa = ia; ob = ib;
+        copy(L, oa, S_T1); copy(L, ob, S_T2);
     }
-    // HZ stages U0-U3
-    __device__ void update(Pt ia, Pt ib, Pt ic, Pt &oa, Pt &ob) {
-        double a = ia.a, b = ib.a;
-        if (!(ia.s < 0.0) || !(ia.v <= phi_lim) || !(ib.s >= 0.0) || !(b > a)) {
-            err = true; oa = ia; ob = ib; return;
+    // HZ stages U0-U3; outputs must not alias the inputs
+    __device__ static void update(LsShared &L, int ia, int ib, int ic, int oa, int ob) {
+        const double a = L.pt[ia].a, b = L.pt[ib].a;
+        if (!(L.pt[ia].s < 0.0) || !(L.pt[ia].v <= L.phi_lim) || !(L.pt[ib].s >= 0.0) || !(b > a)) {
+            L.err = 1; copy(L, oa, ia); copy(L, ob, ib); return;
         }
-        if (ic.a < a || ic.a > b) { oa = ia; ob = ib; return; }
-        if (ic.s >= 0.0) { oa = ia; ob = ic; return; }
-        if (ic.v <= phi_lim) { oa = ic; ob = ib; return; }
-        bisect(ia, ic, oa, ob);
+        const double ca = L.pt[ic].a;
+        if (ca < a || ca > b) { copy(L, oa, ia); copy(L, ob, ib); return; }
+        if (L.pt[ic].s >= 0.0) { copy(L, oa, ia); copy(L, ob, ic); return; }
+        if (L.pt[ic].v <= L.phi_lim) { copy(L, oa, ic); copy(L, ob, ib); return; }
+        bisect(L, ia, ic, oa, ob);
     }
     __device__ __forceinline__ static double secant(double a, double b, double dphi_a, double dphi_b) {
         return div_(sub_(mul_(a, dphi_b), mul_(b, dphi_a)), sub_(dphi_b, dphi_a));
     }
-    // HZ stages S1-S4; returns iswolfe
-    __device__ bool secant2(Pt ia, Pt ib, Pt &oA, Pt &oB) {
-        oA = ia; oB = ib;
-        if (!(ia.s < 0.0 && ib.s >= 0.0)) { err = true; return false; }
-        double c = secant(ia.a, ib.a, ia.s, ib.s);
-        if (!isfinite(c)) { err = true; return false; }
+    // HZ stages S1-S4 on (S_IA, S_IB) -> (S_A, S_B); returns iswolfe
+    __device__ static bool secant2(LsShared &L) {
+        copy(L, S_A, S_IA); copy(L, S_B, S_IB);
+        if (!(L.pt[S_IA].s < 0.0 && L.pt[S_IB].s >= 0.0)) { L.err = 1; return false; }
+        double c = secant(L.pt[S_IA].a, L.pt[S_IB].a, L.pt[S_IA].s, L.pt[S_IB].s);
+        if (!isfinite(c)) { L.err = 1; return false; }
         double phi_c, dphi_c;
-        phidphi(c, phi_c, dphi_c);
-        if (!(isfinite(phi_c) && isfinite(dphi_c))) { err = true; return false; }
-        Pt ic = push(c, phi_c, dphi_c);
-        if (wolfe(c, phi_c, dphi_c)) { oA = ic; oB = ic; return true; }
-        Pt iA, iB;
-        update(ia, ib, ic, iA, iB);
-        if (err) return false;
-        const double a = iA.a, b = iB.a;
-        const bool movedB = (iB.id == ic.id), movedA = (iA.id == ic.id);
-        if (movedB) c = secant(ib.a, iB.a, ib.s, iB.s);
-        else if (movedA) c = secant(ia.a, iA.a, ia.s, iA.s);
+        phidphi(L, c, phi_c, dphi_c);
+        if (!(isfinite(phi_c) && isfinite(dphi_c))) { L.err = 1; return false; }
+        push(L, S_W, c, phi_c, dphi_c);
+        if (wolfe(L, c, phi_c, dphi_c)) { copy(L, S_A, S_W); copy(L, S_B, S_W); return true; }
+        update(L, S_IA, S_IB, S_W, S_U, S_V);
+        if (L.err) return false;
+        const double a = L.pt[S_U].a, b = L.pt[S_V].a;
+        const bool movedB = (L.pt[S_V].id == L.pt[S_W].id), movedA = (L.pt[S_U].id == L.pt[S_W].id);
+        if (movedB) c = secant(L.pt[S_IB].a, L.pt[S_V].a, L.pt[S_IB].s, L.pt[S_V].s);
+        else if (movedA) c = secant(L.pt[S_IA].a, L.pt[S_U].a, L.pt[S_IA].s, L.pt[S_U].s);
         if ((movedA || movedB) && a <= c && c <= b) {
-            phidphi(c, phi_c, dphi_c);
-            if (!(isfinite(phi_c) && isfinite(dphi_c))) { err = true; return false; }
-            ic = push(c, phi_c, dphi_c);
-            if (wolfe(c, phi_c, dphi_c)) { oA = ic; oB = ic; return true; }
-            Pt jA, jB;
-            update(iA, iB, ic, jA, jB);
-            if (err) return false;
-            iA = jA; iB = jB;
+            phidphi(L, c, phi_c, dphi_c);
+            if (!(isfinite(phi_c) && isfinite(dphi_c))) { L.err = 1; return false; }
+            push(L, S_W, c, phi_c, dphi_c);
+            if (wolfe(L, c, phi_c, dphi_c)) { copy(L, S_A, S_W); copy(L, S_B, S_W); return true; }
+            update(L, S_U, S_V, S_W, S_JA, S_JB);
+            if (L.err) return false;
+            copy(L, S_U, S_JA); copy(L, S_V, S_JB);
         }
-        oA = iA; oB = iB;
+        copy(L, S_A, S_U); copy(L, S_B, S_V);
         return false;
     }
 
-    // returns HZ_*; alpha_out = accepted step
-    __device__ int run(double c, double phi0, double dphi0, double &alpha_out) {
+    // returns HZ_*; alpha_out = accepted step.  L.x, L.s hold the base point and the direction.
+    __device__ static int run(LsShared &L, double c, double phi0, double dphi0, double &alpha_out) {
         const double rho = 5.0, epsilon = 1e-6, gamma = 0.66, psi3 = 0.1;
         const int linesearchmax = 50, iterfinitemax = 52;
         double alphamax = (double)INFINITY;
         alpha_out = 0.0;
-        phi_0 = phi0; dphi_0 = dphi0;
+        L.phi_0 = phi0; L.dphi_0 = dphi0;
         if (!(isfinite(phi0) && isfinite(dphi0))) return HZ_LSEXC;
         if (dphi0 >= mul_(DBL_EPSILON, fabs(phi0))) return HZ_LSEXC;
         else if (dphi0 >= 0.0) return HZ_OK;
-        npts = 0; err = false;
-        Pt p0 = push(0.0, phi0, dphi0);
-        phi_lim = add_(phi0, mul_(epsilon, fabs(phi0)));
+        L.npts = 0; L.err = 0;
+        push(L, S_P0, 0.0, phi0, dphi0);
+        L.phi_lim = add_(phi0, mul_(epsilon, fabs(phi0)));
         if (!(c >= 0.0)) return HZ_ERROR;
         if (c <= DBL_EPSILON) return HZ_OK;
         if (!(isfinite(c) && c <= alphamax)) return HZ_ERROR;
         double phi_c, dphi_c;
-        phidphi(c, phi_c, dphi_c);
+        phidphi(L, c, phi_c, dphi_c);
         int iterfinite = 1;
         while (!(isfinite(phi_c) && isfinite(dphi_c)) && iterfinite < iterfinitemax) {
             iterfinite++;
             c = mul_(c, psi3);
-            phidphi(c, phi_c, dphi_c);
+            phidphi(L, c, phi_c, dphi_c);
         }
         if (!(isfinite(phi_c) && isfinite(dphi_c))) return HZ_OK;
-        Pt last = push(c, phi_c, dphi_c);
+        push(L, S_LAST, c, phi_c, dphi_c);
         // most recent point with phi <= phi_lim among the points pushed BEFORE `last`
-        Pt prevok = p0;
+        copy(L, S_PREVOK, S_P0);
         // bracketing, HZ stages B0-B3
         bool isbracketed = false;
-        Pt ia = p0, ib = last;
+        copy(L, S_IA, S_P0); copy(L, S_IB, S_LAST);
         int iter = 1;
         double cold = -1.0;
         while (!isbracketed && iter < linesearchmax) {
             if (dphi_c >= 0.0) {
-                ib = last; ia = prevok;
+                copy(L, S_IB, S_LAST); copy(L, S_IA, S_PREVOK);
                 isbracketed = true;
-            } else if (last.v > phi_lim) {
-                Pt na, nb;
-                bisect(p0, last, na, nb);
-                if (err) return HZ_ERROR;
-                ia = na; ib = nb;
+            } else if (L.pt[S_LAST].v > L.phi_lim) {
+                bisect(L, S_P0, S_LAST, S_NA, S_NB);
+                if (L.err) return HZ_ERROR;
+                copy(L, S_IA, S_NA); copy(L, S_IB, S_NB);
                 isbracketed = true;
             } else {
                 cold = c;
                 if (nextfloat_(cold) >= alphamax) { alpha_out = cold; return HZ_OK; }
                 c = mul_(c, rho);
                 if (c > alphamax) c = alphamax;
-                phidphi(c, phi_c, dphi_c);
+                phidphi(L, c, phi_c, dphi_c);
                 iterfinite = 1;
                 while (!(isfinite(phi_c) && isfinite(dphi_c)) && c > nextfloat_(cold) && iterfinite < iterfinitemax) {
                     alphamax = c;
                     iterfinite++;
                     c = div_(add_(cold, c), 2.0);
-                    phidphi(c, phi_c, dphi_c);
+                    phidphi(L, c, phi_c, dphi_c);
                 }
                 if (!(isfinite(phi_c) && isfinite(dphi_c))) { alpha_out = cold; return HZ_OK; }
-                if (last.v <= phi_lim) prevok = last;
-                last = push(c, phi_c, dphi_c);
+                if (L.pt[S_LAST].v <= L.phi_lim) copy(L, S_PREVOK, S_LAST);
+                push(L, S_LAST, c, phi_c, dphi_c);
             }
             iter++;
         }
         while (iter < linesearchmax) {
-            const double a = ia.a, b = ib.a;
+            const double a = L.pt[S_IA].a, b = L.pt[S_IB].a;
             if (!(b > a)) return HZ_ERROR;
             if (sub_(b, a) <= eps_of(b)) { alpha_out = a; return HZ_OK; }
-            Pt iA, iB;
-            bool iswolfe = secant2(ia, ib, iA, iB);
-            if (err) return HZ_ERROR;
-            if (iswolfe) { alpha_out = iA.a; return HZ_OK; }
-            const double A = iA.a, B = iB.a;
+            const bool iswolfe = secant2(L);
+            if (L.err) return HZ_ERROR;
+            if (iswolfe) { alpha_out = L.pt[S_A].a; return HZ_OK; }
+            const double A = L.pt[S_A].a, B = L.pt[S_B].a;
             if (!(B > A)) return HZ_ERROR;
             if (sub_(B, A) < mul_(gamma, sub_(b, a))) {
-                if (nextfloat_(ia.v) >= ib.v && nextfloat_(iA.v) >= iB.v) { alpha_out = A; return HZ_OK; }
-                ia = iA; ib = iB;
+                if (nextfloat_(L.pt[S_IA].v) >= L.pt[S_IB].v && nextfloat_(L.pt[S_A].v) >= L.pt[S_B].v) { alpha_out = A; return HZ_OK; }
+                copy(L, S_IA, S_A); copy(L, S_IB, S_B);
             } else {
                 c = div_(add_(A, B), 2.0);
-                phidphi(c, phi_c, dphi_c);
+                phidphi(L, c, phi_c, dphi_c);
                 if (!(isfinite(phi_c) && isfinite(dphi_c))) return HZ_ERROR;
-                Pt ic = push(c, phi_c, dphi_c);
-                Pt na, nb;
-                update(iA, iB, ic, na, nb);
-                if (err) return HZ_ERROR;
-                ia = na; ib = nb;
+                push(L, S_C, c, phi_c, dphi_c);
+                update(L, S_A, S_B, S_C, S_NA, S_NB);
+                if (L.err) return HZ_ERROR;
+                copy(L, S_IA, S_NA); copy(L, S_IB, S_NB);
             }
             iter++;
         }
-        alpha_out = ia.a;
+        alpha_out = L.pt[S_IA].a;
         return HZ_LSEXC;
     }
 };
@@ -593,8 +603,14 @@ __device__ __forceinline__ double maxabs3(const double a[3]) { return fmax(fmax(
 template <int THREADS>
 __device__ int lbfgs_fit(const double x0[3], double g_tol, int max_iter, double out_p[3], int &iters_out) {
     constexpr int M = LBFGS_M;
-    double x[3] = {x0[0], x0[1], x0[2]}, x_prev[3], g[3], g_prev[3], s[3], dx[3], dg[3];
     EvalShared &es = eval_shared();
+    // the vectors of the iteration live in shared memory (every lane of the master warp stores the same bits): nothing
+    // but a few scalars is live in registers across the evaluator calls
+    double (&x)[3] = es.vx, (&x_prev)[3] = es.vxp, (&g)[3] = es.vg, (&g_prev)[3] = es.vgp, (&s)[3] = es.vs,
+           (&dx)[3] = es.vdx, (&dg)[3] = es.vdg;
+    x[0] = x0[0]; x[1] = x0[1]; x[2] = x0[2];
+    LsShared &L = es.ls;
+    L.ntrials = 0;
     double (*dxh)[3] = es.hist_dx, (*dgh)[3] = es.hist_dg;
     double *rho = es.hist_rho, *tl_alpha = es.hist_alpha;
     double f, f_prev = nan("");
@@ -605,7 +621,6 @@ __device__ int lbfgs_fit(const double x0[3], double g_tol, int max_iter, double 
     bool converged = g_conv0 || stopped0;
     status = stopped0 ? SHOPT_FIT_NONFINITE : SHOPT_FIT_CONVERGED;
     bool broke = false;
-    LineSearch<THREADS> LS;
     while (!converged && iteration < max_iter) {
         iteration++;
         pseudo++;
@@ -650,9 +665,9 @@ __device__ int lbfgs_fit(const double x0[3], double g_tol, int max_iter, double 
         const double phi_0 = f;
         f_prev = phi_0;
 #pragma unroll
-        for (int k = 0; k < 3; k++) { x_prev[k] = x[k]; LS.x[k] = x[k]; LS.s[k] = s[k]; }
+        for (int k = 0; k < 3; k++) { x_prev[k] = x[k]; L.x[k] = x[k]; L.s[k] = s[k]; }
         double alpha = 1.0;   // InitialStatic(alpha = 1.0, scaled = false)
-        const int hz = LS.run(alpha, phi_0, dphi_0, alpha);
+        const int hz = LineSearch<THREADS>::run(L, alpha, phi_0, dphi_0, alpha);
         if (hz == HZ_ERROR) { status = SHOPT_FIT_THREW; broke = true; break; }
 #pragma unroll
         for (int k = 0; k < 3; k++) { dx[k] = mul_(alpha, s[k]); x[k] = add_(x[k], dx[k]); }
@@ -884,7 +899,10 @@ int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n
     const int npix = n_a * n_a;
     (void)npix;
     if (n_a <= 32) return launch_fit<128, 6>(a, stream);
-    if (n_a <= 80) return launch_fit<256, 3>(a, stream);
+    if (n_a <= 80) {
+        static const int minb = getenv("SHOPT_FIT_MINB") ? atoi(getenv("SHOPT_FIT_MINB")) : 3;   // measurement switch
+        return minb == 2 ? launch_fit<256, 2>(a, stream) : launch_fit<256, 3>(a, stream);
+    }
     if (n_a <= 160) return launch_fit<512, 1>(a, stream);
     return SHOPT_E_UNSUPPORTED;
 }
