@@ -88,18 +88,31 @@ __device__ int jacobi_columns(double *A, int nrows, int ncols, int lda, double *
                     be = fma(xb[t], xb[t], be);
                     ga = fma(xa[t], xb[t], ga);
                 }
-#pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) {
-                    al += __shfl_xor_sync(0xffffffffu, al, o);
-                    be += __shfl_xor_sync(0xffffffffu, be, o);
-                    ga += __shfl_xor_sync(0xffffffffu, ga, o);
+                {   // three warp sums by one halving tree (6 shuffles instead of 15), then broadcast
+                    const bool b4 = lane & 16, b3 = lane & 8;
+                    const double k0 = (b4 ? ga : al) + __shfl_xor_sync(0xffffffffu, b4 ? al : ga, 16);
+                    const double k1 = (b4 ? 0.0 : be) + __shfl_xor_sync(0xffffffffu, b4 ? be : 0.0, 16);
+                    double k = (b3 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, b3 ? k0 : k1, 8);
+                    k += __shfl_xor_sync(0xffffffffu, k, 4);
+                    k += __shfl_xor_sync(0xffffffffu, k, 2);
+                    k += __shfl_xor_sync(0xffffffffu, k, 1);
+                    al = __shfl_sync(0xffffffffu, k, 0);      // lane 0: al, lane 8: be, lane 16: ga
+                    be = __shfl_sync(0xffffffffu, k, 8);
+                    ga = __shfl_sync(0xffffffffu, k, 16);
                 }
                 if (al <= tiny || be <= tiny) continue;
-                if (fabs(ga) <= DBL_EPSILON * sqrt(al) * sqrt(be)) continue;
+                if (ga * ga <= (DBL_EPSILON * DBL_EPSILON) * (al * be)) continue;
                 rotated = 1;
-                const double zeta = (be - al) / (2.0 * ga);
-                const double tt = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-                const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+                // tan of the rotation angle from  t = h sgn(d) / (|d| + sqrt(d^2 + h^2)),  d = be - al, h = 2 ga; only
+                // cs^2 + sn^2 = 1 needs full accuracy (cs = rsqrt(1 + t^2), sn = t cs), so no IEEE division or square root
+                const double dd = be - al, hh = 2.0 * ga;
+                const double ww = fma(dd, dd, hh * hh);
+                const double den = fabs(dd) + ww * rsqrt(ww);
+                const double ri = rsqrt(den);
+                double tt = copysign(hh, hh * dd) * (ri * ri);
+                if (dd == 0.0) tt = copysign(1.0, ga);
+                if (!isfinite(tt)) continue;
+                const double cs = rsqrt(fma(tt, tt, 1.0)), sn = cs * tt;
 #pragma unroll
                 for (int t = 0; t < RT; t++) {
                     const int i = lane + 32 * t;
@@ -390,7 +403,7 @@ __device__ void rayleigh_ritz(const double *Z, double *T, int c, double *Q, doub
 // returns k >= 1 on acceptance (ford[0..k) = block columns of the kept components, Q = Ritz vectors, T = Z'Q), else 0
 template <int NW, int RT>
 __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, double pratio, double *Q, double *Qn,
-                        double *T, int ldq, double *G, double *fth, int *ford, int *s_flag, int *dbg_it, int usecut) {
+                        double *T, int ldq, double *G, double *fth, int *ford, int *s_flag, int *dbg_it, int usecut, int first_check) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
     const int j0 = c / 2 - FB / 2;
     for (int e = tid; e < FB * r; e += nthr) {
@@ -405,7 +418,7 @@ __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, do
     for (int it = 1; it <= 12; it++) {
         mul_zt_q<NW>(Z, r, c, Q, ldq, T);
         __syncthreads();
-        const bool check = (it == 3 || it == 5 || it == 8 || it == 12);
+        const bool check = (it == first_check || it == 3 || it == 5 || it == 8 || it == 12);
         if (check) {
             // Rayleigh-Ritz: T'T = V Theta V' (8 x 8, one warp), then T <- T V and Q <- Q V
             rayleigh_ritz<NW>(Z, T, c, Q, Qn, r, ldq, G + 64, rr_cut);
@@ -618,7 +631,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         // ---- fast path: block subspace iteration with a-posteriori acceptance ----
         int k = 0, status = SHOPT_PCA_OK, dbg_it = 0;
         if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
-            k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag, &dbg_it, a.debug & 4);
+            k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag, &dbg_it, a.debug & 4, (a.debug & 8) ? 2 : 3);
         const bool fastk = k > 0;
         if (fastk) {
             if (tid < k) {
@@ -973,7 +986,7 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
     a.counter = d_counter; a.wglobal = nullptr; a.wstride = 0;
     a.kmax = ncomp < r ? ncomp : r; if (c < a.kmax) a.kmax = c;
     a.fast = (getenv("SHOPT_PCA_NO_FAST") == nullptr);
-    a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on
+    a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on, 8: first acceptance check after 2 iterations
     if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern, a.kz);
     const int rt = ((r > c ? r : c) + 31) / 32;
     switch (rt) {
