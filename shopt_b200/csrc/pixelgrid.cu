@@ -22,6 +22,7 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "pca_eig.cuh"
 
 namespace shopt {
 
@@ -39,7 +40,9 @@ struct PcaArgs {
     size_t wstride;
     int kmax;             // min(ncomp, r, c)
     int fast;             // try the block subspace iteration first (0: always the full Jacobi SVD)
-    int debug;            // status |= (subspace iterations used by the fast path) << 8
+    int debug;            // status |= (subspace iterations used by the fast path; 100 direct path, 200 Jacobi) << 8
+    double *eigscratch;   // non-null: per-CTA global scratch (eigstride doubles: Gram matrix + reflectors) of the direct path
+    size_t eigstride;
     double kern[15 * 15]; // normalised lanczos kernel (2a+1)^2, a <= 7, column-major like the reference's
     double kz[15];        // its 1-D factor: kern = kz (x) kz / sum
 };
@@ -571,14 +574,15 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
     const int kmaxp = (a.kmax + 1) & ~1, ldq = (r + 1) & ~1;
     // shared layout: [ misc 64 B | scratch 2*NW | mu r | sv c | fth 8 | ord c' ints | uoff, yoff kmax' ints | ford 8 ints |
-    //                  (W rc | region) unless global ];  region = Y (kmax x c)  overlaid with  Q, Qn (8 x ldq), T (8 x c), G 64
+    //                  (W rc | region) unless global ];  det (3 r doubles) sits between fth and ord;  region = Y (kmax x c)  overlaid with  Q, Qn (8 x ldq), T (8 x c), G 64
     long long *s_next = reinterpret_cast<long long *>(smem_raw);
     int *s_flag = reinterpret_cast<int *>(smem_raw + 16);
     double *scratch = reinterpret_cast<double *>(smem_raw + 64);
     double *mu = scratch + 2 * NW;
     double *sv = mu + r;
     double *fth = sv + c;
-    int *ord = reinterpret_cast<int *>(fth + FB);
+    double *det = fth + FB;                                       // d, e, tau of the direct path (3 r)
+    int *ord = reinterpret_cast<int *>(det + 3 * r);
     int *uoff = ord + ((c + 1) & ~1);
     int *yoff = uoff + kmaxp;
     int *ford = yoff + kmaxp;
@@ -633,11 +637,26 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
             k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag, &dbg_it, a.debug & 4, (a.debug & 8) ? 2 : 3);
         const bool fastk = k > 0;
+        bool eigk = false;
+        if (!fastk && a.eigscratch && r <= c && r >= 16 && r <= nthr && r <= 32 * RT) {
+            // ---- direct path: eigenvectors of the r x r Gram matrix (pca_eig.cuh); 0 = a check failed ----
+            double *Cg = a.eigscratch + (size_t)blockIdx.x * a.eigstride;
+            k = gram_eig_pca<NW, RT>(W, r, c, a.ncomp, a.pratio, Y, det, sv, fth, s_flag, Cg, Cg + (size_t)r * r);
+            eigk = k > 0;
+            dbg_it = eigk ? 100 : 200;
+            if (!eigk) {                                         // W was consumed: centre the stamp again
+                for (long long p = tid; p < rc; p += nthr) W[p] = nan_to_zero(__ldg(X + p)) - mu[(int)(p % r)];
+                __syncthreads();
+            }
+        }
         if (fastk) {
             if (tid < k) {
                 uoff[tid] = (int)(FQ - W) + ford[tid] * ldq;
                 yoff[tid] = (int)(FT - W) + ford[tid] * c;
             }
+            __syncthreads();
+        } else if (eigk) {
+            if (tid < k) { uoff[tid] = (int)rc + tid * r; yoff[tid] = tid * c; }     // U_k in the region, Y into W
             __syncthreads();
         } else {
             // ---- full SVD: one-sided Jacobi on all c columns; the columns become sigma_j u_j ----
@@ -683,6 +702,8 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
             }
             if (tid < k) { uoff[tid] = ord[tid] * r; yoff[tid] = (int)rc + tid * c; }
             __syncthreads();
+        }
+        if (!fastk) {
             // Y = U_k' Z, Z re-read from the stamp (transform)
             for (int j = warp; j < c; j += NW) {
                 for (int aa = 0; aa < k; aa++) {
@@ -692,7 +713,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
                         s = fma(ua[i], nan_to_zero(__ldg(X + i + (size_t)j * r)) - mu[i], s);
 #pragma unroll
                     for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-                    if (lane == 0) Y[(size_t)aa * c + j] = s;
+                    if (lane == 0) W[yoff[aa] + j] = s;
                 }
             }
             __syncthreads();
@@ -930,7 +951,7 @@ static void lanczos_kernel2d(int a, double *kernel, double *kz = nullptr) {
 
 // ---- launch -----------------------------------------------------------------------------------
 static size_t pca_fixed_smem(int nw, int r, int c, int kmax) {
-    return 64 + (size_t)2 * nw * 8 + (size_t)r * 8 + (size_t)c * 8 + FB * 8 + (size_t)((c + 1) & ~1) * 4 +
+    return 64 + (size_t)2 * nw * 8 + (size_t)r * 8 + (size_t)c * 8 + FB * 8 + (size_t)3 * r * 8 + (size_t)((c + 1) & ~1) * 4 +
            (size_t)2 * ((kmax + 1) & ~1) * 4 + FB * 4;
 }
 static size_t pca_w_doubles(int r, int c, int kmax) {      // W plus the region shared by Y and the fast-path buffers
@@ -940,7 +961,8 @@ static size_t pca_w_doubles(int r, int c, int kmax) {      // W plus the region 
 size_t pca_scratch_bytes(int r, int c, int ncomp) {
     int kmax = ncomp < r ? ncomp : r; if (c < kmax) kmax = c; if (kmax < 1) kmax = 1;
     const size_t wdoubles = pca_w_doubles(r, c, kmax);
-    if (pca_fixed_smem(32, r, c, kmax) + wdoubles * 8 <= 227 * 1024) return 0;
+    if (pca_fixed_smem(32, r, c, kmax) + wdoubles * 8 <= 227 * 1024)
+        return (r <= c && r >= 16) ? (size_t)sm_count() * 2 * r * r * 8 : 0;       // direct path: Gram matrix + reflectors
     return (size_t)sm_count() * wdoubles * 8;
 }
 
@@ -954,6 +976,8 @@ static int pca_launch_t(PcaArgs a, double *scratch, size_t scratch_bytes, cudaSt
         smem = pca_fixed_smem(NW, a.r, a.c, a.kmax);
         if ((size_t)grid * wdoubles * 8 > scratch_bytes) return SHOPT_E_NOMEM;
         a.wglobal = scratch;
+    } else if (a.eigstride && scratch && (size_t)grid * a.eigstride * 8 <= scratch_bytes) {
+        a.eigscratch = scratch;
     }
     auto kern = pca_kernel<NW, RT>;
     SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -984,6 +1008,7 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
     a.stamps = d_stamps; a.r = r; a.c = c; a.N = N; a.ncomp = ncomp; a.pratio = pratio;
     a.lanczos_a = lanczos_a; a.unity_sum = unity_sum; a.pgf = d_pgf; a.k_out = d_k; a.status = d_status;
     a.counter = d_counter; a.wglobal = nullptr; a.wstride = 0;
+    a.eigscratch = nullptr; a.eigstride = getenv("SHOPT_PCA_NO_EIG") ? 0 : (size_t)2 * r * r;
     a.kmax = ncomp < r ? ncomp : r; if (c < a.kmax) a.kmax = c;
     a.fast = (getenv("SHOPT_PCA_NO_FAST") == nullptr);
     a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on, 8: first acceptance check after 2 iterations

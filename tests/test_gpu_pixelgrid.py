@@ -11,14 +11,17 @@ from shopt_b200 import synth
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["fast", "jacobi"], autouse=True)
+@pytest.fixture(params=["fast", "direct", "jacobi"], autouse=True)
 def pca_path(request, monkeypatch):
-    """Every case runs twice: with the block-subspace fast path enabled (it falls back to the full Jacobi SVD whenever
-    its acceptance test fails) and with the Jacobi SVD forced for every star."""
-    if request.param == "jacobi":
+    """Every case runs three times: with the block-subspace fast path enabled (stars it gives up on go to the direct
+    Gram-matrix eigen path, and from there to the Jacobi SVD when a check fails), with the fast path off (direct path
+    first for every star), and with the full Jacobi SVD forced for every star."""
+    for name in ("SHOPT_PCA_NO_FAST", "SHOPT_PCA_NO_EIG", "SHOPT_PCA_DEBUG"):
+        monkeypatch.delenv(name, raising=False)
+    if request.param in ("direct", "jacobi"):
         monkeypatch.setenv("SHOPT_PCA_NO_FAST", "1")
-    else:
-        monkeypatch.delenv("SHOPT_PCA_NO_FAST", raising=False)
+    if request.param == "jacobi":
+        monkeypatch.setenv("SHOPT_PCA_NO_EIG", "1")
     return request.param
 
 
@@ -62,6 +65,27 @@ def test_noise_dominated_stamps_keep_many_components(stage, orc):
     want, kw_, st_ = orc.pixel_grid_pca_batch(img, 50, 0.99, 3, False, nthreads=4)
     assert np.all(k >= 40) and np.array_equal(k, kw_) and np.all(status == 0)
     assert close(pgf, want, 1e-8)
+
+
+def test_flat_spectrum_stamps_take_the_direct_path(stage, orc, pca_path, monkeypatch):
+    """Masked / noisy 131 x 131 stamps keep tens of components: the direct path (tridiagonalised Gram matrix, Sturm
+    multisection, inverse iteration) must serve them, and agree with the oracle's SVD."""
+    rng = np.random.default_rng(21)
+    r = 131
+    yy, xx = np.mgrid[:r, :r]
+    img = np.empty((6, r, r))
+    for i in range(6):
+        g = np.exp(-((yy - 65.0) ** 2 + (xx - 65.0) ** 2) / (2 * (2.0 + 0.3 * i) ** 2))
+        img[i] = g / g.sum() + (1e-4 * (i + 1)) * rng.normal(size=(r, r))
+    img[2][rng.random((r, r)) < 0.01] = np.nan
+    monkeypatch.setenv("SHOPT_PCA_DEBUG", "1")               # status >> 8: 100 direct path, 200 Jacobi after a failed check
+    pgf, k, status = stage.pca_batch(img, 50, 0.99, 3, False)
+    want, kw_, st_ = orc.pixel_grid_pca_batch(img, 50, 0.99, 3, False, nthreads=orc.max_threads())
+    assert np.array_equal(k, kw_) and np.all((status & 0xff) == 0)
+    assert close(pgf, want, 1e-9)
+    assert k.max() > 6
+    if pca_path != "jacobi":
+        assert np.all((status >> 8)[k > 6] == 100), (status >> 8, k)
 
 
 def test_failed_stars_and_exact_rank(stage, orc):
