@@ -131,13 +131,23 @@ __device__ void tridiagonalise(double *A, int n, double *d, double *e, double *t
     __syncthreads();
 }
 
-// number of eigenvalues of the tridiagonal (d, e) below x; e2[i] = e[i]^2
+// 1/q to ~1 ulp for normal q: the 20-bit hardware seed and two Newton steps (the Sturm recurrence needs no IEEE division:
+// a relative error of a few ulp is a relative perturbation of e^2 of the same size)
+__device__ __forceinline__ double rcp_newton(double q) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(q));
+    r = fma(fma(-q, r, 1.0), r, r);
+    r = fma(fma(-q, r, 1.0), r, r);
+    return r;
+}
+
+// number of eigenvalues of the tridiagonal (d, e) below x; e2[i] = e[i]^2; pivmin is a normal number
 __device__ __forceinline__ int sturm_count(const double *d, const double *e2, int n, double x, double pivmin) {
     double q = d[0] - x;
     if (fabs(q) < pivmin) q = -pivmin;
     int cnt = q < 0.0;
     for (int i = 1; i < n; i++) {
-        q = d[i] - x - e2[i - 1] / q;
+        q = fma(-e2[i - 1], rcp_newton(q), d[i] - x);
         if (fabs(q) < pivmin) q = -pivmin;
         cnt += q < 0.0;
     }
@@ -250,7 +260,8 @@ __device__ double tri_inverse_iteration(const double *d, const double *e, int n,
 //   Cg, Hg: r*r doubles each of per-CTA global scratch.
 template <int NW, int RT>
 __device__ int gram_eig_pca(double *W, int r, int c, int ncomp, double pratio, double *region, double *det, double *lam,
-                            double *fth, int *s_flag, double *Cg, double *Hg) {
+                            double *fth, int *s_flag, double *Cg, double *Hg, unsigned long long *prof) {
+#define EIG_TICK(i) do { if (prof && threadIdx.x == 0) prof[i] = clock64(); } while (0)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32, n = r;
     double *d = det, *e = det + n, *tau = det + 2 * n;
     double *V = region;
@@ -258,7 +269,9 @@ __device__ int gram_eig_pca(double *W, int r, int c, int ncomp, double pratio, d
     __syncthreads();
     for (int p = tid; p < n * n; p += nthr) W[p] = Cg[p];
     __syncthreads();
+    EIG_TICK(3);
     tridiagonalise<NW, RT>(W, n, d, e, tau, region, region + n, region + 2 * n, Hg);
+    EIG_TICK(4);
     // Gershgorin bracket, trace, norm
     double *e2 = region;
     if (warp == 0) {
@@ -290,6 +303,7 @@ __device__ int gram_eig_pca(double *W, int r, int c, int ncomp, double pratio, d
     if (c < m) m = c;
     top_eigenvalues<NW>(d, e2, n, m, fth[0], fth[1], DBL_MIN * fmax(1.0, tnorm * tnorm), lam);
     __syncthreads();
+    EIG_TICK(5);
     if (tid == 0) {                                              // choose_pcadim on lambda_i / (c - 1)
         const double den = (double)(c - 1);
         const double thres = (fth[2] / den) * pratio;
@@ -317,6 +331,7 @@ __device__ int gram_eig_pca(double *W, int r, int c, int ncomp, double pratio, d
         bad = !(res <= tol * tol);
     }
     bad = __syncthreads_or(bad);
+    EIG_TICK(6);
     if (bad) return 0;
     // ---- orthogonality of the k vectors; tight clusters are re-orthogonalised (MGS, twice) by warp 0 ----
     int loose = 0;
@@ -361,6 +376,7 @@ __device__ int gram_eig_pca(double *W, int r, int c, int ncomp, double pratio, d
         bad = __syncthreads_or(bad);
         if (bad) return 0;
     }
+    EIG_TICK(7);
     // ---- back through the reflectors: u_a = H_0 ... H_{n-3} v_a, one warp per vector ----
     for (int p = tid; p < n * (n - 2); p += nthr) {
         const int kk = p / n, i = p - kk * n;
@@ -392,7 +408,9 @@ __device__ int gram_eig_pca(double *W, int r, int c, int ncomp, double pratio, d
             if (lane + 32 * t < n) V[(size_t)a * n + lane + 32 * t] = va[t];
     }
     __syncthreads();
+    EIG_TICK(8);
     return k;
+#undef EIG_TICK
 }
 
 }  // namespace shopt

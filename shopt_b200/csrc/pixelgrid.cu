@@ -18,6 +18,7 @@
 // the output, pulled back into the (now free) shared buffer and smoothed from there.  Stamps too large for shared
 // memory (301 x 301) run the same code with W in a per-CTA global scratch block that stays L2-resident.
 // The stage is FP64-compute-bound (O(r c^2) flops per sweep on 8 r c bytes); see DESIGN.md for the roofline.
+#include <cstdio>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -46,6 +47,9 @@ struct PcaArgs {
     double kern[15 * 15]; // normalised lanczos kernel (2a+1)^2, a <= 7, column-major like the reference's
     double kz[15];        // its 1-D factor: kern = kz (x) kz / sum
 };
+
+// SHOPT_PCA_DEBUG bit 16: cycles per phase of pca_kernel, summed over the stars (thread 0 of every CTA), printed by pca_launch
+__device__ unsigned long long g_pca_phase[16];
 
 __device__ __forceinline__ double nan_to_zero(double x) { return isnan(x) ? 0.001 : x; }   // masks.jl:43
 
@@ -573,11 +577,12 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
     const long long rc = (long long)r * c;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
     const int kmaxp = (a.kmax + 1) & ~1, ldq = (r + 1) & ~1;
-    // shared layout: [ misc 64 B | scratch 2*NW | mu r | sv c | fth 8 | ord c' ints | uoff, yoff kmax' ints | ford 8 ints |
+    // shared layout: [ misc 192 B | scratch 2*NW | mu r | sv c | fth 8 | ord c' ints | uoff, yoff kmax' ints | ford 8 ints |
     //                  (W rc | region) unless global ];  det (3 r doubles) sits between fth and ord;  region = Y (kmax x c)  overlaid with  Q, Qn (8 x ldq), T (8 x c), G 64
     long long *s_next = reinterpret_cast<long long *>(smem_raw);
     int *s_flag = reinterpret_cast<int *>(smem_raw + 16);
-    double *scratch = reinterpret_cast<double *>(smem_raw + 64);
+    unsigned long long *prof = (a.debug & 16) ? reinterpret_cast<unsigned long long *>(smem_raw + 64) : nullptr;   // 16 ticks
+    double *scratch = reinterpret_cast<double *>(smem_raw + 192);
     double *mu = scratch + 2 * NW;
     double *sv = mu + r;
     double *fth = sv + c;
@@ -603,6 +608,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         if (tid == 0) nxt = (long long)atomicAdd(a.counter, 1ULL);
         const double *X = a.stamps + star * rc;
         double *out = a.pgf + star * rc;
+        if (prof && tid == 0) { for (int i = 0; i < 16; i++) prof[i] = 0; prof[0] = clock64(); }
 
         // ---- load, nanToZero, finiteness (LAPACK raises on Inf -> shopt.jl:305-309 zeros + failedStars) ----
         int bad = 0;
@@ -632,16 +638,18 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         }
         fro = block_sum1<NW>(fro, scratch, buf);                // |Z|_F^2; the block sum also publishes W
 
+        if (prof && tid == 0) prof[1] = clock64();
         // ---- fast path: block subspace iteration with a-posteriori acceptance ----
         int k = 0, status = SHOPT_PCA_OK, dbg_it = 0;
         if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
             k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag, &dbg_it, a.debug & 4, (a.debug & 8) ? 2 : 3);
         const bool fastk = k > 0;
+        if (prof && tid == 0) prof[2] = clock64();
         bool eigk = false;
         if (!fastk && a.eigscratch && r <= c && r >= 16 && r <= nthr && r <= 32 * RT) {
             // ---- direct path: eigenvectors of the r x r Gram matrix (pca_eig.cuh); 0 = a check failed ----
             double *Cg = a.eigscratch + (size_t)blockIdx.x * a.eigstride;
-            k = gram_eig_pca<NW, RT>(W, r, c, a.ncomp, a.pratio, Y, det, sv, fth, s_flag, Cg, Cg + (size_t)r * r);
+            k = gram_eig_pca<NW, RT>(W, r, c, a.ncomp, a.pratio, Y, det, sv, fth, s_flag, Cg, Cg + (size_t)r * r, prof);
             eigk = k > 0;
             dbg_it = eigk ? 100 : 200;
             if (!eigk) {                                         // W was consumed: centre the stamp again
@@ -703,14 +711,24 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
             if (tid < k) { uoff[tid] = ord[tid] * r; yoff[tid] = (int)rc + tid * c; }
             __syncthreads();
         }
+        if (prof && tid == 0) prof[9] = clock64();
         if (!fastk) {
-            // Y = U_k' Z, Z re-read from the stamp (transform)
+            // Y = U_k' Z, Z re-read from the stamp (transform); a warp holds its column of Z in registers
             for (int j = warp; j < c; j += NW) {
+                double zt[RT];
+#pragma unroll
+                for (int t = 0; t < RT; t++) {
+                    const int i = lane + 32 * t;
+                    zt[t] = (i < r) ? nan_to_zero(__ldg(X + i + (size_t)j * r)) - mu[i] : 0.0;
+                }
                 for (int aa = 0; aa < k; aa++) {
                     const double *ua = W + uoff[aa];
                     double s = 0.0;
-                    for (int i = lane; i < r; i += 32)
-                        s = fma(ua[i], nan_to_zero(__ldg(X + i + (size_t)j * r)) - mu[i], s);
+#pragma unroll
+                    for (int t = 0; t < RT; t++) {
+                        const int i = lane + 32 * t;
+                        if (i < r) s = fma(ua[i], zt[t], s);
+                    }
 #pragma unroll
                     for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
                     if (lane == 0) W[yoff[aa] + j] = s;
@@ -718,6 +736,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
             }
             __syncthreads();
         }
+        if (prof && tid == 0) prof[10] = clock64();
         // the next star's stamp starts its way into L2 now (one bulk prefetch); its load phase then hits L2
         if (tid == 0 && nxt < a.N && !(a.debug & 2)) {
             const uintptr_t p0 = (uintptr_t)(a.stamps + nxt * rc), p1 = (uintptr_t)(a.stamps + (nxt + 1) * rc);
@@ -802,6 +821,17 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
                         }
                     out[p] = val / norm;
                 }
+            }
+        }
+        if (prof) {
+            __syncthreads();
+            if (tid == 0) {
+                const unsigned long long t_end = clock64();
+                unsigned long long prev = prof[0];
+                for (int i = 1; i <= 10; i++)
+                    if (prof[i]) { atomicAdd(&g_pca_phase[i], prof[i] - prev); prev = prof[i]; }
+                atomicAdd(&g_pca_phase[11], t_end - prev);
+                atomicAdd(&g_pca_phase[0], 1ULL);
             }
         }
         if (tid == 0) {
@@ -951,7 +981,7 @@ static void lanczos_kernel2d(int a, double *kernel, double *kz = nullptr) {
 
 // ---- launch -----------------------------------------------------------------------------------
 static size_t pca_fixed_smem(int nw, int r, int c, int kmax) {
-    return 64 + (size_t)2 * nw * 8 + (size_t)r * 8 + (size_t)c * 8 + FB * 8 + (size_t)3 * r * 8 + (size_t)((c + 1) & ~1) * 4 +
+    return 192 + (size_t)2 * nw * 8 + (size_t)r * 8 + (size_t)c * 8 + FB * 8 + (size_t)3 * r * 8 + (size_t)((c + 1) & ~1) * 4 +
            (size_t)2 * ((kmax + 1) & ~1) * 4 + FB * 4;
 }
 static size_t pca_w_doubles(int r, int c, int kmax) {      // W plus the region shared by Y and the fast-path buffers
@@ -983,8 +1013,23 @@ static int pca_launch_t(PcaArgs a, double *scratch, size_t scratch_bytes, cudaSt
     SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (grid > a.N) grid = a.N;
     SHOPT_CUDA_TRY(cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), st));
+    if (a.debug & 16) {
+        unsigned long long zero[16] = {0};
+        SHOPT_CUDA_TRY(cudaMemcpyToSymbolAsync(g_pca_phase, zero, sizeof(zero), 0, cudaMemcpyHostToDevice, st));
+    }
     kern<<<(unsigned)grid, NW * 32, smem, st>>>(a);
     SHOPT_CUDA_TRY(cudaGetLastError());
+    if (a.debug & 16) {
+        static const char *names[12] = {"stars", "load+centre", "fast path", "gram+copy", "tridiagonalise", "eigenvalues",
+                                        "inverse iteration", "orthogonality", "back-transform", "jacobi/offsets", "Y = U'Z",
+                                        "reconstruct+smooth"};
+        unsigned long long ph[16];
+        SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+        SHOPT_CUDA_TRY(cudaMemcpyFromSymbol(ph, g_pca_phase, sizeof(ph)));
+        fprintf(stderr, "[pca phases] stars %llu;", ph[0]);
+        for (int i = 1; i < 12; i++) fprintf(stderr, " %s %.0f;", names[i], ph[0] ? (double)ph[i] / (double)ph[0] : 0.0);
+        fprintf(stderr, " (cycles per star)\n");
+    }
     return SHOPT_OK;
 }
 template <int RT>
@@ -1011,7 +1056,7 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
     a.eigscratch = nullptr; a.eigstride = getenv("SHOPT_PCA_NO_EIG") ? 0 : (size_t)2 * r * r;
     a.kmax = ncomp < r ? ncomp : r; if (c < a.kmax) a.kmax = c;
     a.fast = (getenv("SHOPT_PCA_NO_FAST") == nullptr);
-    a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on, 8: first acceptance check after 2 iterations
+    a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on, 8: first acceptance check after 2 iterations, 16: print cycles per phase
     if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern, a.kz);
     const int rt = ((r > c ? r : c) + 31) / 32;
     switch (rt) {
