@@ -88,8 +88,10 @@ __device__ void tridiagonalise(double *A, int n, double *d, double *e, double *t
                     const int i = lane + 32 * t;
                     pv[t] = 0.0;
                     if (i >= m0 && i < n) {
-                        double s = 0.0;
-                        for (int part = 0; part < NP; part++) s += pp[part * n + i];
+                        double x[8];                             // NP <= 8 partial sums, loaded together
+#pragma unroll
+                        for (int part = 0; part < 8; part++) x[part] = part < NP ? pp[part * n + i] : 0.0;
+                        const double s = ((x[0] + x[1]) + (x[2] + x[3])) + ((x[4] + x[5]) + (x[6] + x[7]));
                         pv[t] = beta * s;
                         up = fma(u[i], pv[t], up);
                     }
@@ -179,11 +181,16 @@ __device__ void top_eigenvalues(const double *d, const double *e2, int n, int m,
     }
 }
 
+// 1/x to ~1 ulp for normal x well inside the exponent range (pivots of T - lam I, floored at eps |T|)
+__device__ __forceinline__ double rcp_pivot(double x) {
+    return (fabs(x) > 1e-290 && fabs(x) < 1e290) ? rcp_newton(x) : 1.0 / x;
+}
+
 // Inverse iteration for one eigenvector of the tridiagonal (d, e) at the shift lamj: LU of T - lamj I with partial
 // pivoting (multipliers F, reciprocal pivots RD, swap flags SW, all interleaved over the kst vectors of the CTA: entry
 // i of vector j at [i kst + j]); the super-diagonals of U follow from the flags.  v (n doubles) receives the unit
 // eigenvector; returns the squared residual |T v - lamj v|^2.
-__device__ double tri_inverse_iteration(const double *d, const double *e, int n, double lamj, int j, int kst, double *F,
+__device__ __forceinline__ double tri_inverse_iteration(const double *d, const double *e, int n, double lamj, int j, int kst, double *F,
                                         double *RD, int *SW, double *v, double tnorm) {
     const double tiny = fmax(DBL_EPSILON * tnorm, DBL_MIN);
     double di = d[0] - lamj, dui = e[0];
@@ -192,13 +199,13 @@ __device__ double tri_inverse_iteration(const double *d, const double *e, int n,
         const size_t o = (size_t)i * kst + j;
         if (fabs(di) >= fabs(dli)) {
             if (di == 0.0) di = tiny;
-            const double f = dli / di;
-            F[o] = f; RD[o] = 1.0 / di; SW[o] = 0;
+            const double rd = rcp_pivot(di), f = dli * rd;
+            F[o] = f; RD[o] = rd; SW[o] = 0;
             di = dnext - f * dui;
             dui = dunext;
         } else {
-            const double f = di / dli;
-            F[o] = f; RD[o] = 1.0 / dli; SW[o] = 1;
+            const double rd = rcp_pivot(dli), f = di * rd;
+            F[o] = f; RD[o] = rd; SW[o] = 1;
             di = dui - f * dnext;
             dui = -f * dunext;
         }

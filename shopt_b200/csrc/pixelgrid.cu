@@ -570,7 +570,10 @@ __device__ __noinline__ void smooth_sep(const double *R, double *out, int r, int
     }
 }
 // rows handled by one lane in the Jacobi kernels: i = lane + 32 t, t < RT  (32 RT >= max(r, c))
-template <int NW, int RT>
+// GW: the W / Y buffers live in the per-CTA global scratch (stamps too large for shared memory).  With GW = false every
+// pointer derived from W is provably a shared-memory address, so the compiler emits LDS/STS with 32-bit addressing
+// instead of generic LD/ST with 64-bit address arithmetic.
+template <int NW, int RT, bool GW>
 __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int r = a.r, c = a.c;
@@ -592,7 +595,9 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
     int *yoff = uoff + kmaxp;
     int *ford = yoff + kmaxp;
     double *tail = reinterpret_cast<double *>(ford + FB);
-    double *W = a.wglobal ? a.wglobal + (size_t)blockIdx.x * a.wstride : tail;
+    double *W;
+    if constexpr (GW) W = a.wglobal + (size_t)blockIdx.x * a.wstride;
+    else W = tail;
     double *Y = W + rc;
     double *FQ = Y, *FQn = FQ + FB * ldq, *FT = FQn + FB * ldq, *FG = FT + FB * c;
     int buf = 0;
@@ -646,7 +651,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         const bool fastk = k > 0;
         if (prof && tid == 0) prof[2] = clock64();
         bool eigk = false;
-        if (!fastk && a.eigscratch && r <= c && r >= 16 && r <= nthr && r <= 32 * RT) {
+        if (!GW && !fastk && a.eigscratch && r <= c && r >= 16 && r <= nthr && r <= 32 * RT) {
             // ---- direct path: eigenvectors of the r x r Gram matrix (pca_eig.cuh); 0 = a check failed ----
             double *Cg = a.eigscratch + (size_t)blockIdx.x * a.eigstride;
             k = gram_eig_pca<NW, RT>(W, r, c, a.ncomp, a.pratio, Y, det, sv, fth, s_flag, Cg, Cg + (size_t)r * r, prof);
@@ -1009,7 +1014,13 @@ static int pca_launch_t(PcaArgs a, double *scratch, size_t scratch_bytes, cudaSt
     } else if (a.eigstride && scratch && (size_t)grid * a.eigstride * 8 <= scratch_bytes) {
         a.eigscratch = scratch;
     }
-    auto kern = pca_kernel<NW, RT>;
+    void (*kern)(const PcaArgs) = nullptr;
+    if (a.wglobal) {
+        if constexpr (RT >= 5) kern = pca_kernel<NW, RT, true>;
+    } else {
+        if constexpr (RT <= 5) kern = pca_kernel<NW, RT, false>;
+    }
+    if (!kern) return SHOPT_E_UNSUPPORTED;                       // unreachable: 32 RT >= max(r, c) fixes which layout fits
     SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (grid > a.N) grid = a.N;
     SHOPT_CUDA_TRY(cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), st));
