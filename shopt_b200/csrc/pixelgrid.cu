@@ -502,9 +502,16 @@ __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, do
 // register window that rotates by full unrolling (no moves, no local memory), so a pixel costs 2 LA + 1 shared loads
 // and 2 (2 LA + 1) FMAs instead of (2 LA + 1)^2 loads.  Lanes run along i: conflict-free shared reads, coalesced stores.
 // ---------------------------------------------------------------------------------------------
-template <int LA>
-__device__ __noinline__ void smooth_sep(const double *R, double *out, int r, int c, const double *kz, int nthr) {
+// SH: R is known to lie in the CTA's dynamic shared memory; the pointer is re-derived from the shared base so that the
+// (not inlined) body reads it with LDS instead of generic loads.
+template <int LA, bool SH = false>
+__device__ __noinline__ void smooth_sep(const double *Rg, double *out, int r, int c, const double *kz, int nthr) {
     constexpr int KW = 2 * LA + 1;
+    const double *R = Rg;
+    if constexpr (SH) {
+        extern __shared__ __align__(16) unsigned char smem_sep[];
+        R = reinterpret_cast<const double *>(smem_sep + (__cvta_generic_to_shared(Rg) - __cvta_generic_to_shared(smem_sep)));
+    }
     int nseg = nthr / r;
     if (nseg < 1) nseg = 1;
     if (nseg > c) nseg = c;
@@ -806,7 +813,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
                 __syncthreads();
             }
             if (!nonfinite && a.lanczos_a == 3) {            // the shipped default (shopt.yml lanczos: 3)
-                smooth_sep<3>(W, out, r, c, a.kz, nthr);
+                smooth_sep<3, !GW>(W, out, r, c, a.kz, nthr);
             } else {                                         // NaN-aware renormalisation, tap by tap like the reference
                 const int la = a.lanczos_a, kw = 2 * la + 1;
                 for (long long p = tid; p < rc; p += nthr) {
@@ -888,7 +895,7 @@ __global__ void __launch_bounds__(512) smooth_kernel(const SmoothArgs a) {
                 for (long long p = threadIdx.x; p < rc; p += 512) out[p] = R[p];
                 continue;
             }
-            if (!bad && la == 3) { smooth_sep<3>(R, out, r, c, skz, 512); continue; }
+            if (!bad && la == 3) { smooth_sep<3, true>(R, out, r, c, skz, 512); continue; }
         }
         const double *src = a.use_smem ? R : X;
         const bool ntz = a.nan_to_zero && !a.use_smem;
