@@ -1,22 +1,25 @@
 #!/usr/bin/env python
 """bench.py -- stars/s of the per-star PSF fitting stage (analytic LBFGS model fit + PCA pixel-grid fit + learned
-analytic fit + degree-3 (u,v) polynomial interpolation with 3 rounds of worst-10 % rejection) on synthetic catalogues.
+analytic fit + degree-n (u,v) polynomial interpolation with rounds of worst-10 % rejection) on synthetic catalogues.
 
-  python bench.py --gpus N --steps K --warmup W            our arm   (N > 1: launched by torch.distributed.run)
-  python bench.py --impl reference ...                     the reference algorithm on the host cores (CPU oracle port)
+  python bench.py --gpus N --steps K --warmup W [--config c3]   our arm   (N > 1: launched by torch.distributed.run)
+  python bench.py --impl reference ...                           the reference algorithm on the host cores (CPU port)
 
-A "step" is one pass of the whole stage over one synthetic catalogue.  Workload (BASELINE.json configs[2], the one
-the metric "stars/sec fitted (LBFGS+PCA+poly interp)" is quoted on): 100 000 stars of 131 x 131 per GPU, n_a = 64,
-PCAterms = 50, lanczos = 3, degree 3, training_ratio 0.9, 3 rounds.  Sharding is weak (100k stars per GPU).
-Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for what each key means.
+A "step" is one pass of the whole stage over one synthetic catalogue.  Workloads (SURVEY.md section 8d / BASELINE.json):
+  c3 (default, configs[2], the one the metric is quoted on): 100 000 stars of 131 x 131 per GPU, n_a = 64, PCAterms 50,
+     lanczos 3, degree 3, training_ratio 0.9, 3 rounds;
+  c4: as c3 with 1 % masked pixels, 2 % contaminated stars, 1 % bad-s stars, 125 000 stars per GPU (1M on 8 GPUs);
+  c5: 301 x 301 stamps, n_a = 128, degree 5, 6 250 stars per GPU (50k on 8 GPUs);
+  c2: 10 000 stars of 75 x 75, n_a = 75, analytic model fit only, 1 GPU.
+Sharding is weak (fixed stars per GPU).  Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement".
 """
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
+import types
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -25,6 +28,14 @@ if ROOT not in sys.path:
 METRIC = "stars/sec fitted (LBFGS+PCA+poly interp)"
 UNIT = "stars/s"
 
+CONFIGS = {
+    "c2": dict(stars=10000, stamp=75, n_a=75, degree=3, fit_only=True, mix={}),
+    "c3": dict(stars=100000, stamp=131, n_a=64, degree=3, fit_only=False, mix={}),
+    "c4": dict(stars=125000, stamp=131, n_a=64, degree=3, fit_only=False,
+               mix=dict(frac_masked=0.01, frac_contaminated=0.02, frac_bad_s=0.01)),
+    "c5": dict(stars=6250, stamp=301, n_a=128, degree=5, fit_only=False, mix={}),
+}
+
 
 def parse_args():
     ap = argparse.ArgumentParser()
@@ -32,41 +43,68 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--stars", type=int, default=100000, help="stars per GPU")
-    ap.add_argument("--stamp", type=int, default=131)
-    ap.add_argument("--n-a", type=int, default=64)
-    ap.add_argument("--degree", type=int, default=3)
-    ap.add_argument("--cpu-sample", type=int, default=2048, help="stars of the CPU baseline sample")
+    ap.add_argument("--config", default="c3", choices=sorted(CONFIGS))
+    ap.add_argument("--stars", type=int, default=None, help="stars per GPU (default: the config's)")
+    ap.add_argument("--stamp", type=int, default=None)
+    ap.add_argument("--n-a", type=int, default=None)
+    ap.add_argument("--degree", type=int, default=None)
+    ap.add_argument("--cpu-sample", type=int, default=None, help="stars of the CPU baseline sample")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--no-sampler", action="store_true", help="A/B: no clock sampling thread during the timed loop")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "library", "callback"])
+    args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    for k in ("stars", "stamp", "degree"):
+        if getattr(args, k) is None:
+            setattr(args, k, cfg[k])
+    if args.n_a is None:
+        args.n_a = cfg["n_a"]
+    args.fit_only, args.mix = cfg["fit_only"], cfg["mix"]
+    if args.cpu_sample is None:      # ~10-30 s of CPU work on 16 cores
+        args.cpu_sample = {"c2": 4096, "c3": 2048, "c4": 1024, "c5": 256}[args.config]
+    return args
+
+
+PARAM_FIELDS = dict(n_a=64, g_tol_model=1e-6, g_tol_learned=1e-6, max_iter=1000, s_lo=0.075, s_hi=1.0, pca_terms=50,
+                    pratio=0.99, lanczos=3, unity_sum=0, degree=3, iterations=3, training_ratio=0.9, median_constraint=0,
+                    sigma_clip=0, mode=0, chisq_fill=0.0)
+
+
+def stage_params_plain(args):
+    """The shopt_params fields as a plain namespace: what the CPU arms use (they never load libshopt_b200.so)."""
+    d = dict(PARAM_FIELDS, n_a=args.n_a, degree=args.degree)
+    return types.SimpleNamespace(**d)
 
 
 def stage_params(args):
     from shopt_b200 import pipeline
-    return pipeline.default_params(n_a=args.n_a, degree=args.degree, iterations=3, training_ratio=0.9, pca_terms=50,
-                                   lanczos=3, unity_sum=0, g_tol_model=1e-6, g_tol_learned=1e-6)
+    d = dict(PARAM_FIELDS, n_a=args.n_a, degree=args.degree)
+    return pipeline.default_params(**d)
 
 
 def workload_config(args, n_gpus):
-    return {"workload": "synthetic %dk Gaussian-PSF stars per GPU, %dx%d stamps, analytic(n_a=%d)+PCA(n=50)+degree-%d "
-                        "(u,v) interpolation, 3 rounds" % (args.stars // 1000, args.stamp, args.stamp, args.n_a, args.degree),
-            "stars_per_gpu": args.stars, "stars_total": args.stars * n_gpus, "stamp": args.stamp, "n_a": args.n_a,
-            "pca_terms": 50, "degree": args.degree, "iterations": 3, "training_ratio": 0.9,
-            "sharding": "stars, contiguous shards, dp%d" % n_gpus,
+    what = ("analytic(n_a=%d) model fit only" % args.n_a) if args.fit_only else (
+        "analytic(n_a=%d)+PCA(n=50)+degree-%d (u,v) interpolation, 3 rounds" % (args.n_a, args.degree))
+    mix = (", " + ", ".join("%s=%g" % kv for kv in sorted(args.mix.items()))) if args.mix else ""
+    return {"workload": "%s: synthetic %d Gaussian-PSF stars per GPU, %dx%d stamps, %s%s"
+                        % (args.config, args.stars, args.stamp, args.stamp, what, mix),
+            "name": args.config, "stars_per_gpu": args.stars, "stars_total": args.stars * n_gpus, "stamp": args.stamp,
+            "n_a": args.n_a, "pca_terms": 50, "degree": args.degree, "iterations": 3, "training_ratio": 0.9,
+            "mix": args.mix, "sharding": "stars, contiguous shards, dp%d" % n_gpus,
             "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2; no flush needed" % (args.stars * args.stamp ** 2 * 8 / 1e9)}
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clocks / throttle reasons DURING the timed region through in-process NVML, at 2 Hz plus one sample at each
+    edge of the loop.  (Round 1 sampled at 20 Hz; on some boxes each NVML call then took 10-16 ms and contended with the
+    CUDA runtime for driver locks -- see profiles/README.md.)"""
 
-    def __init__(self, index):
-        self.index, self.rows, self.stop, self.t = index, [], threading.Event(), None
+    def __init__(self, index, enabled=True):
+        self.rows, self.stop, self.t, self.enabled = [], threading.Event(), None, enabled
         self.nvml = None
-        try:   # in-process NVML: a query costs microseconds; spawning nvidia-smi stalls the driver for ~100 ms per call,
-            import pynvml   # which at 2+ ranks showed up as +70 % step time
+        try:
+            import pynvml
             pynvml.nvmlInit()
             try:
                 import torch
@@ -78,91 +116,111 @@ class ClockSampler:
         except Exception:
             self.nvml = None
 
-    def _sample_nvml(self):
-        nv, h = self.nvml
-        sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
-        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+    def sample(self):
+        if not self.nvml:
+            return
         try:
-            bits = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+            nv, h = self.nvml
+            sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            try:
+                bits = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+            except Exception:
+                bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            self.rows.append((sm, mx, bits))
         except Exception:
-            bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-        act = lambda m: "Active" if bits & m else "Not Active"
-        return [str(sm), str(mx), act(0x8), act(0x40), act(0x20), act(0x4)]
+            pass
 
     def _run(self):
-        while not self.stop.is_set():
-            try:
-                if self.nvml:
-                    self.rows.append(self._sample_nvml())
-                else:
-                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                    self.rows.append([x.strip() for x in out.strip().split(",")])
-            except Exception:
-                pass
-            self.stop.wait(0.05 if self.nvml else 0.5)
+        while not self.stop.wait(0.5):
+            self.sample()
 
     def __enter__(self):
-        self.t = threading.Thread(target=self._run, daemon=True)
-        self.t.start()
+        if self.enabled:
+            self.t = threading.Thread(target=self._run, daemon=True)
+            self.t.start()
         return self
 
     def __exit__(self, *a):
         self.stop.set()
-        self.t.join(timeout=6)
+        if self.t:
+            self.t.join(timeout=6)
 
     def summary(self):
-        sm, mx, reasons = [], 0.0, set()
+        sm = sorted(r[0] for r in self.rows)
+        mx = max([r[1] for r in self.rows], default=None)
+        bits = 0
         for r in self.rows:
-            if len(r) < 6:
-                continue
-            try:
-                sm.append(float(r[0])); mx = max(mx, float(r[1]))
-            except ValueError:
-                continue
-            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+            bits |= r[2]
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(v for k, v in names.items() if bits & k), "samples": len(sm),
+                "sampler": "nvml, 2 Hz + loop edges" if self.enabled else "nvml, loop edges only"}
 
 
 # --------------------------------------------------------------------------------------------------------------
 # CPU side: the reference's algorithm on the host cores (oracle port; the reference itself is Julia and cannot run
 # on this box -- SURVEY.md 8c).  Used for `cpu_baseline` (rank 0, N = 1) and for the whole `--impl reference` arm.
+# Nothing here loads libshopt_b200.so.
 # --------------------------------------------------------------------------------------------------------------
-def cpu_stage_once(args, sample, seed_shift=0):
-    """One pass of the whole stage on `sample` stars with every host thread; returns (seconds, threads)."""
-    import numpy as np
+def host_threads():
+    """Threads the CPU arms use: every core this process may run on.  torch.distributed.run exports OMP_NUM_THREADS=1,
+    so omp_get_max_threads() is not trusted; the count is passed to the oracle explicitly."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_catalog(args, sample, seed_shift=0):
+    from shopt_b200 import synth          # pure torch: manufactures inputs only
+    cat = synth.make_catalog(sample, args.stamp, args.n_a, seed=synth.SEED + 1000 + seed_shift, **args.mix)
+    return {k: cat[k].numpy() for k in ("stamps", "u", "v", "x0_model", "x0_learned", "perm")}
+
+
+def cpu_stage_once(args, a, nthreads, serial_stars=False):
+    """One pass of the workload on the catalogue `a`; returns (seconds, result).  serial_stars: the star loops run on
+    one thread and only the polyfit is threaded -- the shape of the reference (shopt.jl:543 is its only @threads)."""
     from oracle import shopt_oracle as orc
     from oracle import stage_oracle
-    from shopt_b200 import synth
     orc.set_reference_shaped(1)        # value and gradient evaluated separately, like NLSolversBase's fg! does
-    nthr = orc.max_threads()
-    cat = synth.make_catalog(sample, args.stamp, args.n_a, seed=synth.SEED + seed_shift)
-    a = {k: cat[k].numpy() for k in ("stamps", "u", "v", "x0_model", "x0_learned", "perm")}
-    p = stage_params(args)
+    p = stage_params_plain(args)
     t0 = time.perf_counter()
-    stage_oracle.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], a["perm"], nthreads=nthr)
-    return time.perf_counter() - t0, nthr
+    res = stage_oracle.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], a["perm"],
+                                 nthreads=1 if serial_stars else nthreads, nthreads_poly=nthreads, fit_only=args.fit_only)
+    return time.perf_counter() - t0, res
 
 
-def cpu_baseline(args):
-    sec, nthr = cpu_stage_once(args, args.cpu_sample)
-    return {"value": args.cpu_sample / sec, "unit": UNIT, "cores": nthr, "kind": "port",
-            "sample": "%d stars of the same workload, whole stage once, OpenMP over stars (the reference's star loops are "
-                      "serial; only its polyfit is threaded), value+gradient evaluated reference-shaped" % args.cpu_sample,
-            "seconds": sec}
+def cpu_baseline(args, a, res_out):
+    nthr = host_threads()
+    sec, res = cpu_stage_once(args, a, nthr)
+    res_out.update(res)
+    n = a["stamps"].shape[0]
+    out = {"value": n / sec, "unit": UNIT, "cores": nthr, "kind": "port",
+           "sample": "%d stars of the same workload, whole stage once, OpenMP over stars with %d threads (a parallelism the "
+                     "reference lacks: its star loops are serial, only its polyfit is threaded), value+gradient evaluated "
+                     "reference-shaped; oracle built -O3 -march=native" % (n, nthr),
+           "seconds": sec}
+    ns = max(16, min(n, {"c2": 256, "c3": 96, "c4": 64, "c5": 16}.get(args.config, 64)))
+    import numpy as np
+    sub = {k: (v[:ns] if k != "perm" else None) for k, v in a.items()}
+    sub["perm"] = a["perm"][a["perm"] < ns].astype(np.int64)       # the first ns stars, in the permutation's order
+    sec_s, _ = cpu_stage_once(args, sub, nthr, serial_stars=True)
+    out["reference_shaped"] = {"value": ns / sec_s, "unit": UNIT, "cores": nthr, "seconds": sec_s,
+                               "sample": "%d stars, star loops on ONE thread, %d threads in the polyfit only "
+                                         "(mirrors shopt.jl: @threads at :543 only)" % (ns, nthr)}
+    return out
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    nthr = host_threads()
     times = []
     for i in range(args.warmup + args.steps):
-        sec, nthr = cpu_stage_once(args, args.cpu_sample, seed_shift=i)
+        a = cpu_catalog(args, args.cpu_sample, seed_shift=i)
+        sec, _ = cpu_stage_once(args, a, nthr)
         if i >= args.warmup:
             times.append(sec)
     ms = 1e3 * sum(times) / len(times)
@@ -173,8 +231,9 @@ def run_reference(args):
             "dtype": "f64", "data": "synthetic", "config": cfg, "gpu_launches": 0,
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": nthr, "kind": "port",
                              "sample": "each step = the whole stage on %d stars of the workload with %d OpenMP threads over "
-                                       "stars; the reference (Julia) is not runnable here, this is the CPU restatement in "
-                                       "oracle/ (reference-shaped evaluation)" % (args.cpu_sample, nthr)},
+                                       "stars (thread count passed explicitly); the reference (Julia) is not runnable here, "
+                                       "this is the CPU restatement in oracle/ (reference-shaped evaluation, -O3 "
+                                       "-march=native)" % (args.cpu_sample, nthr)},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -182,7 +241,14 @@ def run_reference(args):
 # --------------------------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------------------------
-KERNELS_PER_STEP = 4 + 2 + 3 * 7   # fit, pca, fit, flags; field normal + reduce; 3 rounds x (normal, gram, reduce, median_fix, solve, mse, mse_reduce)
+def load_ncu_facts(config):
+    """Per-kernel DRAM traffic and FP64-pipe activity from the committed ncu --set full capture of this workload
+    (profiles/ncu_facts.json, written by tools/ncu_facts.py from the .ncu-rep): bench.py cannot run ncu itself."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_facts.json")) as f:
+            return json.load(f).get(config, {})
+    except Exception:
+        return {}
 
 
 def run_ours(args):
@@ -190,7 +256,8 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from shopt_b200 import _lib, pipeline, synth
-    if not torch.cuda.is_available() or _lib.lib().shopt_device_count() < 1:
+    L = _lib.lib()
+    if not torch.cuda.is_available() or L.shopt_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -202,9 +269,10 @@ def run_ours(args):
     p = stage_params(args)
     n, r = args.stars, args.stamp
     n_global, offset = n * world, n * rank
-    cat = synth.make_catalog(n, r, args.n_a, seed=synth.SEED + rank, device=dev)
+    cat = synth.make_catalog(n, r, args.n_a, seed=synth.SEED + rank, device=dev, **args.mix)
     perm = np.random.default_rng(synth.SEED).permutation(n_global).astype(np.int64)
-    pgf = torch.empty(n, r, r, dtype=torch.float64, device=dev)
+    perm_dev = torch.from_numpy(perm).to(dev)
+    pgf = None if args.fit_only else torch.empty(n, r, r, dtype=torch.float64, device=dev)
     rc = r * r
 
     def barrier():
@@ -212,20 +280,31 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step():
-        return pipeline.run_stage_dev(p, cat["stamps"], cat["u"], cat["v"], cat["x0_model"], cat["x0_learned"], perm,
-                                      n_global=n_global, offset=offset, pgf=pgf)
+    fit_out = None
+    if args.fit_only:
+        from shopt_b200 import stage as stage_api
+
+        def step():
+            return stage_api.fit_analytic_batch(cat["stamps"], args.n_a, cat["x0_model"], p.g_tol_model, p.max_iter)
+    else:
+        def step():
+            return pipeline.run_stage_dev(p, cat["stamps"], cat["u"], cat["v"], cat["x0_model"], cat["x0_learned"], perm_dev,
+                                          n_global=n_global, offset=offset, pgf=pgf, exchange=args.exchange)
 
     for _ in range(args.warmup):
         out = step()
     barrier()
+    launches0 = L.shopt_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
+    with ClockSampler(local, enabled=not args.no_sampler) as clk:
+        clk.sample()
         ev0.record()
         for _ in range(args.steps):
             out = step()
         ev1.record()
         barrier()
+        clk.sample()
+    launches = L.shopt_launch_count() - launches0
     ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -241,50 +320,84 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback (of fallback)"
-    dom = max(stages, key=lambda k: stages[k]["ms"])
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s",
-                "frac": stages[dom]["gbs"] / peak, "traffic": None, "peak_source": peak_src,
-                "note": "the dominant kernel is FP64-compute-bound (Jacobi PCA); the HBM-bound kernels of the step are "
-                        "listed under stages with their own fractions",
-                "stages": {k: dict(v, frac=v["gbs"] / peak) for k, v in stages.items()},
-                "step_algorithmic_bytes_per_star": 6.878 * 8 * rc, "step_hbm_frac": value / world * 6.878 * 8 * rc / 1e9 / peak}
+    facts = load_ncu_facts(args.config)
+    # the dominant kernel by total device time in the step: launches of the same kernel are added up
+    per_kernel = {}
+    for name, sdict in stages.items():
+        k = name.split("(")[0]
+        e = per_kernel.setdefault(k, {"ms": 0.0, "bytes": 0.0, "launches": 0})
+        e["ms"] += sdict["ms"] * sdict.get("per_step", 1); e["bytes"] += sdict["bytes"] * sdict.get("per_step", 1)
+        e["launches"] += sdict.get("per_step", 1)
+    dom = max(per_kernel, key=lambda k: per_kernel[k]["ms"])
+    d = per_kernel[dom]
+    ach = d["bytes"] / d["ms"] / 1e6
+    kf = facts.get(dom, {})
+    dfma = measure_dfma(L)
+    bytes_per_star = (8 * args.n_a ** 2 + 56) if args.fit_only else 6.878 * 8 * rc
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": kf.get("dram_bytes_per_launch"), "traffic_source": kf.get("source"),
+                "peak_source": peak_src, "launches_per_step": d["launches"], "ms_per_step_in_kernel": d["ms"],
+                "fp64_pipe_pct": kf.get("fp64_pipe_pct"), "dfma_peak_tflops_measured": dfma,
+                "note": "the dominant kernel is FP64-pipe/issue bound (hundreds of flops per byte), so its HBM fraction is "
+                        "small by construction; fp64_pipe_pct (ncu sm__pipe_fp64_cycles_active) is its own roofline. The "
+                        "HBM-bound kernels (normal_kernel, mse_kernel) are listed under stages with their fractions",
+                "stages": {k: dict(v, frac=v["gbs"] / peak, **{kk: vv for kk, vv in facts.get(k.split("(")[0], {}).items()
+                                                             if kk in ("fp64_pipe_pct", "dram_bytes_per_launch")})
+                           for k, v in stages.items()},
+                "kernel_ms_sum": sum(v["ms"] * v.get("per_step", 1) for v in stages.values()),
+                "step_algorithmic_bytes_per_star": bytes_per_star,
+                "step_hbm_frac": value / world * bytes_per_star / 1e9 / peak}
 
     # ---- end to end: host buffers in, results out, copies inside the timed region ----
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(args, p, cat, perm, world, n_global, offset, pgf, barrier)
-    cpu = None
+        e2e = run_e2e(args, p, cat, perm, world, n_global, offset, barrier)
+    cpu, mismatch = None, None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_baseline(args)
+        a = cpu_catalog(args, args.cpu_sample)
+        want = {}
+        cpu = cpu_baseline(args, a, want)
+        mismatch = mismatch_rate(args, p, a, want)
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": workload_config(args, world), "clocks": clk.summary(),
-                "gpu_launches": KERNELS_PER_STEP * args.steps, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
-                "counts": out["counts"], "n_per_round": [int(x) for x in out["n_per_round"]]}
+                "gpu_launches": int(launches), "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
+                "mismatch_rate": mismatch}
+        if not args.fit_only:
+            line["counts"] = out["counts"]
+            line["n_per_round"] = [int(x) for x in out["n_per_round"]]
+            line["exchange"] = ("library NCCL communicator (shopt_comm_*)" if args.exchange != "callback" else
+                                "torch.distributed callback") if world > 1 else "none (one GPU)"
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
+def measure_dfma(L):
+    """Measured FP64 FMA peak of this GPU (TFLOP/s): 16 independent DFMA chains per thread, all SMs, CUDA events."""
+    import ctypes as C
+    out = C.c_double(0.0)
+    try:
+        if L.shopt_bench_dfma(C.byref(out)) != 0:
+            return None
+        return out.value
+    except Exception:
+        return None
+
+
 def stage_breakdown(args, p, cat, pgf, out):
     """Each kernel of the step timed alone with CUDA events on the launching (torch current) stream; GB/s from the
-    ALGORITHMIC bytes of DESIGN.md (what must cross HBM once), not from counters."""
+    ALGORITHMIC bytes of DESIGN.md (what must cross HBM once), not from counters.  per_step = how many launches of that
+    size one step holds (the polyfit rounds shrink by 10 % each: 1 + 0.9 + 0.81)."""
     import ctypes as C
     import torch
-    from shopt_b200 import _lib, stage
+    from shopt_b200 import _lib
     L = _lib.lib()
     n, r = args.stars, args.stamp
     rc = r * r
-    dev = pgf.device
+    dev = cat["stamps"].device
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    train = torch.nonzero(out["flags"] & _lib.FLAG_TRAINING).flatten().contiguous()
-    nt = int(train.numel())
-    K = (args.degree + 1) * (args.degree + 2) // 2
-    acc = torch.empty(L.shopt_polyfit_acc_len(r, r, args.degree), dtype=torch.float64, device=dev)
-    poly = torch.empty(K, r, r, dtype=torch.float64, device=dev)
-    mse = torch.empty(max(nt, 1), dtype=torch.float64, device=dev)
-    info = torch.zeros(4, dtype=torch.int32, device=dev)
     s = torch.empty(3, n, dtype=torch.float64, device=dev)
     ist = torch.empty(2, n, dtype=torch.int32, device=dev)
     u, v = cat["u"], cat["v"]
@@ -307,65 +420,127 @@ def stage_breakdown(args, p, cat, pgf, out):
     res = {}
     fit_bytes = n * (8 * args.n_a ** 2 + 32 + 24)
     t = timed(lambda: fit(cat["stamps"], cat["x0_model"], p.g_tol_model))
-    res["fit_kernel(model)"] = {"ms": t, "bytes": fit_bytes, "gbs": fit_bytes / t / 1e6}
+    res["fit_kernel(model)"] = {"ms": t, "bytes": fit_bytes, "gbs": fit_bytes / t / 1e6, "per_step": 1}
+    if args.fit_only:
+        return res
     t = timed(lambda: _lib.check(L.shopt_pca_batch_dev(cat["stamps"].data_ptr(), r, r, n, p.pca_terms, p.pratio, p.lanczos,
                                                        p.unity_sum, pgf.data_ptr(), ist[0].data_ptr(), ist[1].data_ptr(), st)))
-    res["pca_kernel"] = {"ms": t, "bytes": 2 * 8 * rc * n, "gbs": 2 * 8 * rc * n / t / 1e6}
+    res["pca_kernel"] = {"ms": t, "bytes": 2 * 8 * rc * n, "gbs": 2 * 8 * rc * n / t / 1e6, "per_step": 1}
     t = timed(lambda: fit(pgf, cat["x0_learned"], p.g_tol_learned))
-    res["fit_kernel(learned)"] = {"ms": t, "bytes": fit_bytes, "gbs": fit_bytes / t / 1e6}
+    res["fit_kernel(learned)"] = {"ms": t, "bytes": fit_bytes, "gbs": fit_bytes / t / 1e6, "per_step": 1}
+    train = torch.nonzero(out["flags"] & _lib.FLAG_TRAINING).flatten().contiguous()
+    nt = int(train.numel())
     if nt >= 5:
+        K = (args.degree + 1) * (args.degree + 2) // 2
+        acc = torch.empty(L.shopt_polyfit_acc_len(r, r, args.degree), dtype=torch.float64, device=dev)
+        poly = torch.empty(K, r, r, dtype=torch.float64, device=dev)
+        mse = torch.empty(max(nt, 1), dtype=torch.float64, device=dev)
+        info = torch.zeros(4, dtype=torch.int32, device=dev)
+        ctr = torch.empty(4, dtype=torch.float64, device=dev)
+        _lib.check(L.shopt_polyfit_centre_dev(u.data_ptr(), v.data_ptr(), n, ctr.data_ptr(), st))
+        w = 1 + 0.9 + 0.81
         t = timed(lambda: _lib.check(L.shopt_polyfit_normal_dev(pgf.data_ptr(), r, r, u.data_ptr(), v.data_ptr(),
-                                                                train.data_ptr(), nt, args.degree, acc.data_ptr(), st)), 3)
-        res["normal_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6}
-        t = timed(lambda: _lib.check(L.shopt_polyfit_solve_dev(acc.data_ptr(), r, r, args.degree, poly.data_ptr(),
-                                                               info.data_ptr(), st)), 3)
-        res["solve_kernel"] = {"ms": t, "bytes": 16 * K * rc, "gbs": 16 * K * rc / t / 1e6}
+                                                                train.data_ptr(), nt, args.degree, ctr.data_ptr(),
+                                                                acc.data_ptr(), st)), 3)
+        res["normal_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6, "per_step": w}
+        t = timed(lambda: _lib.check(L.shopt_polyfit_solve_dev(acc.data_ptr(), r, r, args.degree, ctr.data_ptr(), nt,
+                                                               poly.data_ptr(), info.data_ptr(), st)), 3)
+        res["solve_kernel(+factor)"] = {"ms": t, "bytes": 16 * K * rc, "gbs": 16 * K * rc / t / 1e6, "per_step": 3}
         t = timed(lambda: _lib.check(L.shopt_polyfit_mse_dev(pgf.data_ptr(), r, r, u.data_ptr(), v.data_ptr(),
                                                              train.data_ptr(), nt, args.degree, poly.data_ptr(),
                                                              mse.data_ptr(), st)), 3)
-        res["mse_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6}
+        res["mse_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6, "per_step": w}
     return res
 
 
-def run_e2e(args, p, cat, perm, world, n_global, offset, pgf, barrier):
+def run_e2e(args, p, cat, perm, world, n_global, offset, barrier):
     """The same step through the public API with HOST buffers: pinned inputs -> H2D -> stage -> D2H of the results
     (model/learned parameters, flags, polynomial cube) through the C ABI host entry points: shopt_stage_run at N = 1,
-    shopt_stage_run_comm (this rank's shard + the all-reduce callback) at N > 1; the copies happen inside the library,
-    chunked and overlapped with the per-star kernels."""
+    shopt_stage_run_comm (this rank's shard + the library's NCCL communicator) at N > 1; the copies happen inside the
+    library, chunked and overlapped with the per-star kernels.  Two input formats are timed: the FITS-native float32
+    VIGNET cube (what the reference reads: dataPreprocessing.jl:312 converts on ingest; here the widening runs on the
+    device) -- the headline -- and a float64 cube of the same stamps."""
     import numpy as np
     import torch
     import torch.distributed as dist
-    from shopt_b200 import pipeline
+    from shopt_b200 import pipeline, stage as stage_api
     n, r = args.stars, args.stamp
     K = (args.degree + 1) * (args.degree + 2) // 2
-    names = ("stamps", "u", "v", "x0_model", "x0_learned")
-    host = {k: torch.empty(cat[k].shape, dtype=torch.float64, pin_memory=True) for k in names}
-    for k in names:
+    small = ("u", "v", "x0_model", "x0_learned")
+    host = {k: torch.empty(cat[k].shape, dtype=torch.float64, pin_memory=True) for k in small}
+    for k in small:
         host[k].copy_(cat[k])
-    torch.cuda.synchronize()
-    h2d = sum(host[k].numel() * 8 for k in names)
-    d2h = 8 * (6 * n + K * r * r) + 8 * n
-    steps = max(1, min(args.steps, 2))
+    res = {}
+    for fmt in ("f32", "f64"):
+        dt = torch.float32 if fmt == "f32" else torch.float64
+        stamps = torch.empty(cat["stamps"].shape, dtype=dt, pin_memory=True)
+        stamps.copy_(cat["stamps"])             # float32: rounds the synthetic stamps to the FITS dtype
+        torch.cuda.synchronize()
+        h2d = stamps.numel() * stamps.element_size() + sum(host[k].numel() * 8 for k in small)
+        d2h = 8 * 3 * n if args.fit_only else 8 * (6 * n + K * r * r) + 8 * n
+        a = {k: host[k].numpy() for k in small}
+        a["stamps"] = stamps.numpy()
 
-    def once():
-        a = {k: host[k].numpy() for k in names}
-        if world == 1:
-            return pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], perm, want_pgf=False)
-        return pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], perm, want_pgf=False,
-                                  n_global=n_global, offset=offset)
-    once()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(steps):
+        def once():
+            if args.fit_only:
+                if fmt == "f32":
+                    return None
+                return stage_api.fit_analytic_batch(a["stamps"], args.n_a, a["x0_model"], p.g_tol_model, p.max_iter)
+            if world == 1:
+                return pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], perm, want_pgf=False)
+            return pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], perm, want_pgf=False,
+                                      n_global=n_global, offset=offset, exchange=args.exchange)
+        if args.fit_only and fmt == "f32":
+            continue
         once()
-    barrier()
-    sec = torch.tensor([(time.perf_counter() - t0) / steps], dtype=torch.float64, device=pgf.device)
-    if world > 1:
-        dist.all_reduce(sec, op=dist.ReduceOp.MAX)
-    return {"value": n_global / float(sec.item()), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "ms_per_step": 1e3 * float(sec.item()), "steps": steps,
-            "api": "shopt_stage_run (C ABI, host buffers)" if world == 1 else
-            "shopt_stage_run_comm (C ABI, host buffers of the shard, torch.distributed all-reduce callback)"}
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            once()
+        barrier()
+        sec = torch.tensor([(time.perf_counter() - t0) / args.steps], dtype=torch.float64, device=cat["stamps"].device)
+        if world > 1:
+            dist.all_reduce(sec, op=dist.ReduceOp.MAX)
+        res[fmt] = {"value": n_global / float(sec.item()), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": 1e3 * float(sec.item()), "steps": args.steps}
+        del stamps, a
+    head = res.get("f32") or res["f64"]
+    api = ("shopt_fit_analytic_batch (C ABI, host buffers)" if args.fit_only else
+           "shopt_stage_run (C ABI, host buffers)" if world == 1 else
+           "shopt_stage_run_comm (C ABI, host buffers of the shard, library NCCL communicator)")
+    out = dict(head, api=api, input="float32 VIGNET cube (FITS-native), widened on the device" if "f32" in res else "float64 stamps")
+    if "f32" in res:
+        out["float64_input"] = res["f64"]
+    return out
+
+
+def mismatch_rate(args, p, a, want):
+    """GPU vs oracle on the CPU-baseline sample of the workload (outside every timed region): the fraction of stars whose
+    fitted (s, g1, g2) differ by more than 1e-6 relative (trajectory-chaotic starts), whether the
+    flags / selection are bit-identical, and the largest relative coefficient difference."""
+    import numpy as np
+    from shopt_b200 import pipeline, stage as stage_api
+
+    def agree(x, y, tol=1e-6):
+        gn = np.hypot(y[1], y[2])
+        with np.errstate(invalid="ignore"):
+            ok = (np.abs(x[0] - y[0]) <= tol * np.abs(y[0])) & (np.abs(x[1] - y[1]) <= tol * gn) & (np.abs(x[2] - y[2]) <= tol * gn)
+        return ok | ~np.isfinite(y).all(axis=0)
+    if args.fit_only:
+        s, g1, g2, _, _ = stage_api.fit_analytic_batch(a["stamps"], args.n_a, a["x0_model"], p.g_tol_model, p.max_iter)
+        ok = agree(np.stack([s, g1, g2]), want["model"])
+        return {"stars": int(len(s)), "model_fit": float(1.0 - ok.mean())}
+    got = pipeline.run_stage(p, a["stamps"], a["u"], a["v"], a["x0_model"], a["x0_learned"], a["perm"], want_pgf=False)
+    okm = agree(got["model"], want["model"])
+    live = (want["flags"] & 2) == 0
+    okl = agree(got["learned"][:, live], want["learned"][:, live])
+    scale = np.abs(want["poly"]).max(axis=(1, 2), keepdims=True)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        cerr = float(np.nanmax(np.abs(got["poly"] - want["poly"]) / scale))
+    return {"stars": int(a["stamps"].shape[0]), "model_fit": float(1.0 - okm.mean()), "learned_fit": float(1.0 - okl.mean()),
+            "flags_identical": bool(np.array_equal(got["flags"], want["flags"])),
+            "pca_k_identical": bool(np.array_equal(got["pca_k"], want["pca_k"])),
+            "counts_identical": got["counts"] == want["counts"], "max_rel_coef_err": cerr, "tol": 1e-6}
 
 
 def main():

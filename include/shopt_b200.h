@@ -58,6 +58,27 @@ int         shopt_last_timing(double ms[3]);
 /* The host entry points keep their large device blocks (stamp cube, pixel-grid cube, scratch) between calls on the
  * calling thread's context; this frees them. */
 int         shopt_release_buffers(void);
+/* kernels this process has launched so far (every launch function of the library counts what it enqueues) */
+int64_t     shopt_launch_count(void);
+/* measured FP64 FMA throughput of the current device in TFLOP/s (a 10 ms micro-benchmark; the compute roofline of the
+ * FP64-bound kernels, reported by bench.py next to the HBM roofline) */
+int         shopt_bench_dfma(double *tflops_out);
+
+/* ---- communicator of a sharded run (one process per GPU) --------------------------------------------
+ * The reference has no distributed mode; stars shard naturally and the stage's only exchanges are sum-all-reduces of
+ * small device buffers.  The library owns its NCCL communicator (bound at run time with dlopen, so single-GPU users
+ * need no NCCL): rank 0 calls shopt_comm_unique_id and hands the 128 bytes to the other ranks by any means (a file,
+ * MPI, torch.distributed, Julia's Distributed); every rank then calls shopt_comm_init on its device.
+ * shopt_comm_allreduce is a shopt_allreduce_fn whose `user` is the shopt_comm*: pass the pair to shopt_stage_run_dev /
+ * shopt_stage_run_comm and every exchange is enqueued on the stage's stream from C. */
+#define SHOPT_UNIQUE_ID_BYTES 128
+typedef struct shopt_comm shopt_comm;
+int shopt_comm_unique_id(void *id_out /* SHOPT_UNIQUE_ID_BYTES */);
+int shopt_comm_init(const void *id_in, int rank, int world, shopt_comm **out);
+int shopt_comm_destroy(shopt_comm *c);
+int shopt_comm_rank(const shopt_comm *c);
+int shopt_comm_world(const shopt_comm *c);
+int shopt_comm_allreduce(void *d_buf, int64_t count, int dtype, void *stream, void *user);
 
 /* ---- (0) ingest: the per-star work of cataloging() that precedes the stage --------------------------
  * Replaces, in dataPreprocessing.jl:342-397 (FITS decoding stays with astropy / CFITSIO):
@@ -162,17 +183,32 @@ int shopt_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, c
                   int median_constraint, int sigma_clip, double *poly_out, double *mse_out,
                   int64_t *kept_idx, int64_t *n_kept, int64_t *n_per_round);
 
-/* Building blocks of one round on device buffers (what shopt_polyfit and the multi-GPU host loop call).
- *  normal_dev : acc[0..K*K) += V'V, acc[K*K .. K*K + K*r*c) += V'P over the listed stars of this shard
- *               (acc is zeroed by the call; layout V'P[k*rc + px]); the buffer every rank all-reduces.
- *  solve_dev  : Cholesky of V'V, back-substitution for every pixel -> poly (r,c,K).
- *               Returns SHOPT_OK; *d_info (device int) != 0 when V'V is not positive definite.
- *  mse_dev    : mse[t] = mean_px (sum_k poly[px,k] u_t^p v_t^q - pgf[idx_t, px])^2 for the listed stars. */
+/* Building blocks of one round on device buffers (what shopt_polyfit and the stage call).
+ *  normal_dev : acc[0..K*K) = V'V, acc[K*K .. K*K + K*r*c) = V'P over the listed stars of this shard (layout
+ *               V'P[k*rc + px]); the buffer every rank all-reduces.  V is built from CENTRED, SCALED coordinates
+ *               ((u - u0)/su, (v - v0)/sv) when d_centre = {u0, 1/su, v0, 1/sv} (device) is given, raw when NULL:
+ *               the reference passes raw sky coordinates (RA ~ 150, Dec ~ 2), for which V'V in raw monomials is useless.
+ *  solve_dev  : A \ z of interpolate.jl:138 for every pixel from those normal equations: pivoted Cholesky in the
+ *               centred basis, then the K x K change of basis is factored by column-pivoted QR with LAPACK's rank rule
+ *               (rcond = min(n,K) eps) and minimum-norm completion, so poly (r,c,K) holds RAW-monomial coefficients with
+ *               the reference's meaning whether the design is well conditioned, ill conditioned or rank deficient.
+ *               n_rows = rows of the design matrix (training stars).  d_info (2 ints, device): numerical rank, SHOPT_POLY_* bits.
+ *  mse_dev    : mse[t] = mean_px (sum_k poly[px,k] u_t^p v_t^q - pgf[idx_t, px])^2 for the listed stars (raw u, v). */
+#define SHOPT_POLY_RANK_DEFICIENT  1  /* raw design numerically rank deficient: minimum-norm answer, like A \ z     */
+#define SHOPT_POLY_NONFINITE       2  /* NaN / Inf in the normal equations: coefficients are NaN                    */
+#define SHOPT_POLY_ILL_CONDITIONED 4  /* centred design nearly dependent: the normal equations lose digits          */
 int64_t shopt_polyfit_acc_len(int r, int c, int degree);                   /* K*K + K*r*c doubles */
+int shopt_polyfit_centre_dev(const double *d_u, const double *d_v, int64_t n, double *d_centre /* 4 */, void *stream);
 int shopt_polyfit_normal_dev(const double *d_pgf, int r, int c, const double *d_u, const double *d_v,
-                             const int64_t *d_idx, int64_t n, int degree, double *d_acc, void *stream);
-int shopt_polyfit_solve_dev(const double *d_acc, int r, int c, int degree, double *d_poly,
-                            int32_t *d_info, void *stream);
+                             const int64_t *d_idx, int64_t n, int degree, const double *d_centre, double *d_acc,
+                             void *stream);
+int shopt_polyfit_solve_dev(const double *d_acc, int r, int c, int degree, const double *d_centre, int64_t n_rows,
+                            double *d_poly, int32_t *d_info, void *stream);
+/* The K x K part of that solve on the host (no device needed): G = V'V (K x K, row-major) in the basis `centre`
+ * describes (NULL = raw), b (K, nrhs) right-hand sides V'z stored b[k * nrhs + j] -> coef[k * nrhs + j] raw-monomial
+ * coefficients.  Returns the numerical rank (K = full) or a negative SHOPT_E_*; info_out receives SHOPT_POLY_* bits. */
+int shopt_polyfit_factor_host(const double *G, int degree, const double *centre, int64_t n_rows, const double *b,
+                              int nrhs, double *coef, int32_t *info_out);
 int shopt_polyfit_mse_dev(const double *d_pgf, int r, int c, const double *d_u, const double *d_v,
                           const int64_t *d_idx, int64_t n, int degree, const double *d_poly,
                           double *d_mse, void *stream);
@@ -243,7 +279,8 @@ void shopt_default_params(shopt_params *p);     /* README.md:300-330 documented 
 
 #define SHOPT_FLAG_BLACKLISTED 1   /* model s out of [s_lo, s_hi]            (shopt.jl:166-171)   */
 #define SHOPT_FLAG_PCA_FAILED  2   /* pixel-grid fit failed -> zeros         (shopt.jl:305-309)   */
-#define SHOPT_FLAG_LEARNED_OOB 4   /* learned s out of bounds                (shopt.jl:384-386)   */
+#define SHOPT_FLAG_LEARNED_OOB 4   /* learned s out of bounds                (shopt.jl:384-386); a learned fit that THREW
+                                      has s = 0 from the catch (:387-393) but is NOT pushed to failedStars there       */
 #define SHOPT_FLAG_TRAINING    8   /* star was in the training split                              */
 #define SHOPT_FLAG_REJECTED   16   /* dropped by worst_10_percent in some round (shopt.jl:557-575) */
 
@@ -281,6 +318,15 @@ typedef struct shopt_stage_io {
      * field[10 j + k], j = s, g1, g2, the reference's coefficient order (see shopt_field_interp); HOST */
     double field[30];
     int32_t field_rank;          /* numerical rank of the cubic design matrix (10 = full)          */
+    /* ---- added in version 2 ---- */
+    int32_t polyfit_rank;        /* out: numerical rank of the last round's design matrix (K = full; 0 when no solve ran) */
+    int32_t polyfit_info;        /* out: SHOPT_POLY_* bits of the last round                       */
+    int32_t stamps_f32;          /* in, shopt_stage_run / _comm only: `stamps` is the raw FITS VIGNET cube in float32
+                                    (r, c, n_local); it is uploaded as such (half the bytes) and ingested on the device:
+                                    nanMask (masks.jl:5-17) and, with unity_sum, ./ sum(nanToZero(.))                  */
+    const int64_t *perm_dev;     /* in, optional: DEVICE copy of perm (saves the upload per call); perm may then be NULL */
+    int32_t *model_status, *model_iters;       /* out, optional (n_local): SHOPT_FIT_* and iterations of the model fit   */
+    int32_t *learned_status, *learned_iters;   /* out, optional (n_local): ... of the learned fit                        */
 } shopt_stage_io;
 
 /* Host logic of the split, exposed for sharded hosts and tests (shopt.jl:472-478): flags (n_global) = SHOPT_FLAG_* of
@@ -289,8 +335,11 @@ typedef struct shopt_stage_io {
 int64_t shopt_training_split(const int32_t *flags, int64_t n_global, const int64_t *perm, double training_ratio,
                              int64_t *train_out);
 
-/* device-resident shard; comm == NULL runs a single GPU.  Blocks until the stage is done (the outlier selection
- * between rounds runs on the host). */
+/* device-resident shard; comm == NULL runs a single GPU.  Blocks until the stage is done; the control flow between
+ * the kernels (survivor counts, training split, worst_10_percent, list compaction) runs on the device, the call
+ * synchronises the stream twice and allocates nothing after the first call of a given size.
+ * Sharded runs: median_constraint and NaN pixel-grid values among the training stars (chisq mode with masked pixels)
+ * need per-pixel medians across shards. */
 int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream);
 /* host buffers, one GPU: H2D (chunked on a copy stream, overlapped with the per-star kernels), stage, D2H */
 int shopt_stage_run(const shopt_params *p, shopt_stage_io *io);

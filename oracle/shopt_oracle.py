@@ -19,11 +19,28 @@ _LIB = None
 FIT_CONVERGED, FIT_MAXITER, FIT_LS_FAILED, FIT_NONFINITE, FIT_THREW = 0, 1, 2, 3, -1
 
 
+def _cpu_stamp():
+    """The library is built -march=native; a copy built on another CPU model must be rebuilt before it is loaded."""
+    try:
+        with open("/proc/cpuinfo") as f:
+            lines = [ln.split(":", 1)[1].strip() for ln in f if ln.startswith(("model name", "flags"))][:2]
+        return "|".join(lines)
+    except OSError:
+        return "unknown"
+
+
 def build(force=False):
     so = os.path.join(_HERE, "libshopt_oracle.so")
+    stamp = os.path.join(_HERE, ".build_cpu")
     src = [os.path.join(_HERE, f) for f in ("shopt_oracle.c", "shopt_oracle.h", "Makefile")]
-    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src):
-        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    same_cpu = os.path.exists(stamp) and open(stamp).read() == _cpu_stamp()
+    if force or not same_cpu or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
+        try:
+            with open(stamp, "w") as f:
+                f.write(_cpu_stamp())
+        except OSError:
+            pass
     return so
 
 

@@ -97,13 +97,17 @@ def pixel_grid_elementwise(mode, stamps, lanczos, unity_sum, weights=None, x0_pi
     return out
 
 
-def run_stage(p, stamps, u, v, x0_model, x0_learned, perm, nthreads=1, fit_only=False, weights=None, x0_pixels=None):
-    """p: any object with the shopt_params fields.  Returns the same dict layout as shopt_b200.pipeline.run_stage."""
+def run_stage(p, stamps, u, v, x0_model, x0_learned, perm, nthreads=1, fit_only=False, weights=None, x0_pixels=None,
+              nthreads_poly=None):
+    """p: any object with the shopt_params fields.  Returns the same dict layout as shopt_b200.pipeline.run_stage.
+    nthreads: threads of the per-star loops (the reference runs them serially); nthreads_poly: threads of the per-pixel
+    polyfit (the reference's only @threads loop, shopt.jl:543); default: nthreads."""
     N = stamps.shape[0]
-    s, g1, g2, _, _ = orc.fit_analytic_batch(stamps, p.n_a, x0_model, p.g_tol_model, p.max_iter, nthreads)
+    nthreads_poly = nthreads if nthreads_poly is None else nthreads_poly
+    s, g1, g2, mst, mit = orc.fit_analytic_batch(stamps, p.n_a, x0_model, p.g_tol_model, p.max_iter, nthreads)
     model = np.stack([s, g1, g2])
     if fit_only:
-        return dict(model=model)
+        return dict(model=model, model_status=mst, model_iters=mit)
     flags = np.zeros(N, np.int32)
     flags[(s < p.s_lo) | (s > p.s_hi)] |= FLAG_BLACKLISTED                         # shopt.jl:166-171
     mode = getattr(p, "mode", 0)
@@ -114,19 +118,22 @@ def run_stage(p, stamps, u, v, x0_model, x0_learned, perm, nthreads=1, fit_only=
                                      getattr(p, "chisq_fill", 0.0))
         k, pst = np.zeros(N, np.int32), np.zeros(N, np.int32)
     flags[pst == 1] |= FLAG_PCA_FAILED                                               # shopt.jl:305-309
-    sl, g1l, g2l, _, _ = orc.fit_analytic_batch(pgf, p.n_a, x0_learned, p.g_tol_learned, p.max_iter, nthreads)
-    flags[(sl < p.s_lo) | (sl > p.s_hi)] |= FLAG_LEARNED_OOB                        # shopt.jl:384-386
+    sl, g1l, g2l, lst, lit = orc.fit_analytic_batch(pgf, p.n_a, x0_learned, p.g_tol_learned, p.max_iter, nthreads)
+    # shopt.jl:384-386 sits INSIDE the try: a learned fit that threw lands in the catch (:387-393: s = g1 = g2 = 0) and
+    # is never pushed to failedStars
+    flags[((sl < p.s_lo) | (sl > p.s_hi)) & (lst != orc.FIT_THREW)] |= FLAG_LEARNED_OOB
     surv = flags == 0
     field = field_interp(u[surv], v[surv], sl[surv], g1l[surv], g2l[surv])        # shopt.jl:422-466
     n_train = int(np.rint(p.training_ratio * surv.sum()))                            # round(Int, .): half to even
     train = np.array([g for g in perm if surv[g]][:n_train], dtype=np.int64)
     flags[train] |= FLAG_TRAINING
-    res = orc.polyfit(pgf, u, v, train, p.degree, p.iterations, bool(p.median_constraint), bool(p.sigma_clip), nthreads)
+    res = orc.polyfit(pgf, u, v, train, p.degree, p.iterations, bool(p.median_constraint), bool(p.sigma_clip), nthreads_poly)
     rejected = np.setdiff1d(train, res["kept"])
     flags[rejected] |= FLAG_REJECTED
     black = (flags & FLAG_BLACKLISTED) != 0
     failed = ~black & ((flags & (FLAG_PCA_FAILED | FLAG_LEARNED_OOB)) != 0)
     return dict(model=model, learned=np.stack([sl, g1l, g2l]), pgf=pgf, flags=flags, pca_k=k, poly=res["poly"],
+                model_status=mst, model_iters=mit, learned_status=lst, learned_iters=lit,
                 n_per_round=res["n_per_round"][:p.iterations], field=field,
                 counts=dict(blacklisted=int(black.sum()), failed=int(failed.sum()), training=len(train),
                             kept=len(res["kept"])))

@@ -45,12 +45,16 @@ class StageIO(C.Structure):
                 ("x0_model", vp), ("x0_learned", vp), ("n_global", C.c_int64), ("offset", C.c_int64), ("perm", vp),
                 ("model", vp), ("learned", vp), ("pgf", vp), ("flags", vp), ("pca_k", vp), ("poly", vp),
                 ("n_per_round", vp), ("counts", C.c_int64 * 4), ("weights", vp), ("x0_pixels", vp),
-                ("field", C.c_double * 30), ("field_rank", C.c_int32)]
+                ("field", C.c_double * 30), ("field_rank", C.c_int32),
+                ("polyfit_rank", C.c_int32), ("polyfit_info", C.c_int32), ("stamps_f32", C.c_int32), ("perm_dev", vp),
+                ("model_status", vp), ("model_iters", vp), ("learned_status", vp), ("learned_iters", vp)]
 
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p)
 MODE_PCA, MODE_SMOOTH, MODE_CHISQ = 0, 1, 2
 FLAG_BLACKLISTED, FLAG_PCA_FAILED, FLAG_LEARNED_OOB, FLAG_TRAINING, FLAG_REJECTED = 1, 2, 4, 8, 16
+POLY_RANK_DEFICIENT, POLY_NONFINITE, POLY_ILL_CONDITIONED = 1, 2, 4
+UNIQUE_ID_BYTES = 128
 
 # name -> (restype, argtypes); every symbol include/shopt_b200.h declares
 SIGNATURES = {
@@ -60,6 +64,14 @@ SIGNATURES = {
     "shopt_last_error": (C.c_char_p, []),
     "shopt_last_timing": (C.c_int, [dp]),
     "shopt_release_buffers": (C.c_int, []),
+    "shopt_launch_count": (C.c_int64, []),
+    "shopt_bench_dfma": (C.c_int, [dp]),
+    "shopt_comm_unique_id": (C.c_int, [vp]),
+    "shopt_comm_init": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(vp)]),
+    "shopt_comm_destroy": (C.c_int, [vp]),
+    "shopt_comm_rank": (C.c_int, [vp]),
+    "shopt_comm_world": (C.c_int, [vp]),
+    "shopt_comm_allreduce": (C.c_int, [vp, C.c_int64, C.c_int, vp, vp]),
     "shopt_fit_analytic_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, dp, C.c_double, C.c_int,
                                            dp, dp, dp, ip, ip]),
     "shopt_fit_analytic_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, C.c_double, C.c_int,
@@ -87,8 +99,10 @@ SIGNATURES = {
     "shopt_polyfit": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, dp, dp, lp, C.c_int64, C.c_int, C.c_int, C.c_int,
                                 C.c_int, dp, dp, lp, lp, lp]),
     "shopt_polyfit_acc_len": (C.c_int64, [C.c_int, C.c_int, C.c_int]),
-    "shopt_polyfit_normal_dev": (C.c_int, [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
-    "shopt_polyfit_solve_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]),
+    "shopt_polyfit_centre_dev": (C.c_int, [vp, vp, C.c_int64, vp, vp]),
+    "shopt_polyfit_normal_dev": (C.c_int, [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_int, vp, vp, vp]),
+    "shopt_polyfit_solve_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int64, vp, vp, vp]),
+    "shopt_polyfit_factor_host": (C.c_int, [dp, C.c_int, dp, C.c_int64, dp, C.c_int, dp, ip]),
     "shopt_polyfit_mse_dev": (C.c_int, [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_int, vp, vp, vp]),
     "shopt_worst_10_percent": (C.c_int64, [dp, C.c_int64, C.c_int, lp]),
     "shopt_psf_at_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int, dp, dp, C.c_int64, dp]),

@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <numeric>
 #include <vector>
 
@@ -13,6 +14,7 @@
 namespace shopt {
 
 static thread_local char g_err[512] = "";
+std::atomic<long long> g_launches{0};
 void set_last_error_text(const char *text) { snprintf(g_err, sizeof g_err, "%s", text); }
 void set_last_error(const char *what, cudaError_t e) {
     snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(e));
@@ -49,12 +51,40 @@ int Ctx::need_cache(int i, size_t bytes, void **out) {
     *out = cache[i];
     return SHOPT_OK;
 }
+// grow-only block: freed (after the device has drained) only when a larger one is needed
+static int grow_block(void **p, size_t *have, size_t bytes, const char *what) {
+    if (bytes <= *have) return SHOPT_OK;
+    if (*p) { cudaDeviceSynchronize(); cudaFree(*p); *p = nullptr; *have = 0; }
+    bytes = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e != cudaSuccess) { *p = nullptr; set_last_error(what, e); (void)cudaGetLastError(); return SHOPT_E_NOMEM; }
+    *have = bytes;
+    return SHOPT_OK;
+}
+int Ctx::need_arena(size_t bytes) { return grow_block(&arena, &arena_bytes, bytes, "cudaMalloc(arena)"); }
+int Ctx::need_arena2(size_t bytes) { return grow_block(&arena2, &arena2_bytes, bytes, "cudaMalloc(arena2)"); }
+int Ctx::need_pinned(size_t bytes) {
+    if (bytes <= pinned_bytes) return SHOPT_OK;
+    if (pinned) { cudaDeviceSynchronize(); cudaFreeHost(pinned); pinned = nullptr; pinned_bytes = 0; }
+    bytes = (bytes + 65535) & ~(size_t)65535;
+    cudaError_t e = cudaHostAlloc(&pinned, bytes, cudaHostAllocDefault);
+    if (e != cudaSuccess) { pinned = nullptr; set_last_error("cudaHostAlloc", e); (void)cudaGetLastError(); return SHOPT_E_NOMEM; }
+    pinned_bytes = bytes;
+    return SHOPT_OK;
+}
 void Ctx::release_cache() {
     cudaDeviceSynchronize();
     for (int i = 0; i < NCACHE; i++) { if (cache[i]) cudaFree(cache[i]); cache[i] = nullptr; cache_bytes[i] = 0; }
     if (scratch) { cudaFree(scratch); scratch = nullptr; scratch_bytes = 0; }
+    if (arena) { cudaFree(arena); arena = nullptr; arena_bytes = 0; }
+    if (arena2) { cudaFree(arena2); arena2 = nullptr; arena2_bytes = 0; }
+    if (pinned) { cudaFreeHost(pinned); pinned = nullptr; pinned_bytes = 0; }
 }
-static thread_local Ctx g_ctx[16];
+// One context per device for the whole process (not per thread: a second calling thread would silently get its own
+// streams and its own tens of GB of cached blocks).  Calls on ONE device must not overlap; the reference calls the
+// stage from its main thread only.
+static Ctx g_ctx[16];
+static std::mutex g_ctx_mutex;
 
 int get_ctx(Ctx **out) {
     int n = 0;
@@ -67,6 +97,7 @@ int get_ctx(Ctx **out) {
     SHOPT_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 16) return SHOPT_E_UNSUPPORTED;
     Ctx &c = g_ctx[dev];
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
     if (c.dev != dev) {
         SHOPT_CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
         SHOPT_CUDA_TRY(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
@@ -89,13 +120,48 @@ int finish_timing(Ctx *c) {
     return SHOPT_OK;
 }
 
+// FP64 FMA peak: 16 independent chains per thread, 8 CTAs of 256 threads per SM
+__global__ void __launch_bounds__(256) dfma_kernel(double *out, int iters, double a, double b) {
+    double x[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) x[i] = (double)threadIdx.x + i;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) x[i] = fma(x[i], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) s += x[i];
+    if (s == 12345.678) out[0] = s;      // never true: keeps the chains alive
+}
+
 }  // namespace shopt
 
 using namespace shopt;
 
 extern "C" {
 
-int shopt_b200_version(void) { return 100; }
+// Measured FP64 FMA throughput of the current device (TFLOP/s), the compute roofline of fit_kernel / pca_kernel
+// (tcgen05 has no FP64 path; MEASURED_PEAKS.json holds no FP64 figure).
+int shopt_bench_dfma(double *tflops_out) {
+    if (!tflops_out) return SHOPT_E_BADARG;
+    Ctx *ctx; TRY(get_ctx(&ctx));
+    TRY(ctx->need_arena2(256));
+    const int iters = 20000, grid = sm_count() * 8;
+    cudaStream_t st = ctx->stream;
+    dfma_kernel<<<grid, 256, 0, st>>>((double *)ctx->arena2, 1000, 0.999999, 1e-9);     // warm-up
+    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[0], st));
+    dfma_kernel<<<grid, 256, 0, st>>>((double *)ctx->arena2, iters, 0.999999, 1e-9);
+    SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[1], st));
+    SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    SHOPT_CUDA_TRY(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+    *tflops_out = 2.0 * 16.0 * iters * 256.0 * grid / (ms * 1e-3) / 1e12;
+    return SHOPT_OK;
+}
+
+int shopt_b200_version(void) { return 200; }
+int64_t shopt_launch_count(void) { return (int64_t)g_launches.load(); }
 
 int shopt_device_count(void) {
     int n = 0;

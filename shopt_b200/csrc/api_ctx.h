@@ -1,5 +1,6 @@
 // api_ctx.h -- host-side context shared by the api_*.cu files: per-thread/per-device stream, timing events, work
-// counters and a grow-only device scratch block; self-freeing device buffers; error plumbing.
+// counters, grow-only device blocks (scratch, stage arena, stamp caches) and a grow-only pinned host block;
+// self-freeing device buffers for the one-shot host entry points; error plumbing; the communicator of a sharded run.
 #pragma once
 #include "common.cuh"
 #include "kernels.h"
@@ -23,7 +24,19 @@ struct Ctx {
     static constexpr int NCACHE = 4;
     void *cache[NCACHE] = {};
     size_t cache_bytes[NCACHE] = {};
+    // grow-only device arena of the stage (indices, keys, histograms, normal equations, ...) and pinned host staging:
+    // a stage call allocates and frees NOTHING once the first call of a given size has run (cudaFree synchronises the
+    // device and cudaMalloc takes driver locks -- both showed up as 100+ ms of idle GPU in round 1)
+    void *arena = nullptr;
+    size_t arena_bytes = 0;
+    void *arena2 = nullptr;                  // the host-buffer entry points' own block (small per-star arrays)
+    size_t arena2_bytes = 0;
+    void *pinned = nullptr;
+    size_t pinned_bytes = 0;
     int need_cache(int i, size_t bytes, void **out);
+    int need_arena(size_t bytes);
+    int need_arena2(size_t bytes);
+    int need_pinned(size_t bytes);
     void release_cache();
     unsigned long long *next_counter() { return counter + (slot++ & 7u); }
     // Work on a context is stream-ordered by the caller; growing frees the old block only after the device is idle.
@@ -33,7 +46,20 @@ int get_ctx(Ctx **out);
 int finish_timing(Ctx *c);   // synchronise the context's stream and read ev[0..3] into ms[0..2]
 void set_last_error_text(const char *text);
 
-// device allocation that frees itself
+// bump allocator over a block that is already large enough (sizes are computed twice: once to size the block)
+struct Bump {
+    char *base = nullptr;
+    size_t off = 0;
+    explicit Bump(void *b = nullptr) : base(static_cast<char *>(b)) {}
+    template <class T> T *take(size_t count) {
+        const size_t bytes = (count * sizeof(T) + 255) & ~(size_t)255;
+        T *p = base ? reinterpret_cast<T *>(base + off) : nullptr;
+        off += bytes;
+        return p;
+    }
+};
+
+// device allocation that frees itself (one-shot host entry points only; the stage uses the arena)
 struct DevBuf {
     void *p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
@@ -51,5 +77,19 @@ struct RawBuf {
     template <class T> T *as() const { return static_cast<T *>(p); }
 };
 #define TRY(expr) do { int _rc = (expr); if (_rc != SHOPT_OK) return _rc; } while (0)
+
+// The exchange of a sharded run: a sum-all-reduce on a device buffer, in stream order.  Either the caller's callback
+// (shopt_allreduce_fn) or the library's own NCCL communicator (comm.cu; shopt_comm_allreduce is such a callback).
+struct Exchange {
+    shopt_allreduce_fn fn = nullptr;
+    void *user = nullptr;
+    void *stream = nullptr;
+    bool on() const { return fn != nullptr; }
+    int sum(void *d_buf, long long count, int dtype) const {
+        if (!fn) return SHOPT_OK;
+        if (fn(d_buf, (int64_t)count, dtype, stream, user) != 0) { set_last_error_text("all-reduce failed"); return SHOPT_E_CUDA; }
+        return SHOPT_OK;
+    }
+};
 
 }  // namespace shopt

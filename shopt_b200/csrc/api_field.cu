@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "api_ctx.h"
+#include "polyfit_factor.h"
 
 namespace shopt {
 
@@ -20,113 +21,49 @@ static inline void field_terms(double u, double v, double *t) {
     t[7] = u; t[8] = v; t[9] = 1.0;
 }
 
-// min |A x - b_j| for nrhs right-hand sides; A (n x 10, column-major) and B (n x nrhs) are overwritten.
-// Returns the numerical rank found on the diagonal of R (10 = full).
-int field_lstsq(std::vector<double> &A, std::vector<double> &B, long long n, int nrhs, double *coef /* 10 x nrhs */) {
-    constexpr int K = 10;
-    int rank = 0;
-    double rmax = 0.0;
-    for (int k = 0; k < K && k < n; k++) {
-        double *ak = A.data() + (size_t)k * n;
-        double nrm = 0.0;
-        for (long long i = k; i < n; i++) nrm = std::hypot(nrm, ak[i]);
-        if (nrm == 0.0) continue;
-        const double alpha = ak[k] > 0 ? -nrm : nrm;
-        ak[k] -= alpha;                                   // v = x - alpha e1
-        double vnorm2 = 0.0;
-        for (long long i = k; i < n; i++) vnorm2 += ak[i] * ak[i];
-        if (vnorm2 > 0.0) {
-            auto reflect = [&](double *col) {
-                double dot = 0.0;
-                for (long long i = k; i < n; i++) dot += ak[i] * col[i];
-                const double f = 2.0 * dot / vnorm2;
-                for (long long i = k; i < n; i++) col[i] -= f * ak[i];
-            };
-            for (int j = k + 1; j < K; j++) reflect(A.data() + (size_t)j * n);
-            for (int j = 0; j < nrhs; j++) reflect(B.data() + (size_t)j * n);
-        }
-        ak[k] = alpha;                                    // R[k][k]
-        rmax = std::fmax(rmax, std::fabs(alpha));
-    }
-    for (int k = 0; k < K && k < n; k++)
-        if (std::fabs(A[(size_t)k * n + k]) > rmax * 1e-13) rank++;
-    for (int j = 0; j < nrhs; j++) {
-        double *x = coef + j * K;
-        for (int k = K - 1; k >= 0; k--) {
-            if (k >= n || !(std::fabs(A[(size_t)k * n + k]) > rmax * 1e-13)) { x[k] = 0.0; continue; }
-            double s = B[(size_t)j * n + k];
-            for (int m = k + 1; m < K; m++) s -= A[(size_t)m * n + k] * x[m];
-            x[k] = s / A[(size_t)k * n + k];
-        }
-    }
-    return rank;
-}
-
-
-// The same least squares from its normal equations G x = b_j (G = T'T 10 x 10 row-major, b 10 x nrhs stored [j][k]):
-// diagonal equilibration, Cholesky with diagonal pivoting (rank-revealing: pivots below 1e-13 of the largest end the
-// factorisation and the remaining coefficients are 0).  What the sharded stage uses: G and b add over shards.
-int field_solve_normal(const double *G, const double *b, int nrhs, double *coef) {
-    constexpr int K = 10;
-    double A[K][K], d[K];
-    int perm[K];
-    for (int i = 0; i < K; i++) { d[i] = G[i * K + i] > 0.0 ? 1.0 / std::sqrt(G[i * K + i]) : 0.0; perm[i] = i; }
-    for (int i = 0; i < K; i++)
-        for (int j = 0; j < K; j++) A[i][j] = G[i * K + j] * d[i] * d[j];
-    int rank = 0;
-    for (int k = 0; k < K; k++) {                          // A[perm][perm] = L L'
-        int pv = k;
-        for (int i = k + 1; i < K; i++) if (A[perm[i]][perm[i]] > A[perm[pv]][perm[pv]]) pv = i;
-        std::swap(perm[k], perm[pv]);
-        const int p = perm[k];
-        if (!(A[p][p] > 1e-13)) break;
-        const double l = std::sqrt(A[p][p]);
-        A[p][p] = l;
-        for (int i = k + 1; i < K; i++) A[perm[i]][p] /= l;
-        for (int i = k + 1; i < K; i++)
-            for (int j = k + 1; j <= i; j++) {
-                A[perm[i]][perm[j]] -= A[perm[i]][p] * A[perm[j]][p];
-                A[perm[j]][perm[i]] = A[perm[i]][perm[j]];
-            }
-        rank++;
-    }
-    for (int j = 0; j < nrhs; j++) {
-        double y[K], x[K];
-        for (int k = 0; k < rank; k++) {
-            double s = b[j * K + perm[k]] * d[perm[k]];
-            for (int m = 0; m < k; m++) s -= A[perm[k]][perm[m]] * y[m];
-            y[k] = s / A[perm[k]][perm[k]];
-        }
-        for (int k = rank - 1; k >= 0; k--) {
-            double s = y[k];
-            for (int m = k + 1; m < rank; m++) s -= A[perm[m]][perm[k]] * x[m];
-            x[k] = s / A[perm[k]][perm[k]];
-        }
-        for (int k = 0; k < K; k++) coef[j * K + k] = 0.0;
-        for (int k = 0; k < rank; k++) coef[j * K + perm[k]] = x[k] * d[perm[k]];
-    }
-    return rank;
-}
-
 }  // namespace shopt
 
 using namespace shopt;
 
 extern "C" {
 
+// The cubic is a degree-3 polynomial_optimizer problem in another term order: the normal equations are formed in the
+// centred and scaled basis (raw sky coordinates make the raw cubic design matrix numerically singular) and solved by
+// polyfit_factor.h -- the same path the stage runs on the device (api_stage.cu: field_normal_kernel).
 int shopt_field_interp(const double *u, const double *v, const double *const *values, int nvalues, int64_t n,
                        double *coef) {
     if (!u || !v || !values || !coef || nvalues < 1 || nvalues > 8 || n < 0) return SHOPT_E_BADARG;
     for (int j = 0; j < nvalues; j++) if (!values[j]) return SHOPT_E_BADARG;
-    std::vector<double> A((size_t)std::max<int64_t>(n, 1) * 10), B((size_t)std::max<int64_t>(n, 1) * nvalues);
-    for (int64_t i = 0; i < n; i++) {
-        double t[10];
-        field_terms(u[i], v[i], t);
-        for (int k = 0; k < 10; k++) A[(size_t)k * n + i] = t[k];
-        for (int j = 0; j < nvalues; j++) B[(size_t)j * n + i] = values[j][i];
+    constexpr int K = 10;
+    double ctr[4] = {0.0, 1.0, 0.0, 1.0};
+    if (n > 0) {                                          // the device's rule (select.cu: uv_centre_kernel)
+        double su = 0, sv = 0, suu = 0, svv = 0;
+        for (int64_t i = 0; i < n; i++) { su += u[i]; sv += v[i]; suu += u[i] * u[i]; svv += v[i] * v[i]; }
+        const double u0 = su / n, v0 = sv / n, vu = suu / n - u0 * u0, vv = svv / n - v0 * v0;
+        double sc_u = 1.0, sc_v = 1.0;
+        if (std::isfinite(vu) && vu > 1e-12 * u0 * u0 && vu > 0.0) sc_u = std::sqrt(3.0 * vu);
+        if (std::isfinite(vv) && vv > 1e-12 * v0 * v0 && vv > 0.0) sc_v = std::sqrt(3.0 * vv);
+        ctr[0] = std::isfinite(u0) ? u0 : 0.0; ctr[1] = 1.0 / sc_u; ctr[2] = std::isfinite(v0) ? v0 : 0.0; ctr[3] = 1.0 / sc_v;
     }
-    const int rank = field_lstsq(A, B, n, nvalues, coef);
-    return rank;                                          // 10 = full rank; fewer: the dependent coefficients are 0
+    std::vector<double> G(K * K, 0.0), B((size_t)K * nvalues, 0.0), work(6 * K * K);
+    for (int64_t i = 0; i < n; i++) {
+        const double a = (u[i] - ctr[0]) * ctr[1], b = (v[i] - ctr[2]) * ctr[3];
+        const double t[K] = {1.0, b, b * b, b * b * b, a, a * b, a * b * b, a * a, a * a * b, a * a * a};   // p outer, q inner
+        for (int p = 0; p < K; p++) {
+            for (int q = 0; q < K; q++) G[p * K + q] += t[p] * t[q];
+            for (int j = 0; j < nvalues; j++) B[(size_t)p * nvalues + j] += t[p] * values[j][i];
+        }
+    }
+    std::vector<PolyFactor> F(1);
+    polyfit_factor(3, G.data(), ctr, n, 0, work.data(), F.data());
+    const int map[K] = {9, 3, 8, 6, 7, 2, 5, 4, 1, 0};    // polynomial_optimizer's order -> interpolate.jl:8
+    for (int j = 0; j < nvalues; j++) {
+        double bj[KMAX], cj[KMAX];
+        for (int k = 0; k < K; k++) bj[k] = B[(size_t)k * nvalues + j];
+        polyfit_apply(F.data(), bj, cj);
+        for (int k = 0; k < K; k++) coef[j * K + k] = cj[map[k]];
+    }
+    return F[0].rank;                                      // 10 = full rank; fewer: the minimum-norm solution, like A \ z
 }
 
 int shopt_field_eval(const double *coef, const double *u, const double *v, int64_t n, double *out) {

@@ -96,6 +96,7 @@ int ingest_launch(const void *d_in, int f32, int r0, int c0, long long N, int un
     long long grid = (long long)sm_count() * 8;
     if (grid > N) grid = N;
     ingest_kernel<<<(unsigned)grid, 256, 0, st>>>(a);
+    count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     if (a.resize && lanczos_a > 0) return smooth_launch(d_tmp, new_dim, new_dim, N, lanczos_a, 0, d_out, st);
     return SHOPT_OK;

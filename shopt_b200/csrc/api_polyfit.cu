@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "api_ctx.h"
+#include "polyfit_factor.h"
 
 using namespace shopt;
 
@@ -16,20 +17,57 @@ int64_t shopt_polyfit_acc_len(int r, int c, int degree) {
     return K * K + K * (int64_t)r * c;
 }
 
+int shopt_polyfit_centre_dev(const double *d_u, const double *d_v, int64_t n, double *d_centre, void *stream) {
+    if (!d_u || !d_v || !d_centre || n < 0) return SHOPT_E_BADARG;
+    Ctx *ctx; TRY(get_ctx(&ctx));
+    TRY(ctx->need_arena2(256));
+    return uv_centre_launch(d_u, d_v, n, (double *)ctx->arena2, d_centre, Exchange(), (cudaStream_t)stream);
+}
+
 int shopt_polyfit_normal_dev(const double *d_pgf, int r, int c, const double *d_u, const double *d_v,
-                             const int64_t *d_idx, int64_t n, int degree, double *d_acc, void *stream) {
+                             const int64_t *d_idx, int64_t n, int degree, const double *d_centre, double *d_acc, void *stream) {
     if (!d_pgf || !d_u || !d_v || !d_acc || r < 1 || c < 1 || n < 0 || degree < 0 || degree > 8) return SHOPT_E_BADARG;
     Ctx *ctx; TRY(get_ctx(&ctx));
     const long long rc = (long long)r * c;
     TRY(ctx->need_scratch(polyfit_scratch_bytes(rc, n, degree)));
-    return polyfit_normal_launch(d_pgf, rc, d_u, d_v, (const long long *)d_idx, n, degree, d_acc,
-                                 (double *)ctx->scratch, ctx->scratch_bytes, (cudaStream_t)stream);
+    StarList sl; sl.idx = (const long long *)d_idx; sl.n = n;
+    return polyfit_normal_launch(d_pgf, rc, d_u, d_v, sl, degree, d_centre, d_acc, (double *)ctx->scratch, ctx->scratch_bytes,
+                                 (cudaStream_t)stream);
 }
 
-int shopt_polyfit_solve_dev(const double *d_acc, int r, int c, int degree, double *d_poly, int32_t *d_info, void *stream) {
-    if (!d_acc || !d_poly || !d_info || r < 1 || c < 1 || degree < 0 || degree > 8) return SHOPT_E_BADARG;
+namespace shopt {
+__global__ void factor_head_kernel(const PolyFactor *F, int *info) { info[0] = F->rank; info[1] = F->info; }
+}
+
+int shopt_polyfit_solve_dev(const double *d_acc, int r, int c, int degree, const double *d_centre, int64_t n_rows,
+                            double *d_poly, int32_t *d_info, void *stream) {
+    if (!d_acc || !d_poly || r < 1 || c < 1 || degree < 0 || degree > 8 || n_rows < 0) return SHOPT_E_BADARG;
     Ctx *ctx; TRY(get_ctx(&ctx));
-    return polyfit_solve_launch(d_acc, (long long)r * c, degree, d_poly, d_info, (cudaStream_t)stream);
+    TRY(ctx->need_arena2(sizeof(PolyFactor) + 512));
+    PolyFactor *F = reinterpret_cast<PolyFactor *>((char *)ctx->arena2 + 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    TRY(polyfit_factor_launch(d_acc, degree, d_centre, nullptr, n_rows, 0, F, st));
+    TRY(polyfit_solve_launch(d_acc, (long long)r * c, degree, F, nullptr, nullptr, d_poly, st));
+    if (d_info) { factor_head_kernel<<<1, 1, 0, st>>>(F, d_info); count_launches(1); }
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+
+int shopt_polyfit_factor_host(const double *G, int degree, const double *centre, int64_t n_rows, const double *b, int nrhs,
+                              double *coef, int32_t *info_out) {
+    if (!G || degree < 0 || degree > 8 || n_rows < 0 || nrhs < 0 || (nrhs > 0 && (!b || !coef))) return SHOPT_E_BADARG;
+    const int K = (degree + 1) * (degree + 2) / 2;
+    std::vector<double> work((size_t)6 * K * K);
+    std::vector<PolyFactor> F(1);
+    polyfit_factor(degree, G, centre, n_rows, 0, work.data(), F.data());
+    for (int j = 0; j < nrhs; j++) {
+        double bj[KMAX], cj[KMAX];
+        for (int k = 0; k < K; k++) bj[k] = b[(size_t)k * nrhs + j];
+        polyfit_apply(F.data(), bj, cj);
+        for (int k = 0; k < K; k++) coef[(size_t)k * nrhs + j] = cj[k];
+    }
+    if (info_out) *info_out = F[0].info;
+    return F[0].rank;
 }
 
 int shopt_polyfit_mse_dev(const double *d_pgf, int r, int c, const double *d_u, const double *d_v, const int64_t *d_idx,
@@ -39,8 +77,9 @@ int shopt_polyfit_mse_dev(const double *d_pgf, int r, int c, const double *d_u, 
     Ctx *ctx; TRY(get_ctx(&ctx));
     const long long rc = (long long)r * c;
     TRY(ctx->need_scratch(polyfit_scratch_bytes(rc, n, degree)));
-    return polyfit_mse_launch(d_pgf, rc, d_u, d_v, (const long long *)d_idx, n, degree, d_poly, d_mse,
-                              (double *)ctx->scratch, ctx->scratch_bytes, (cudaStream_t)stream);
+    StarList sl; sl.idx = (const long long *)d_idx; sl.n = n;
+    return polyfit_mse_launch(d_pgf, rc, d_u, d_v, sl, degree, d_poly, d_mse, (double *)ctx->scratch, ctx->scratch_bytes,
+                              (cudaStream_t)stream);
 }
 
 // shopt.jl:513-520: sort (index, error) by error, rev = true (stable: ties keep the lower index first; a NaN error is
@@ -95,8 +134,11 @@ int shopt_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, c
     const int K = (degree + 1) * (degree + 2) / 2;
     const size_t n0 = (size_t)n_train;
     // only the training stars travel to the device, compacted in training order
-    DevBuf dpgf, du, dv, didx, dacc, dpoly, dmse, dinfo, dmed;
+    DevBuf dpgf, du, dv, didx, dacc, dpoly, dmse, dinfo, dmed, dfac, drows;
     if (median_constraint) TRY(dmed.alloc((size_t)rc * 8));
+    TRY(dfac.alloc(2 * sizeof(PolyFactor) + 1024)); TRY(drows.alloc((size_t)4 * rc * 8 + 64));
+    PolyFactor *F = dfac.as<PolyFactor>(), *Fred = F + 1;
+    double *dctr = reinterpret_cast<double *>(Fred + 1), *dsums = dctr + 8;
     TRY(dpgf.alloc(std::max<size_t>(n0, 1) * rc * 8)); TRY(du.alloc(n0 * 8)); TRY(dv.alloc(n0 * 8)); TRY(didx.alloc(n0 * 8));
     TRY(dacc.alloc((size_t)shopt_polyfit_acc_len(r, c, degree) * 8)); TRY(dpoly.alloc((size_t)K * rc * 8));
     TRY(dmse.alloc(n0 * 8)); TRY(dinfo.alloc(16));
@@ -112,6 +154,7 @@ int shopt_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, c
     SHOPT_CUDA_TRY(cudaMemcpyAsync(du.p, tu.data(), n0 * 8, cudaMemcpyHostToDevice, st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(dv.p, tv.data(), n0 * 8, cudaMemcpyHostToDevice, st));
     SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[1], st));
+    TRY(uv_centre_launch(du.as<double>(), dv.as<double>(), (long long)n0, dsums, dctr, Exchange(), st));
     std::vector<int64_t> cur(n0);             // positions in the compacted device batch
     std::iota(cur.begin(), cur.end(), (int64_t)0);
     std::vector<double> err(n0);
@@ -122,23 +165,29 @@ int shopt_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, c
         const int64_t n = (int64_t)cur.size();
         if (n_per_round) n_per_round[loop - 1] = n;
         SHOPT_CUDA_TRY(cudaMemcpyAsync(didx.p, cur.data(), (size_t)n * 8, cudaMemcpyHostToDevice, st));
-        const long long *idx = didx.as<long long>();
+        StarList sl; sl.idx = didx.as<long long>(); sl.n = n;
         if (n < 5) {                           // interpolate.jl:142-145
-            TRY(small_median_launch(dpgf.as<double>(), rc, idx, (int)n, degree, dpoly.as<double>(), st));
+            for (int64_t t = 0; t < n; t++)
+                SHOPT_CUDA_TRY(cudaMemcpyAsync(drows.as<double>() + (size_t)t * rc, dpgf.as<double>() + (size_t)cur[(size_t)t] * rc,
+                                               (size_t)rc * 8, cudaMemcpyDeviceToDevice, st));
+            TRY(small_median_launch(drows.as<double>(), rc, (int)n, degree, dpoly.as<double>(), st));
         } else {
-            TRY(polyfit_normal_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), idx, n, degree,
+            TRY(polyfit_normal_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), sl, degree, dctr,
                                       dacc.as<double>(), (double *)ctx->scratch, ctx->scratch_bytes, st));
             if (!median_constraint)            // NaN values -> median before the solve (interpolate.jl:126-130)
-                TRY(polyfit_median_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), idx, n, degree, 2,
+                TRY(polyfit_median_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), sl, degree, dctr, 2,
                                           dacc.as<double>(), nullptr, st));
-            TRY(polyfit_solve_launch(dacc.as<double>(), rc, degree, dpoly.as<double>(), dinfo.as<int>(), st));
+            TRY(polyfit_factor_launch(dacc.as<double>(), degree, dctr, nullptr, n, 0, F, st));
             if (median_constraint) {           // interpolate.jl:118-124, 139-141
-                TRY(polyfit_median_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), idx, n, degree, 1,
+                TRY(polyfit_factor_launch(dacc.as<double>(), degree, dctr, nullptr, n, 1, Fred, st));
+                TRY(polyfit_median_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), sl, degree, dctr, 1,
                                           nullptr, dmed.as<double>(), st));
-                TRY(polyfit_set_coef0_launch(dmed.as<double>(), rc, dpoly.as<double>(), st));
+                TRY(polyfit_solve_launch(dacc.as<double>(), rc, degree, F, Fred, dmed.as<double>(), dpoly.as<double>(), st));
+            } else {
+                TRY(polyfit_solve_launch(dacc.as<double>(), rc, degree, F, nullptr, nullptr, dpoly.as<double>(), st));
             }
         }
-        TRY(polyfit_mse_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), idx, n, degree, dpoly.as<double>(),
+        TRY(polyfit_mse_launch(dpgf.as<double>(), rc, du.as<double>(), dv.as<double>(), sl, degree, dpoly.as<double>(),
                                dmse.as<double>(), (double *)ctx->scratch, ctx->scratch_bytes, st));
         SHOPT_CUDA_TRY(cudaMemcpyAsync(err.data(), dmse.p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
         SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
@@ -159,7 +208,7 @@ int shopt_polyfit(const double *pgf, int r, int c, int64_t N, const double *u, c
     TRY(finish_timing(ctx));
     if (kept_idx) for (size_t t = 0; t < cur.size(); t++) kept_idx[t] = train_idx[cur[t]];
     if (n_kept) *n_kept = (int64_t)cur.size();
-    return SHOPT_OK;   // a singular V'V leaves NaN coefficients, like a failed factorisation would
+    return SHOPT_OK;
 }
 
 int shopt_psf_at_batch_dev(const double *d_poly, int r, int c, int degree, const double *d_u, const double *d_v, int64_t M,

@@ -1,6 +1,7 @@
 // common.cuh -- shared device helpers for libshopt_b200 (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <stdint.h>
 #include <math.h>
 #include <float.h>
@@ -21,6 +22,11 @@ void set_last_error(const char *what, cudaError_t e);
     } while (0)
 
 int sm_count();   // SMs of the current device (cached per device)
+
+// kernels launched by this process (every *_launch adds what it enqueues): bench.py's `gpu_launches` is a count, not a
+// constant
+extern std::atomic<long long> g_launches;
+inline void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 // ---- deterministic CTA-wide sum of NV doubles ----------------------------------------------
 // Every thread returns with the same bits in v[]: xor-butterfly inside the warp (commutative, so all

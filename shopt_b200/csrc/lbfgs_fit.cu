@@ -881,6 +881,7 @@ static int launch_fit(FitArgs a, cudaStream_t stream) {
     if (grid > a.N) grid = a.N;
     SHOPT_CUDA_TRY(cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream));
     kern<<<(unsigned)grid, THREADS + 32, best_smem, stream>>>(a);
+    count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }

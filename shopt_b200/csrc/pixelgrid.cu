@@ -974,6 +974,7 @@ int elem_pgf_launch(const double *d_in, const double *d_w, const double *d_x0, d
     long long grid = (long long)sm_count() * 8;
     if (grid > N) grid = N;
     elem_pgf_kernel<<<(unsigned)grid, 256, 0, st>>>(a);
+    count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
@@ -1036,6 +1037,7 @@ static int pca_launch_t(PcaArgs a, double *scratch, size_t scratch_bytes, cudaSt
         SHOPT_CUDA_TRY(cudaMemcpyToSymbolAsync(g_pca_phase, zero, sizeof(zero), 0, cudaMemcpyHostToDevice, st));
     }
     kern<<<(unsigned)grid, NW * 32, smem, st>>>(a);
+    count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     if (a.debug & 16) {
         static const char *names[12] = {"stars", "load+centre", "fast path", "gram+copy", "tridiagonalise", "eigenvalues",
@@ -1107,6 +1109,7 @@ int smooth_launch(const double *d_in, int r, int c, long long N, int lanczos_a, 
     long long grid = (long long)sm_count() * per_sm;
     if (grid > N) grid = N;
     smooth_kernel<<<(unsigned)grid, 512, smem, st>>>(a);
+    count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }

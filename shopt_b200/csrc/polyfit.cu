@@ -21,8 +21,8 @@
 //                  per-star partial sums per pixel tile, reduced in tile order by mse_reduce_kernel.
 #include <cstdlib>
 
-#include "common.cuh"
-#include "kernels.h"
+#include "api_ctx.h"
+#include "polyfit_factor.h"
 
 namespace shopt {
 
@@ -45,6 +45,11 @@ __device__ __forceinline__ void basis_eval(double u, double v, double *b) {
     }
 }
 
+// centred and scaled coordinates (polyfit_factor.h): ctr = {u0, 1/su, v0, 1/sv} on the device, or null = raw
+__device__ __forceinline__ void centre_uv(const double *__restrict__ ctr, double &u, double &v) {
+    if (ctr) { u = (u - ctr[0]) * ctr[1]; v = (v - ctr[2]) * ctr[3]; }
+}
+
 constexpr int POLY_THREADS = 128;
 constexpr int POLY_CFG_DEFAULT = 2;   // 4 pixels per thread (K <= 10), star loop unrolled by 4: normal_kernel 2.98 -> 2.71 ms
 constexpr int SCHUNK = 64;   // stars staged per shared-memory refill
@@ -62,11 +67,14 @@ template <int DEG> struct PolyCfg {
 template <int DEG, int PX, int UNR>
 __global__ void __launch_bounds__(POLY_THREADS) normal_kernel(const double *__restrict__ pgf, long long rc,
                                                               const double *__restrict__ u, const double *__restrict__ v,
-                                                              const long long *__restrict__ idx, long long n,
-                                                              long long per_chunk, double *__restrict__ part) {
+                                                              const long long *__restrict__ idx, long long n_bound,
+                                                              const long long *__restrict__ n_ptr,
+                                                              const double *__restrict__ ctr, double *__restrict__ part) {
     constexpr int K = PolyCfg<DEG>::K;
     __shared__ double sV[SCHUNK][K];
     __shared__ long long sOff[SCHUNK];
+    const long long n = n_ptr ? *n_ptr : n_bound;
+    const long long per_chunk = (n + gridDim.y - 1) / gridDim.y;
     const long long t0 = (long long)blockIdx.y * per_chunk;
     const long long t1 = (t0 + per_chunk < n) ? t0 + per_chunk : n;
     const long long px0 = (long long)blockIdx.x * (POLY_THREADS * PX) + threadIdx.x;
@@ -80,8 +88,9 @@ __global__ void __launch_bounds__(POLY_THREADS) normal_kernel(const double *__re
         __syncthreads();
         if (threadIdx.x < m) {
             const long long star = idx ? idx[base + threadIdx.x] : base + threadIdx.x;
-            double b[K];
-            basis_eval<DEG>(u[star], v[star], b);
+            double b[K], cu = u[star], cv = v[star];
+            centre_uv(ctr, cu, cv);
+            basis_eval<DEG>(cu, cv, b);
 #pragma unroll
             for (int k = 0; k < K; k++) sV[threadIdx.x][k] = b[k];
             sOff[threadIdx.x] = star * rc;
@@ -117,10 +126,13 @@ __global__ void __launch_bounds__(POLY_THREADS) normal_kernel(const double *__re
 // G = V'V partials: one block per chunk, the K*K entries strided over the threads
 template <int DEG>
 __global__ void __launch_bounds__(POLY_THREADS) gram_kernel(const double *__restrict__ u, const double *__restrict__ v,
-                                                            const long long *__restrict__ idx, long long n,
-                                                            long long per_chunk, long long rc, double *__restrict__ part) {
+                                                            const long long *__restrict__ idx, long long n_bound,
+                                                            const long long *__restrict__ n_ptr, const double *__restrict__ ctr,
+                                                            long long rc, double *__restrict__ part) {
     constexpr int K = PolyCfg<DEG>::K;
     __shared__ double sV[SCHUNK][K];
+    const long long n = n_ptr ? *n_ptr : n_bound;
+    const long long per_chunk = (n + gridDim.x - 1) / gridDim.x;
     const long long t0 = (long long)blockIdx.x * per_chunk;
     const long long t1 = (t0 + per_chunk < n) ? t0 + per_chunk : n;
     constexpr int NE = (K * K + POLY_THREADS - 1) / POLY_THREADS;
@@ -132,8 +144,9 @@ __global__ void __launch_bounds__(POLY_THREADS) gram_kernel(const double *__rest
         __syncthreads();
         if (threadIdx.x < m) {
             const long long star = idx ? idx[base + threadIdx.x] : base + threadIdx.x;
-            double b[K];
-            basis_eval<DEG>(u[star], v[star], b);
+            double b[K], cu = u[star], cv = v[star];
+            centre_uv(ctr, cu, cv);
+            basis_eval<DEG>(cu, cv, b);
 #pragma unroll
             for (int k = 0; k < K; k++) sV[threadIdx.x][k] = b[k];
         }
@@ -165,63 +178,85 @@ __global__ void reduce_kernel(const double *__restrict__ part, long long len, in
 }
 
 // ---------------------------------------------------------------------------------------------
-// solve: G = L L' after symmetric diagonal equilibration; poly[px + k*rc] = (G^-1 B)[k][px]
+// solve: factor_kernel turns G = Vc'Vc (K x K) into the solve operator of polyfit_factor.h (one thread: K <= 45, a few
+// thousand dependent flops in shared memory); solve_kernel applies it to every pixel's right-hand side:
+// forward substitution with the pivoted Cholesky factor, then one K x rc matrix-vector product.
+// median_constraint (interpolate.jl:118-124, 139-141): the first design column is the constant m = median(z) instead of
+// 1, so for m != 0 the solution is the unconstrained one with coefficient 1 divided by m -- and coefficient 1 is then
+// overwritten by m; for m == 0 the column vanishes, LAPACK's rank-revealing solve drops it, and the other coefficients
+// are those of the fit WITHOUT a constant term (the `red` factorisation); m = NaN makes every coefficient NaN.
 // ---------------------------------------------------------------------------------------------
+__global__ void factor_kernel(int degree, const double *__restrict__ G, const double *__restrict__ ctr,
+                              const long long *__restrict__ nrows_ptr, long long nrows, int drop_const,
+                              PolyFactor *__restrict__ F) {
+    extern __shared__ __align__(16) double fac_work[];
+    if (threadIdx.x != 0) return;
+    polyfit_factor(degree, G, ctr, nrows_ptr ? *nrows_ptr : nrows, drop_const, fac_work, F);
+}
+
 template <int DEG>
-__global__ void __launch_bounds__(128) solve_kernel(const double *__restrict__ acc, long long rc, double *__restrict__ poly,
-                                                    int *__restrict__ info) {
+__global__ void __launch_bounds__(128) solve_kernel(const double *__restrict__ acc, long long rc,
+                                                    const PolyFactor *__restrict__ F, const PolyFactor *__restrict__ Fred,
+                                                    const double *__restrict__ med, double *__restrict__ poly) {
     constexpr int K = PolyCfg<DEG>::K;
-    __shared__ double L[K][K + 1];
-    __shared__ double dsc[K];
-    __shared__ int bad;
-    if (threadIdx.x == 0) {
-        bad = 0;
-        for (int i = 0; i < K; i++) {
-            const double d = acc[i * K + i];
-            if (!(d > 0.0) || !isfinite(d)) bad = 1;
-            dsc[i] = bad ? 1.0 : 1.0 / sqrt(d);
-        }
-        for (int i = 0; i < K; i++)
-            for (int j = 0; j < K; j++) L[i][j] = acc[i * K + j] * dsc[i] * dsc[j];
-        for (int j = 0; j < K && !bad; j++) {
-            double d = L[j][j];
-            for (int k = 0; k < j; k++) d -= L[j][k] * L[j][k];
-            if (!(d > 0.0) || !isfinite(d)) { bad = 1; break; }
-            const double lj = sqrt(d);
-            L[j][j] = lj;
-            for (int i = j + 1; i < K; i++) {
-                double s = L[i][j];
-                for (int k = 0; k < j; k++) s -= L[i][k] * L[j][k];
-                L[i][j] = s / lj;
-            }
-        }
-        if (bad && blockIdx.x == 0) *info = 1;
+    extern __shared__ __align__(16) double solve_smem[];           // (Fred ? 4 : 2) matrices of K x (K+1)
+    typedef double (*Mat)[K + 1];
+    Mat L = reinterpret_cast<Mat>(solve_smem), W = reinterpret_cast<Mat>(solve_smem + K * (K + 1));
+    Mat Lr = reinterpret_cast<Mat>(solve_smem + 2 * K * (K + 1)), Wr = reinterpret_cast<Mat>(solve_smem + 3 * K * (K + 1));
+    __shared__ double dsc[2][K];
+    __shared__ int piv[2][K];
+    for (int e = threadIdx.x; e < K * K; e += blockDim.x) {
+        L[e / K][e % K] = F->L[e]; W[e / K][e % K] = F->W2[e];
+        if (Fred) { Lr[e / K][e % K] = Fred->L[e]; Wr[e / K][e % K] = Fred->W2[e]; }
+    }
+    for (int e = threadIdx.x; e < K; e += blockDim.x) {
+        dsc[0][e] = F->dsc[e]; piv[0][e] = F->piv[e];
+        if (Fred) { dsc[1][e] = Fred->dsc[e]; piv[1][e] = Fred->piv[e]; }
     }
     __syncthreads();
     const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (px >= rc) return;
-    double y[K];
-    if (bad) {
+    double b[K], y[K];
 #pragma unroll
-        for (int k = 0; k < K; k++) poly[px + (size_t)k * rc] = nan("");
-        return;
+    for (int k = 0; k < K; k++) b[k] = acc[(size_t)K * K + (size_t)k * rc + px];
+    const double m = med ? med[px] : 1.0;
+    const bool red = med && (m == 0.0);
+    const int rcr = red ? Fred->rc_rank : F->rc_rank;
+    if (!red) {
+#pragma unroll
+        for (int i = 0; i < K; i++) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < K; k++) if (k == piv[0][i]) s = b[k] * dsc[0][k];
+#pragma unroll
+            for (int k = 0; k < i; k++) s -= L[i][k] * y[k];
+            y[i] = (i < rcr) ? s / L[i][i] : 0.0;
+        }
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+            double s = 0.0;
+#pragma unroll
+            for (int i = 0; i < K; i++) s = fma(W[j][i], y[i], s);
+            poly[px + (size_t)j * rc] = (med && j == 0) ? m : (med && isnan(m)) ? m : s;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < K; i++) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < K; k++) if (k == piv[1][i]) s = b[k] * dsc[1][k];
+#pragma unroll
+            for (int k = 0; k < i; k++) s -= Lr[i][k] * y[k];
+            y[i] = (i < rcr) ? s / Lr[i][i] : 0.0;
+        }
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+            double s = 0.0;
+#pragma unroll
+            for (int i = 0; i < K; i++) s = fma(Wr[j][i], y[i], s);
+            poly[px + (size_t)j * rc] = (j == 0) ? m : s;
+        }
     }
-#pragma unroll
-    for (int i = 0; i < K; i++) {
-        double s = acc[(size_t)K * K + (size_t)i * rc + px] * dsc[i];
-#pragma unroll
-        for (int k = 0; k < i; k++) s -= L[i][k] * y[k];
-        y[i] = s / L[i][i];
-    }
-#pragma unroll
-    for (int i = K - 1; i >= 0; i--) {
-        double s = y[i];
-#pragma unroll
-        for (int k = i + 1; k < K; k++) s -= L[k][i] * y[k];
-        y[i] = s / L[i][i];
-    }
-#pragma unroll
-    for (int k = 0; k < K; k++) poly[px + (size_t)k * rc] = y[k] * dsc[k];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -230,13 +265,15 @@ __global__ void __launch_bounds__(128) solve_kernel(const double *__restrict__ a
 template <int DEG, int PX, int UNR>
 __global__ void __launch_bounds__(POLY_THREADS) mse_kernel(const double *__restrict__ pgf, long long rc,
                                                            const double *__restrict__ u, const double *__restrict__ v,
-                                                           const long long *__restrict__ idx, long long n,
-                                                           long long per_chunk, const double *__restrict__ poly,
+                                                           const long long *__restrict__ idx, long long n_bound,
+                                                           const long long *__restrict__ n_ptr, const double *__restrict__ poly,
                                                            double *__restrict__ part) {
     constexpr int K = PolyCfg<DEG>::K, NW = POLY_THREADS / 32;
     __shared__ double sV[SCHUNK][K];
     __shared__ long long sOff[SCHUNK];
     __shared__ double sE[SCHUNK][NW];
+    const long long n = n_ptr ? *n_ptr : n_bound;
+    const long long per_chunk = ((n + gridDim.y - 1) / gridDim.y + SCHUNK - 1) / SCHUNK * SCHUNK;
     const long long t0 = (long long)blockIdx.y * per_chunk;
     const long long t1 = (t0 + per_chunk < n) ? t0 + per_chunk : n;
     const long long px0 = (long long)blockIdx.x * (POLY_THREADS * PX) + threadIdx.x;
@@ -311,8 +348,9 @@ __global__ void __launch_bounds__(POLY_THREADS) mse_kernel(const double *__restr
         }
     }
 }
-__global__ void mse_reduce_kernel(const double *__restrict__ part, long long n, int ntile, double inv_rc,
-                                  double *__restrict__ mse) {
+__global__ void mse_reduce_kernel(const double *__restrict__ part, long long n_bound, const long long *__restrict__ n_ptr,
+                                  int ntile, double inv_rc, double *__restrict__ mse) {
+    const long long n = n_ptr ? *n_ptr : n_bound;
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     double s = 0.0;
@@ -351,15 +389,14 @@ __global__ void __launch_bounds__(256) psf_at_kernel(const double *__restrict__ 
 // fewer than 5 training stars (interpolate.jl:142-145): coefficients = [median(z), 0, ...]; and the per-pixel
 // median of the non-NaN values of a SMALL training set (n <= 64) used for that override.
 // ---------------------------------------------------------------------------------------------
-__global__ void small_median_kernel(const double *__restrict__ pgf, long long rc, const long long *__restrict__ idx,
-                                    int n, int K, double *__restrict__ poly) {
+// rows: (n, rc) the training stars' pixel-grid fits gathered into one small buffer (see small_gather_kernel)
+__global__ void small_median_kernel(const double *__restrict__ rows, long long rc, int n, int K, double *__restrict__ poly) {
     const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (px >= rc) return;
     double z[4];
     int m = 0;
     for (int t = 0; t < n && t < 4; t++) {
-        const long long star = idx ? idx[t] : t;
-        const double val = pgf[star * rc + px];
+        const double val = rows[(size_t)t * rc + px];
         if (!isnan(val)) {   // insertion sort
             int i = m++;
             while (i > 0 && z[i - 1] > val) { z[i] = z[i - 1]; i--; }
@@ -370,6 +407,38 @@ __global__ void small_median_kernel(const double *__restrict__ pgf, long long rc
     if (m > 0) med = (m & 1) ? z[m / 2] : (z[m / 2 - 1] / 2 + z[m / 2] / 2);   // Statistics.middle
     poly[px] = med;
     for (int k = 1; k < K; k++) poly[px + (size_t)k * rc] = 0.0;
+}
+// The (at most four) training stars of the whole catalogue may live on different shards: every shard marks the
+// permutation positions of its own ones in a bit set (all-reduced by the caller), a star's slot is its rank among the
+// marked positions, and the shards' rows (zero elsewhere) add up to the gathered (n, rc) block.
+__global__ void alive_bits_kernel(const unsigned *__restrict__ pos, const long long *__restrict__ n_dev, unsigned *__restrict__ bits) {
+    const long long n = *n_dev;
+    for (long long t = threadIdx.x; t < n; t += blockDim.x) atomicOr(&bits[pos[t] >> 5], 1u << (pos[t] & 31));
+}
+__global__ void __launch_bounds__(256) small_gather_kernel(const double *__restrict__ pgf, long long rc,
+                                                           const long long *__restrict__ idx, const unsigned *__restrict__ pos,
+                                                           const long long *__restrict__ n_dev, const unsigned *__restrict__ bits,
+                                                           double *__restrict__ rows) {
+    __shared__ int s_part[8];
+    const long long n = *n_dev;
+    const int t = blockIdx.y;
+    if (t >= n) return;
+    const unsigned p = pos[t];
+    int cnt = 0;
+    for (unsigned w = threadIdx.x; w <= (p >> 5); w += blockDim.x) {
+        unsigned b = bits[w];
+        if (w == (p >> 5)) b &= (1u << (p & 31)) - 1u;
+        cnt += __popc(b);
+    }
+#pragma unroll
+    for (int m = 16; m >= 1; m >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, m);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    int slot = 0;
+    for (int w = 0; w < 8; w++) slot += s_part[w];
+    if (slot >= 4) return;
+    const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (px < rc) rows[(size_t)slot * rc + px] = pgf[idx[t] * rc + px];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -397,9 +466,12 @@ __device__ __forceinline__ double key_value(unsigned long long k) {
 template <int DEG>
 __global__ void __launch_bounds__(MED_THREADS) median_fix_kernel(const double *__restrict__ pgf, long long rc,
                                                                  const double *__restrict__ u, const double *__restrict__ v,
-                                                                 const long long *__restrict__ idx, long long n, int mode,
+                                                                 const long long *__restrict__ idx, long long n_bound,
+                                                                 const long long *__restrict__ n_ptr,
+                                                                 const double *__restrict__ ctr, int mode,
                                                                  double *__restrict__ acc, double *__restrict__ med_out) {
     constexpr int K = PolyCfg<DEG>::K;
+    const long long n = n_ptr ? *n_ptr : n_bound;
     extern __shared__ __align__(16) unsigned char med_smem[];
     unsigned int *hist = reinterpret_cast<unsigned int *>(med_smem);            // [256][MED_PX]
     __shared__ unsigned long long s_prefix[MED_PX], s_next[MED_PX];
@@ -498,8 +570,9 @@ __global__ void __launch_bounds__(MED_THREADS) median_fix_kernel(const double *_
             const long long star = idx ? idx[t] : t;
             double z = __ldg(pgf + star * rc + px);
             if (isnan(z)) z = m;
-            double b[K];
-            basis_eval<DEG>(u[star], v[star], b);
+            double b[K], cu = u[star], cv = v[star];
+            centre_uv(ctr, cu, cv);
+            basis_eval<DEG>(cu, cv, b);
 #pragma unroll
             for (int k = 0; k < K; k++) a[k] = fma(b[k], z, a[k]);
         }
@@ -517,11 +590,6 @@ __global__ void __launch_bounds__(MED_THREADS) median_fix_kernel(const double *_
         }
     }
 }
-__global__ void set_coef0_kernel(const double *__restrict__ med, long long rc, double *__restrict__ poly) {
-    const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (px < rc) poly[px] = med[px];
-}
-
 // ---- launch -----------------------------------------------------------------------------------
 static int pick_chunks(long long n, int tiles) {
     long long want = ((long long)sm_count() * 16 + tiles - 1) / tiles;
@@ -542,67 +610,70 @@ static int poly_px(int K, int cfg) {
     const int base = (K <= 10) ? 4 : (K <= 21 ? 2 : 1);
     return (cfg & 1) ? (base > 1 ? base / 2 : 1) : base;
 }
+// The list length may live on the device (sl.n_dev): grids are sized from the bound sl.n, the kernels split the ACTUAL
+// count over the chunks they were launched with (empty chunks write zeros).
 template <int DEG, int PX, int UNR>
-static int normal_launch_v(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
-                           long long n, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
+static int normal_launch_v(const double *pgf, long long rc, const double *u, const double *v, StarList sl, const double *ctr,
+                           double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
     constexpr int K = PolyCfg<DEG>::K;
     const long long len = (long long)K * K + (long long)K * rc;
-    if (n == 0) { SHOPT_CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)len * 8, st)); return SHOPT_OK; }
+    if (sl.n == 0) { SHOPT_CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)len * 8, st)); return SHOPT_OK; }
     const int tiles = (int)((rc + POLY_THREADS * PX - 1) / (POLY_THREADS * PX));
-    int nchunk = pick_chunks(n, tiles);
+    int nchunk = pick_chunks(sl.n, tiles);
     while (nchunk > 1 && (size_t)nchunk * len * 8 > scratch_bytes) nchunk--;
     if ((size_t)nchunk * len * 8 > scratch_bytes) return SHOPT_E_NOMEM;
-    const long long per_chunk = (n + nchunk - 1) / nchunk;
-    nchunk = (int)((n + per_chunk - 1) / per_chunk);
-    normal_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, idx, n, per_chunk, scratch);
-    gram_kernel<DEG><<<nchunk, POLY_THREADS, 0, st>>>(u, v, idx, n, per_chunk, rc, scratch);
+    normal_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, ctr, scratch);
+    gram_kernel<DEG><<<nchunk, POLY_THREADS, 0, st>>>(u, v, sl.idx, sl.n, sl.n_dev, ctr, rc, scratch);
     reduce_kernel<<<(unsigned)((len + 255) / 256), 256, 0, st>>>(scratch, len, nchunk, acc);
+    count_launches(3);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
 template <int DEG>
-static int normal_launch_t(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
-                           long long n, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
+static int normal_launch_t(const double *pgf, long long rc, const double *u, const double *v, StarList sl, const double *ctr,
+                           double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
     constexpr int P0 = PolyCfg<DEG>::PX, P1 = (P0 > 1 ? P0 / 2 : 1);
     switch (poly_cfg()) {
-        case 0: return normal_launch_v<DEG, P0, 2>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st);
-        case 1: return normal_launch_v<DEG, P1, 2>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st);
-        case 2: return normal_launch_v<DEG, P0, 4>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st);
-        default: return normal_launch_v<DEG, P1, 4>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st);
+        case 0: return normal_launch_v<DEG, P0, 2>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
+        case 1: return normal_launch_v<DEG, P1, 2>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
+        case 2: return normal_launch_v<DEG, P0, 4>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
+        default: return normal_launch_v<DEG, P1, 4>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
     }
 }
 template <int DEG>
-static int solve_launch_t(const double *acc, long long rc, double *poly, int *info, cudaStream_t st) {
-    SHOPT_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int), st));
-    solve_kernel<DEG><<<(unsigned)((rc + 127) / 128), 128, 0, st>>>(acc, rc, poly, info);
+static int solve_launch_t(const double *acc, long long rc, const PolyFactor *F, const PolyFactor *Fred, const double *med,
+                          double *poly, cudaStream_t st) {
+    constexpr int K = PolyCfg<DEG>::K;
+    const size_t smem = (size_t)(Fred ? 4 : 2) * K * (K + 1) * sizeof(double);
+    auto kern = solve_kernel<DEG>;
+    if (smem > 48 * 1024) SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)((rc + 127) / 128), 128, smem, st>>>(acc, rc, F, Fred, med, poly);
+    count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
 template <int DEG, int PX, int UNR>
-static int mse_launch_v(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
-                        long long n, const double *poly, double *mse, double *scratch, size_t scratch_bytes,
-                        cudaStream_t st) {
-    if (n == 0) return SHOPT_OK;
+static int mse_launch_v(const double *pgf, long long rc, const double *u, const double *v, StarList sl, const double *poly,
+                        double *mse, double *scratch, size_t scratch_bytes, cudaStream_t st) {
+    if (sl.n == 0) return SHOPT_OK;
     const int tiles = (int)((rc + POLY_THREADS * PX - 1) / (POLY_THREADS * PX));
-    if ((size_t)tiles * n * 8 > scratch_bytes) return SHOPT_E_NOMEM;
-    int nchunk = pick_chunks(n, tiles);
-    const long long per_chunk = ((n + nchunk - 1) / nchunk + SCHUNK - 1) / SCHUNK * SCHUNK;
-    nchunk = (int)((n + per_chunk - 1) / per_chunk);
-    mse_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, idx, n, per_chunk, poly, scratch);
-    mse_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(scratch, n, tiles, 1.0 / (double)rc, mse);
+    if ((size_t)tiles * sl.n * 8 > scratch_bytes) return SHOPT_E_NOMEM;
+    const int nchunk = pick_chunks(sl.n, tiles);
+    mse_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, poly, scratch);
+    mse_reduce_kernel<<<(unsigned)((sl.n + 255) / 256), 256, 0, st>>>(scratch, sl.n, sl.n_dev, tiles, 1.0 / (double)rc, mse);
+    count_launches(2);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
 template <int DEG>
-static int mse_launch_t(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
-                        long long n, const double *poly, double *mse, double *scratch, size_t scratch_bytes,
-                        cudaStream_t st) {
+static int mse_launch_t(const double *pgf, long long rc, const double *u, const double *v, StarList sl, const double *poly,
+                        double *mse, double *scratch, size_t scratch_bytes, cudaStream_t st) {
     constexpr int P0 = PolyCfg<DEG>::PX, P1 = (P0 > 1 ? P0 / 2 : 1);
     switch (poly_cfg()) {
-        case 0: return mse_launch_v<DEG, P0, 2>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st);
-        case 1: return mse_launch_v<DEG, P1, 2>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st);
-        case 2: return mse_launch_v<DEG, P0, 4>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st);
-        default: return mse_launch_v<DEG, P1, 4>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st);
+        case 0: return mse_launch_v<DEG, P0, 2>(pgf, rc, u, v, sl, poly, mse, scratch, scratch_bytes, st);
+        case 1: return mse_launch_v<DEG, P1, 2>(pgf, rc, u, v, sl, poly, mse, scratch, scratch_bytes, st);
+        case 2: return mse_launch_v<DEG, P0, 4>(pgf, rc, u, v, sl, poly, mse, scratch, scratch_bytes, st);
+        default: return mse_launch_v<DEG, P1, 4>(pgf, rc, u, v, sl, poly, mse, scratch, scratch_bytes, st);
     }
 }
 template <int DEG>
@@ -610,6 +681,7 @@ static int psf_launch_t(const double *poly, long long rc, const double *u, const
                         cudaStream_t st) {
     if (M == 0) return SHOPT_OK;
     psf_at_kernel<DEG><<<(unsigned)M, 256, 0, st>>>(poly, rc, u, v, out);
+    count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
@@ -637,21 +709,33 @@ size_t polyfit_scratch_bytes(long long rc, long long n, int degree) {
     const size_t b = (size_t)tiles * (n > 0 ? n : 1) * 8;
     return a > b ? a : b;
 }
-int polyfit_normal_launch(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
-                          long long n, int degree, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
-#define CALL(D) normal_launch_t<D>(pgf, rc, u, v, idx, n, acc, scratch, scratch_bytes, st)
+int polyfit_normal_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
+                          const double *ctr, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
+#define CALL(D) normal_launch_t<D>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st)
     DEG_SWITCH(degree, CALL)
 #undef CALL
 }
-int polyfit_solve_launch(const double *acc, long long rc, int degree, double *poly, int *info, cudaStream_t st) {
-#define CALL(D) solve_launch_t<D>(acc, rc, poly, info, st)
+int polyfit_factor_launch(const double *G, int degree, const double *ctr, const long long *nrows_dev, long long nrows,
+                          int drop_const, PolyFactor *F, cudaStream_t st) {
+    if (degree < 0 || degree > 8) return SHOPT_E_BADARG;
+    const int K = num_terms(degree);
+    const size_t smem = (size_t)6 * K * K * sizeof(double);
+    if (smem > 48 * 1024)
+        SHOPT_CUDA_TRY(cudaFuncSetAttribute(factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    factor_kernel<<<1, 32, smem, st>>>(degree, G, ctr, nrows_dev, nrows, drop_const, F);
+    count_launches(1);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+int polyfit_solve_launch(const double *acc, long long rc, int degree, const PolyFactor *F, const PolyFactor *Fred,
+                         const double *med, double *poly, cudaStream_t st) {
+#define CALL(D) solve_launch_t<D>(acc, rc, F, Fred, med, poly, st)
     DEG_SWITCH(degree, CALL)
 #undef CALL
 }
-int polyfit_mse_launch(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
-                       long long n, int degree, const double *poly, double *mse, double *scratch, size_t scratch_bytes,
-                       cudaStream_t st) {
-#define CALL(D) mse_launch_t<D>(pgf, rc, u, v, idx, n, poly, mse, scratch, scratch_bytes, st)
+int polyfit_mse_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
+                       const double *poly, double *mse, double *scratch, size_t scratch_bytes, cudaStream_t st) {
+#define CALL(D) mse_launch_t<D>(pgf, rc, u, v, sl, poly, mse, scratch, scratch_bytes, st)
     DEG_SWITCH(degree, CALL)
 #undef CALL
 }
@@ -661,35 +745,46 @@ int psf_at_launch(const double *poly, long long rc, int degree, const double *u,
     DEG_SWITCH(degree, CALL)
 #undef CALL
 }
-int small_median_launch(const double *pgf, long long rc, const long long *idx, int n, int degree, double *poly,
-                        cudaStream_t st) {
-    small_median_kernel<<<(unsigned)((rc + 127) / 128), 128, 0, st>>>(pgf, rc, idx, n, num_terms(degree), poly);
+int small_median_launch(const double *rows, long long rc, int n, int degree, double *poly, cudaStream_t st) {
+    small_median_kernel<<<(unsigned)((rc + 127) / 128), 128, 0, st>>>(rows, rc, n, num_terms(degree), poly);
+    count_launches(1);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+// fewer than five training stars in the whole catalogue: gather their rows (see small_gather_kernel); `bits` holds
+// NG bits, rows 4 * rc doubles
+int small_gather_launch(const double *pgf, long long rc, const long long *idx, const unsigned *pos, const long long *n_dev,
+                        long long NG, unsigned *bits, double *rows, const Exchange &ex, cudaStream_t st) {
+    const long long W = (NG + 31) >> 5;
+    SHOPT_CUDA_TRY(cudaMemsetAsync(bits, 0, (size_t)(W > 0 ? W : 1) * 4, st));
+    SHOPT_CUDA_TRY(cudaMemsetAsync(rows, 0, (size_t)4 * rc * 8, st));
+    alive_bits_kernel<<<1, 32, 0, st>>>(pos, n_dev, bits);
+    TRY(ex.sum(bits, W, 1));
+    small_gather_kernel<<<dim3((unsigned)((rc + 255) / 256), 4), 256, 0, st>>>(pgf, rc, idx, pos, n_dev, bits, rows);
+    TRY(ex.sum(rows, 4 * rc, 0));
+    count_launches(2);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
 
 template <int DEG>
-static int median_launch_t(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
-                           long long n, int mode, double *acc, double *med, cudaStream_t st) {
-    if (n == 0) return SHOPT_OK;
+static int median_launch_t(const double *pgf, long long rc, const double *u, const double *v, StarList sl, const double *ctr,
+                           int mode, double *acc, double *med, cudaStream_t st) {
+    if (sl.n == 0) return SHOPT_OK;
     const size_t smem = (size_t)256 * MED_PX * sizeof(unsigned int);
     auto kern = median_fix_kernel<DEG>;
     SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)((rc + MED_PX - 1) / MED_PX), MED_THREADS, smem, st>>>(pgf, rc, u, v, idx, n, mode, acc, med);
+    kern<<<(unsigned)((rc + MED_PX - 1) / MED_PX), MED_THREADS, smem, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, ctr, mode, acc, med);
+    count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
-int polyfit_median_launch(const double *pgf, long long rc, const double *u, const double *v, const long long *idx,
-                          long long n, int degree, int mode, double *acc, double *med, cudaStream_t st) {
+int polyfit_median_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
+                          const double *ctr, int mode, double *acc, double *med, cudaStream_t st) {
     if ((mode == 1 && !med) || (mode == 2 && !acc) || mode < 1 || mode > 2) return SHOPT_E_BADARG;
-#define CALL(D) median_launch_t<D>(pgf, rc, u, v, idx, n, mode, acc, med, st)
+#define CALL(D) median_launch_t<D>(pgf, rc, u, v, sl, ctr, mode, acc, med, st)
     DEG_SWITCH(degree, CALL)
 #undef CALL
-}
-int polyfit_set_coef0_launch(const double *med, long long rc, double *poly, cudaStream_t st) {
-    set_coef0_kernel<<<(unsigned)((rc + 255) / 256), 256, 0, st>>>(med, rc, poly);
-    SHOPT_CUDA_TRY(cudaGetLastError());
-    return SHOPT_OK;
 }
 
 }  // namespace shopt

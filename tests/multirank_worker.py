@@ -29,7 +29,7 @@ def main():
     # single-GPU run of the whole catalogue on every rank (no process group involved: world of one)
     full = {k: cat[k].cuda() for k in names}
     io_one = pipeline.run_stage_dev(p, full["stamps"], full["u"], full["v"], full["x0_model"], full["x0_learned"], perm,
-                                    group=dist.new_group([rank]) if world > 1 else None)
+                                    exchange="none")
     torch.cuda.synchronize()
     assert got["counts"] == io_one["counts"], (got["counts"], io_one["counts"])
     assert got["n_per_round"].tolist() == io_one["n_per_round"].tolist()

@@ -99,7 +99,7 @@ def test_building_blocks_shard_additively(stage):
         idx = idx.contiguous()
         acc = torch.empty(n_acc, device="cuda", dtype=torch.float64)
         _lib.check(L.shopt_polyfit_normal_dev(pgf.data_ptr(), r, c, u.data_ptr(), v.data_ptr(), idx.data_ptr(), len(idx),
-                                              deg, acc.data_ptr(), st))
+                                              deg, None, acc.data_ptr(), st))
         torch.cuda.synchronize()
         return acc
     idx = torch.randperm(N, device="cuda")[:700]
