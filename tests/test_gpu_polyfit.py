@@ -141,3 +141,72 @@ def test_nan_pixel_grid_values_are_replaced_by_the_median(stage, orc):
     assert np.all(np.isfinite(got["poly"])) and coef_close(got["poly"], want["poly"])
     assert np.array_equal(np.isnan(got["mse"]), np.isnan(want["mse"]))
     assert np.allclose(got["mse"], want["mse"], rtol=1e-9, equal_nan=True)
+
+
+def _design(u, v, degree):
+    return np.stack([u ** p * v ** q for p in range(degree + 1) for q in range(degree + 1 - p)], axis=1)
+
+
+@pytest.mark.parametrize("degree", [1, 2, 3])
+def test_raw_sky_coordinates(stage, orc, degree):
+    """The reference hands RAW sky coordinates to polynomial_optimizer (shopt.jl:472-490 pass u_coordinates = RA,
+    v_coordinates = Dec in degrees): u ~ 150, v ~ 2, field 0.2 deg wide, cond(A) up to 1e17.  Julia's A \\ z (pivoted QR,
+    rank truncation, minimum norm) still fits; the product's centred-basis solve must give finite coefficients whose
+    FITTED VALUES agree with the oracle's QR to 1e-6, with the same rank decision and the same rejected stars."""
+    rng = np.random.default_rng(40 + degree)
+    N, r, c = 1500, 9, 8
+    a, b = rng.uniform(-1, 1, N), rng.uniform(-1, 1, N)
+    u, v = 150.0 + 0.1 * a, 2.2 + 0.1 * b
+    K = (degree + 1) * (degree + 2) // 2
+    truth = rng.normal(size=(K, c, r)) * 0.1 + 1.0
+    pgf = np.einsum("nk,kcr->ncr", _design(a, b, degree), truth) + 1e-3 * rng.normal(size=(N, c, r))
+    pgf[rng.choice(N, 8, replace=False)] += 0.5
+    train = rng.permutation(N)[:1200]
+    got = stage.polyfit(pgf, u, v, train, degree, 3)
+    want = orc.polyfit(pgf, u, v, train, degree, 3, nthreads=orc.max_threads())
+    assert np.all(np.isfinite(got["poly"]))
+    assert got["n_per_round"].tolist() == want["n_per_round"].tolist()
+    assert got["kept"].tolist() == want["kept"].tolist()
+    V = _design(u[got["kept"]], v[got["kept"]], degree)
+    fit_g = np.einsum("nk,kcr->ncr", V, got["poly"])
+    fit_w = np.einsum("nk,kcr->ncr", V, want["poly"])
+    assert np.max(np.abs(fit_g - fit_w)) <= 1e-6 * np.max(np.abs(fit_w))
+    assert np.allclose(got["mse"], want["mse"], rtol=1e-5)
+
+
+def test_duplicated_columns_minimum_norm(stage, orc):
+    """All training stars on one line v = 2 u + 1: the design matrix is rank deficient; A \\ z returns the minimum-norm
+    solution, not NaN."""
+    rng = np.random.default_rng(77)
+    N, r, c, degree = 600, 7, 6, 3
+    u = rng.uniform(-1, 1, N)
+    v = 2 * u + 1
+    pgf = (0.2 + 0.1 * v + 0.05 * v * u)[:, None, None] * (1 + rng.uniform(size=(1, c, r))) + 1e-4 * rng.normal(size=(N, c, r))
+    train = rng.permutation(N)[:480]
+    got = stage.polyfit(pgf, u, v, train, degree, 2)
+    want = orc.polyfit(pgf, u, v, train, degree, 2, nthreads=orc.max_threads())
+    assert np.all(np.isfinite(got["poly"]))
+    assert got["kept"].tolist() == want["kept"].tolist()
+    V = _design(u[train], v[train], degree)
+    fit_g, fit_w = np.einsum("nk,kcr->ncr", V, got["poly"]), np.einsum("nk,kcr->ncr", V, want["poly"])
+    assert np.max(np.abs(fit_g - fit_w)) <= 1e-6 * np.max(np.abs(fit_w))
+    assert coef_close(got["poly"], want["poly"], 1e-6)
+
+
+def test_median_constraint_with_zero_and_nan_medians(stage, orc):
+    """interpolate.jl:118-124 with a per-pixel median of exactly 0 (the first design column vanishes: the rank-revealing
+    solve fits WITHOUT a constant term) and with a pixel that is NaN for every star (every coefficient NaN)."""
+    pgf, u, v, train, _ = make_case(21, 400, 6, 5, 2, n_out=0)
+    pgf[:, 1, 2] -= np.median(pgf[train, 1, 2])                    # odd count below: the median is an element -> exactly 0
+    train = train[:301]
+    pgf[:, 1, 2] -= np.median(pgf[train, 1, 2])
+    assert np.median(pgf[train, 1, 2]) == 0.0
+    pgf[:, 3, 3] = 0.0                                              # identically zero pixel
+    got = stage.polyfit(pgf, u, v, train, 2, 1, median_constraint=True)
+    want = orc.polyfit(pgf, u, v, train, 2, 1, median_constraint=True, nthreads=orc.max_threads())
+    assert np.array_equal(got["poly"][0], want["poly"][0])
+    assert got["poly"][0, 1, 2] == 0.0 and np.all(got["poly"][:, 3, 3] == 0.0)
+    assert coef_close(got["poly"], want["poly"])
+    pgf[:, 0, 0] = np.nan
+    got = stage.polyfit(pgf, u, v, train, 2, 1, median_constraint=True)
+    assert np.all(np.isnan(got["poly"][:, 0, 0])) and np.all(np.isfinite(got["poly"][:, 1, 1]))
