@@ -26,71 +26,12 @@ namespace shopt {
 // Scalar section: dual numbers with 3 partials, evaluated op for op like ForwardDiff does on the
 // reference's expression.  __dmul_rn/__dadd_rn/... are never contracted into FMAs.
 // ---------------------------------------------------------------------------------------------
-struct Dual {
-    double v, d[3];
-};
 __device__ __forceinline__ double mul_(double a, double b) { return __dmul_rn(a, b); }
 __device__ __forceinline__ double add_(double a, double b) { return __dadd_rn(a, b); }
 __device__ __forceinline__ double sub_(double a, double b) { return __dsub_rn(a, b); }
 __device__ __forceinline__ double div_(double a, double b) { return __ddiv_rn(a, b); }
 __device__ __forceinline__ double sqrt_(double a) { return __dsqrt_rn(a); }
-
-__device__ __forceinline__ Dual d_seed(double v, int i) {
-    Dual r = {v, {0.0, 0.0, 0.0}};
-    r.d[i] = 1.0;
-    return r;
-}
-__device__ __forceinline__ Dual d_add(Dual a, Dual b) {
-    Dual r; r.v = add_(a.v, b.v);
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = add_(a.d[i], b.d[i]);
-    return r;
-}
-__device__ __forceinline__ Dual d_sub(Dual a, Dual b) {
-    Dual r; r.v = sub_(a.v, b.v);
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = sub_(a.d[i], b.d[i]);
-    return r;
-}
-__device__ __forceinline__ Dual d_radd(double a, Dual b) { b.v = add_(a, b.v); return b; }
-__device__ __forceinline__ Dual d_rsub(double a, Dual b) {
-    Dual r; r.v = sub_(a, b.v);
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = -b.d[i];
-    return r;
-}
-__device__ __forceinline__ Dual d_rmul(double a, Dual b) {
-    Dual r; r.v = mul_(a, b.v);
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = mul_(b.d[i], a);
-    return r;
-}
-__device__ __forceinline__ Dual d_div(Dual a, Dual b) {
-    Dual r; double ib = div_(1.0, b.v), w = -div_(a.v, mul_(b.v, b.v));
-    r.v = div_(a.v, b.v);
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = add_(mul_(a.d[i], ib), mul_(b.d[i], w));
-    return r;
-}
-__device__ __forceinline__ Dual d_rdiv(double a, Dual b) {
-    Dual r; double divv = div_(a, b.v), w = -div_(divv, b.v);
-    r.v = divv;
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = mul_(w, b.d[i]);
-    return r;
-}
-__device__ __forceinline__ Dual d_sqrt(Dual a) {
-    Dual r; r.v = sqrt_(a.v); double w = div_(1.0, mul_(2.0, r.v));
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = mul_(w, a.d[i]);
-    return r;
-}
-__device__ __forceinline__ Dual d_sq(Dual a) {
-    Dual r; r.v = mul_(a.v, a.v); double w = mul_(2.0, a.v);
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = mul_(w, a.d[i]);
-    return r;
-}
+__device__ __forceinline__ double bcast_(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 // Float64 ^ 4 the way Julia >= 1.8 evaluates a literal integer power (compensated squaring).
 __device__ __forceinline__ double pow4_(double x) {
     double x2 = mul_(x, x);
@@ -101,21 +42,89 @@ __device__ __forceinline__ double pow4_(double x) {
     if (!isfinite(x4)) return x4;
     return add_(x4, lo4);
 }
-__device__ __forceinline__ Dual d_pow4(Dual a) {
-    Dual r; r.v = pow4_(a.v); double v3 = mul_(mul_(a.v, a.v), a.v);
-#pragma unroll
-    for (int i = 0; i < 3; i++) r.d[i] = mul_(mul_(a.d[i], 4.0), v3);
-    return r;
+// ---------------------------------------------------------------------------------------------
+// analyticLBFGS.jl:10-18 under ForwardDiff, restructured for ONE warp without changing a single IEEE operation.
+// ForwardDiff's Dual{3} arithmetic on  sigma, e1, e2 -> g1, g2, ms = s^2 / (1 - g1^2 - g2^2)  is 24 IEEE divisions and
+// square roots in a dependent-looking chain; executed by every lane redundantly (round 1) it WAS the critical path of
+// an evaluation: the worker warps sat on the barrier while the master ground through it.  But
+//   * the VALUE channel needs only 10 of them, three of which are independent (one lane-parallel division), as are
+//     g1 and g2 (another);
+//   * every other division is a helper of a partial (1/b, a/b^2, 1/(2 sqrt), (a/b)/b) whose operands are VALUES: all
+//     thirteen are independent of each other and run as ONE division, one helper per lane;
+//   * the three partial channels are independent: lane c carries channel c, and what is left per channel is a
+//     straight line of multiplications and additions.
+// Same operations on the same operands with the same roundings (mul_/add_/... are never contracted): the bits are
+// those of the op-for-op dual evaluation.
+// ---------------------------------------------------------------------------------------------
+struct ScalarVals {   // value channel with the intermediates the partials need
+    double ell, ell2, p4, r4, r1p, r1, inner, normG, ratio, g1, g2, sg, sg2, D, ms;
+};
+__device__ __forceinline__ ScalarVals scalar_values(double x0, double x1, double x2, int lane) {
+    ScalarVals v;
+    v.ell = sqrt_(add_(mul_(x1, x1), mul_(x2, x2)));
+    v.ell2 = mul_(v.ell, v.ell);
+    v.p4 = pow4_(v.ell);
+    {   // 4 / ell2 (lane 0), 1 / ell^4 (lane 1), 1 / ell2 (lane 2)
+        const double q = div_((lane == 0) ? 4.0 : 1.0, (lane == 1) ? v.p4 : v.ell2);
+        v.r4 = bcast_(q, 0); v.r1p = bcast_(q, 1); v.r1 = bcast_(q, 2);
+    }
+    v.inner = sqrt_(add_(v.r4, v.r1p));
+    v.normG = sqrt_(add_(1.0, mul_(0.5, sub_(v.r1, v.inner))));
+    v.ratio = div_(v.ell, v.normG);
+    {   // g1 = e1 / ratio (lane 0), g2 = e2 / ratio (lane 1)
+        const double q = div_((lane == 0) ? x1 : x2, v.ratio);
+        v.g1 = bcast_(q, 0); v.g2 = bcast_(q, 1);
+    }
+    v.sg = mul_(x0, x0);
+    v.sg2 = mul_(v.sg, v.sg);
+    v.D = sub_(sub_(1.0, mul_(v.g1, v.g1)), mul_(v.g2, v.g2));
+    v.ms = div_(v.sg2, v.D);
+    return v;
 }
-// analyticLBFGS.jl:10-18 on duals
-__device__ __forceinline__ void e_to_g_dual(Dual e1, Dual e2, Dual &g1, Dual &g2) {
-    Dual ell = d_sqrt(d_add(d_sq(e1), d_sq(e2)));
-    Dual ell2 = d_sq(ell);
-    Dual inner = d_sqrt(d_add(d_rdiv(4.0, ell2), d_rdiv(1.0, d_pow4(ell))));
-    Dual normG = d_sqrt(d_radd(1.0, d_rmul(0.5, d_sub(d_rdiv(1.0, ell2), inner))));
-    Dual ratio = d_div(ell, normG);
-    g1 = d_div(e1, ratio);
-    g2 = d_div(e2, ratio);
+// partial channel `lane` (0: d/dsigma, 1: d/de1, 2: d/de2; other lanes carry zeros) of a11 = 1 + g1, g2 and ms
+// (a22 = 1 - g1 has the negated partial of a11)
+__device__ __forceinline__ void scalar_partials(const ScalarVals &v, double x0, double x1, double x2, int lane, double &a11_d,
+                                                double &g2_d, double &ms_d) {
+    double num, den;
+    switch (lane) {   // the helper quotient of lane k
+        case 0: num = 1.0; den = mul_(2.0, v.ell); break;                  // d_sqrt(sum):        1 / (2 ell)
+        case 1: num = v.r4; den = v.ell2; break;                           // d_rdiv(4, ell2):   -(4/ell2) / ell2
+        case 2: num = v.r1p; den = v.p4; break;                            // d_rdiv(1, ell^4):  -(1/ell^4) / ell^4
+        case 3: num = 1.0; den = mul_(2.0, v.inner); break;                // d_sqrt(...):        1 / (2 inner)
+        case 4: num = v.r1; den = v.ell2; break;                           // d_rdiv(1, ell2):   -(1/ell2) / ell2
+        case 5: num = 1.0; den = mul_(2.0, v.normG); break;                // d_sqrt(...):        1 / (2 normG)
+        case 6: num = 1.0; den = v.normG; break;                           // d_div(ell, normG):  1 / normG
+        case 7: num = v.ell; den = mul_(v.normG, v.normG); break;          //                    -ell / normG^2
+        case 8: num = 1.0; den = v.ratio; break;                           // d_div(e, ratio):    1 / ratio
+        case 9: num = x1; den = mul_(v.ratio, v.ratio); break;             //                    -e1 / ratio^2
+        case 10: num = x2; den = mul_(v.ratio, v.ratio); break;            //                    -e2 / ratio^2
+        case 11: num = 1.0; den = v.D; break;                              // d_div(sg^2, D):     1 / D
+        case 12: num = v.sg2; den = mul_(v.D, v.D); break;                 //                    -sg^2 / D^2
+        default: num = 1.0; den = 1.0; break;
+    }
+    const double q = div_(num, den);
+    const double w_ell = bcast_(q, 0), w4 = -bcast_(q, 1), w1p = -bcast_(q, 2), w_inner = bcast_(q, 3), w1 = -bcast_(q, 4);
+    const double w_ng = bcast_(q, 5), ib_ng = bcast_(q, 6), w_ratio = -bcast_(q, 7), ib_r = bcast_(q, 8);
+    const double w_g1 = -bcast_(q, 9), w_g2 = -bcast_(q, 10), ib_D = bcast_(q, 11), w_ms = -bcast_(q, 12);
+    const double sig_d = (lane == 0) ? 1.0 : 0.0, e1_d = (lane == 1) ? 1.0 : 0.0, e2_d = (lane == 2) ? 1.0 : 0.0;
+    const double sg_d = mul_(mul_(2.0, x0), sig_d);                                  // d_sq(sig)
+    const double sum_d = add_(mul_(mul_(2.0, x1), e1_d), mul_(mul_(2.0, x2), e2_d)); // d_add(d_sq(e1), d_sq(e2))
+    const double ell_d = mul_(w_ell, sum_d);                                         // d_sqrt
+    const double ell2_d = mul_(mul_(2.0, v.ell), ell_d);                             // d_sq(ell)
+    const double r4_d = mul_(w4, ell2_d);                                            // d_rdiv(4, ell2)
+    const double p4_d = mul_(mul_(ell_d, 4.0), mul_(mul_(v.ell, v.ell), v.ell));     // d_pow4(ell)
+    const double r1p_d = mul_(w1p, p4_d);                                            // d_rdiv(1, ell^4)
+    const double inner_d = mul_(w_inner, add_(r4_d, r1p_d));                         // d_sqrt(d_add)
+    const double r1_d = mul_(w1, ell2_d);                                            // d_rdiv(1, ell2)
+    const double ng2_d = mul_(sub_(r1_d, inner_d), 0.5);                             // d_radd(1, d_rmul(0.5, d_sub))
+    const double normG_d = mul_(w_ng, ng2_d);                                        // d_sqrt
+    const double ratio_d = add_(mul_(ell_d, ib_ng), mul_(normG_d, w_ratio));         // d_div(ell, normG)
+    const double g1_d = add_(mul_(e1_d, ib_r), mul_(ratio_d, w_g1));                 // d_div(e1, ratio)
+    g2_d = add_(mul_(e2_d, ib_r), mul_(ratio_d, w_g2));                              // d_div(e2, ratio)
+    a11_d = g1_d;                                                                    // d_radd(1, g1); a22: d_rsub -> -g1_d
+    const double sg2_d = mul_(mul_(2.0, v.sg), sg_d);                                // d_sq(sg)
+    const double D_d = sub_(-mul_(mul_(2.0, v.g1), g1_d), mul_(mul_(2.0, v.g2), g2_d));   // d_sub(d_rsub(1, d_sq(g1)), d_sq(g2))
+    ms_d = add_(mul_(sg2_d, ib_D), mul_(D_d, w_ms));                                 // d_div(sg^2, D)
 }
 // shopt.jl:145-153 on plain doubles
 __device__ __forceinline__ void e_to_g(double e1, double e2, double &g1, double &g2) {
@@ -308,26 +317,19 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
         return out;
     }
     double *s = es.sc;
-    {   // value channel of the scalar section, op for op the .v of the dual evaluation below
-        double g1v, g2v;
-        e_to_g(x1, x2, g1v, g2v);
-        const double sgv = mul_(x0, x0);
-        const double msv = div_(mul_(sgv, sgv), sub_(sub_(1.0, mul_(g1v, g1v)), mul_(g2v, g2v)));
-        if ((threadIdx.x & 31) == 0) {
-            s[0] = add_(1.0, g1v); s[1] = sub_(1.0, g1v); s[2] = g2v; s[3] = msv;
-            es.cmd = CMD_EVAL;
-        }
+    const int lane = threadIdx.x & 31;
+    // value channel of the scalar section: all the pixel passes need
+    const ScalarVals sv = scalar_values(x0, x1, x2, lane);
+    const double A11 = add_(1.0, sv.g1), A22 = sub_(1.0, sv.g1), G2 = sv.g2, MS = sv.ms;
+    if (lane == 0) {
+        s[0] = A11; s[1] = A22; s[2] = G2; s[3] = MS;
+        es.cmd = CMD_EVAL;
     }
     bar_eval<THREADS>();                                   // workers start the pixel passes
-    Dual a11, a22, g2, ms;
-    {   // dual-number scalar section (analyticLBFGS.jl:10-18 under ForwardDiff), overlapped with pass A
-        Dual sig = d_seed(x0, 0), e1 = d_seed(x1, 1), e2 = d_seed(x2, 2);
-        Dual sg = d_sq(sig);
-        Dual g1;
-        e_to_g_dual(e1, e2, g1, g2);
-        a11 = d_radd(1.0, g1); a22 = d_rsub(1.0, g1);
-        ms = d_div(d_sq(sg), d_sub(d_rsub(1.0, d_sq(g1)), d_sq(g2)));
-    }
+    // partial channel of this lane (sigma, e1, e2 on lanes 0, 1, 2), overlapped with pass A
+    double a11_d, g2_d, ms_d;
+    scalar_partials(sv, x0, x1, x2, lane, a11_d, g2_d, ms_d);
+    const double a22_d = -a11_d;
     const double *scrA = reinterpret_cast<const double *>(smem_raw + ES_BYTES);
     const double *scrB = scrA + NWARPS * 4;
     double M[4], T[5];
@@ -339,21 +341,16 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
         for (int w = 1; w < NWARPS; w++) t += scrA[w * 4 + i];
         M[i] = t;
     }
-    const double A11 = a11.v, A22 = a22.v, G2 = g2.v, MS = ms.v;
     const double qa = A11 * A11 + G2 * G2, qb = 2.0 * (G2 * (A11 + A22)), qc = G2 * G2 + A22 * A22;
     const double A = 1.0 / M[0];
-    // rebuild the reference's sums from the moments, then the chain rule:
+    // rebuild the reference's sums from the moments, then the chain rule, one channel per lane:
     //   sum.d_j = -(ms.d_j Sq + 2 ms (a11.d_j S2 + g2.d_j S3 + a22.d_j S4))
     const double Sq = qa * M[1] + qb * M[2] + qc * M[3];
     const double Sw1u = A11 * M[1] + G2 * M[2];
     const double Sx = (A11 + A22) * M[2] + G2 * (M[1] + M[3]);
     const double Sw2v = G2 * M[2] + A22 * M[3];
-    double dA[3];
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-        const double dS = -(ms.d[j] * Sq + 2.0 * MS * (a11.d[j] * Sw1u + g2.d[j] * Sx + a22.d[j] * Sw2v));
-        dA[j] = -(A / M[0]) * dS;
-    }
+    const double dS = -(ms_d * Sq + 2.0 * MS * (a11_d * Sw1u + g2_d * Sx + a22_d * Sw2v));
+    const double dA = -(A / M[0]) * dS;
     bar_eval<THREADS>();                                   // pass B partials are in
 #pragma unroll
     for (int i = 0; i < 5; i++) {
@@ -366,12 +363,10 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
     const double Tw1u = A11 * T[2] + G2 * T[3];
     const double Tx = (A11 + A22) * T[3] + G2 * (T[2] + T[4]);
     const double Tw2v = G2 * T[3] + A22 * T[4];
+    const double dT = -(ms_d * Tq + 2.0 * MS * (a11_d * Tw1u + g2_d * Tx + a22_d * Tw2v));
+    const double gl = dA * T[1] + A * dT;                  // this lane's gradient component
     double g[3];
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-        const double dT = -(ms.d[j] * Tq + 2.0 * MS * (a11.d[j] * Tw1u + g2.d[j] * Tx + a22.d[j] * Tw2v));
-        g[j] = dA[j] * T[1] + A * dT;
-    }
+    g[0] = bcast_(gl, 0); g[1] = bcast_(gl, 1); g[2] = bcast_(gl, 2);
     out.f = T[0]; out.g0 = g[0]; out.g1 = g[1]; out.g2 = g[2];
     // every lane of the master warp stores the same bits
     es.xl[0] = x0; es.xl[1] = x1; es.xl[2] = x2;
