@@ -220,19 +220,32 @@ struct EvalShared {
     LsShared ls;                       // line-search points and base point / direction
     uint32_t crop_s, fbuf_s;           // shared-space byte addresses: staged crop, profile plane (same indexing)
     int n_a, pitch, TV, m0, rodd, plane, have_last, cmd;
+    int newstar, parity;               // first evaluation of a star: the workers look at the crop's mbarrier phase too
 };
 struct FG {
     double f, g0, g1, g2;
 };
 extern __shared__ __align__(16) unsigned char smem_raw[];
-__device__ __forceinline__ EvalShared &eval_shared() { return *reinterpret_cast<EvalShared *>(smem_raw); }
 constexpr int ES_BYTES = (sizeof(EvalShared) + 15) & ~15;
+// A CTA serves NSLOT stars at a time ("slots"): each slot has its own master warp, optimiser state, reduction scratch
+// and staged crop; the worker warps alternate between the slots, so that one star's serial phase (the master's scalar
+// chain between two evaluations: ~40 % of an evaluation's period when a CTA held one star) hides behind the other
+// star's pixel passes.  The profile plane is shared: it is live only between the two passes of one evaluation.
+template <int THREADS> __host__ __device__ constexpr int slot_stride() { return ES_BYTES + 2 * (THREADS / 32) * 6 * (int)sizeof(double); }
+template <int THREADS> __device__ __forceinline__ EvalShared &eval_shared(int slot) {
+    return *reinterpret_cast<EvalShared *>(smem_raw + slot * slot_stride<THREADS>());
+}
+template <int THREADS> __device__ __forceinline__ double *eval_scratch(int slot) {
+    return reinterpret_cast<double *>(smem_raw + slot * slot_stride<THREADS>() + ES_BYTES);
+}
+// the slot a master warp owns (master warps follow the THREADS worker threads)
+template <int THREADS> __device__ __forceinline__ int master_slot() { return ((int)threadIdx.x - THREADS) >> 5; }
 
 // Barrier of one evaluation (id 1; the star loop uses __syncthreads = id 0).  The master warp and the worker warps
 // arrive from different code, which named barriers allow as long as every warp of the CTA arrives.
 // THREADS counts the WORKER threads (warps 0 .. THREADS/32 - 1); the master warp is the extra, last warp of the CTA.
 template <int THREADS>
-__device__ __forceinline__ void bar_eval() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS + 32) : "memory"); }
+__device__ __forceinline__ void bar_eval(int slot) { asm volatile("bar.sync %0, %1;" ::"r"(1 + slot), "n"(THREADS + 32) : "memory"); }
 
 // Deterministic warp sums with a fixed tree that halves the number of live values at each step instead of carrying
 // every value through five butterflies: 6 (8) 64-bit shuffles for 4 (5) values instead of 20 (25).
@@ -266,10 +279,10 @@ __device__ __forceinline__ double warp_reduce5(double v0, double v1, double v2, 
 // published by the master) and its third.  The totals are needed by the master alone; a worker needs sum f (the
 // normalisation) for the second pass.
 template <int THREADS>
-__device__ __forceinline__ void eval_pixels() {
+__device__ __forceinline__ void eval_pixels(int slot) {
     constexpr int NWARPS = THREADS / 32;
-    EvalShared &es = eval_shared();
-    double *scrA = reinterpret_cast<double *>(smem_raw + ES_BYTES);   // NWARPS x 4
+    EvalShared &es = eval_shared<THREADS>(slot);
+    double *scrA = eval_scratch<THREADS>(slot);                       // NWARPS x 4
     double *scrB = scrA + NWARPS * 4;                                  // NWARPS x 5
     const double *s = es.sc;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -331,7 +344,7 @@ __device__ __forceinline__ void eval_pixels() {
         const double k = warp_reduce4(S0, (du * du) * S0, du * S1, S2);
         if ((lane & 7) == 0) scrA[warp * 4 + (lane >> 3)] = k;
     }
-    bar_eval<THREADS>();
+    bar_eval<THREADS>(slot);
     double sumf = scrA[0];
 #pragma unroll
     for (int w = 1; w < NWARPS; w++) sumf += scrA[w * 4];
@@ -385,7 +398,7 @@ __device__ __forceinline__ void eval_pixels() {
         if ((lane & 7) == 0) scrB[warp * 5 + 1 + (lane >> 3)] = k;
         else if (lane == 4) scrB[warp * 5] = k;
     }
-    bar_eval<THREADS>();
+    bar_eval<THREADS>(slot);
 }
 
 // value_gradient!(d, x): the reference runs g! (ForwardDiff over cost) and then cost(x); the value channel of the dual
@@ -395,7 +408,8 @@ __device__ __forceinline__ void eval_pixels() {
 template <int THREADS>
 __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
     constexpr int NWARPS = THREADS / 32;
-    EvalShared &es = eval_shared();
+    const int slot = master_slot<THREADS>();
+    EvalShared &es = eval_shared<THREADS>(slot);
     FG out;
     if (es.have_last && x0 == es.xl[0] && x1 == es.xl[1] && x2 == es.xl[2]) {
         out.f = es.fl; out.g0 = es.gl[0]; out.g1 = es.gl[1]; out.g2 = es.gl[2];
@@ -410,15 +424,15 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
         s[0] = A11; s[1] = A22; s[2] = G2; s[3] = MS;
         es.cmd = CMD_EVAL;
     }
-    bar_eval<THREADS>();                                   // workers start the pixel passes
+    bar_eval<THREADS>(slot);                               // workers start the pixel passes
     // partial channel of this lane (sigma, e1, e2 on lanes 0, 1, 2), overlapped with pass A
     double a11_d, g2_d, ms_d;
     scalar_partials(sv, x0, x1, x2, lane, a11_d, g2_d, ms_d);
     const double a22_d = -a11_d;
-    const double *scrA = reinterpret_cast<const double *>(smem_raw + ES_BYTES);
+    const double *scrA = eval_scratch<THREADS>(slot);
     const double *scrB = scrA + NWARPS * 4;
     double M[4], T[5];
-    bar_eval<THREADS>();                                   // pass A partials are in
+    bar_eval<THREADS>(slot);                               // pass A partials are in
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         double t = scrA[i];
@@ -436,7 +450,7 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
     const double Sw2v = G2 * M[2] + A22 * M[3];
     const double dS = -(ms_d * Sq + 2.0 * MS * (a11_d * Sw1u + g2_d * Sx + a22_d * Sw2v));
     const double dA = -(A / M[0]) * dS;
-    bar_eval<THREADS>();                                   // pass B partials are in
+    bar_eval<THREADS>(slot);                               // pass B partials are in
 #pragma unroll
     for (int i = 0; i < 5; i++) {
         double t = scrB[i];
@@ -457,18 +471,25 @@ __device__ __noinline__ FG eval_fg(double x0, double x1, double x2) {
     es.xl[0] = x0; es.xl[1] = x1; es.xl[2] = x2;
     es.fl = out.f; es.gl[0] = g[0]; es.gl[1] = g[1]; es.gl[2] = g[2];
     es.have_last = 1;
+    es.newstar = 0;
     __syncwarp();
     return out;
 }
 
-// Worker warps: wait for the master's command, join the pixel passes, repeat until the star is done.
-template <int THREADS>
-__device__ __forceinline__ void worker_loop() {
-    EvalShared &es = eval_shared();
-    for (;;) {
-        bar_eval<THREADS>();
-        if (*reinterpret_cast<volatile int *>(&es.cmd) == CMD_EXIT) break;
-        eval_pixels<THREADS>();
+// Worker warps: serve the slots in strict alternation -- wait for slot k's master (its next evaluation request), run
+// the two pixel passes, move on to the other slot -- until every master has said it is out of stars.  Between two stars
+// a master simply stays away from its barrier; the workers meanwhile serve the other slot and then wait.
+template <int THREADS, int NSLOT>
+__device__ __forceinline__ void worker_loop(uint64_t *bars) {
+    int alive = (1 << NSLOT) - 1;
+    for (int k = 0; alive; k = (k + 1 == NSLOT) ? 0 : k + 1) {
+        if (!(alive & (1 << k))) continue;
+        bar_eval<THREADS>(k);
+        EvalShared &es = eval_shared<THREADS>(k);
+        const int cmd = *reinterpret_cast<volatile int *>(&es.cmd);
+        if (cmd == CMD_EXIT) { alive &= ~(1 << k); continue; }
+        if (es.newstar) mbar_wait(&bars[k], (uint32_t)es.parity);   // the crop's bulk copies, observed by this thread too
+        eval_pixels<THREADS>(k);
     }
 }
 
@@ -683,7 +704,7 @@ __device__ __forceinline__ double maxabs3(const double a[3]) { return fmax(fmax(
 template <int THREADS>
 __device__ int lbfgs_fit(const double x0[3], double g_tol, int max_iter, double out_p[3], int &iters_out) {
     constexpr int M = LBFGS_M;
-    EvalShared &es = eval_shared();
+    EvalShared &es = eval_shared<THREADS>(master_slot<THREADS>());
     // the vectors of the iteration live in shared memory (every lane of the master warp stores the same bits): nothing
     // but a few scalars is live in registers across the evaluator calls
     double (&x)[3] = es.vx, (&x_prev)[3] = es.vxp, (&g)[3] = es.vg, (&g_prev)[3] = es.vgp, (&s)[3] = es.vs,
@@ -826,7 +847,7 @@ __device__ __forceinline__ void stage_issue(const FitArgs &a, long long star, do
     }
     mbar_arrive_expect_tx(bar, bytes);
 }
-// plain-load fallback for the (at most two) columns stage_issue skipped; all threads
+// plain-load fallback for the (at most two) columns stage_issue skipped; the slot's master warp
 __device__ __forceinline__ void load_edges(const FitArgs &a, long long star, double *crop) {
     const int r0 = (a.r - a.n_a) / 2, c0 = (a.c - a.n_a) / 2;
     const long long total = a.N * (long long)a.r * a.c;
@@ -838,132 +859,132 @@ __device__ __forceinline__ void load_edges(const FitArgs &a, long long star, dou
         const long long start = ge - m;
         const int len = (m + a.n_a + 1) & ~1;
         if (!(start >= 0 && start + len <= total)) {
-            for (int u = threadIdx.x; u < a.n_a; u += blockDim.x) crop[(size_t)v * a.pitch + m + u] = a.stamps[ge + u];
+            for (int u = threadIdx.x & 31; u < a.n_a; u += 32) crop[(size_t)v * a.pitch + m + u] = a.stamps[ge + u];
         }
     }
 }
 
-template <int THREADS, int MINB>
-__global__ void __launch_bounds__(THREADS + 32, MINB) fit_kernel(const FitArgs a) {
-    constexpr int NWARPS = THREADS / 32;
-    // [ EvalShared | scratch 2*NWARPS*6 | mbarriers 2 x 8 B | next_star 2 x 8 B | coff nbuf*stride | crop nbuf | f plane ]
-    EvalShared &es = eval_shared();
-    double *scratch = reinterpret_cast<double *>(smem_raw + ES_BYTES);
-    uint64_t *bars = reinterpret_cast<uint64_t *>(scratch + 2 * NWARPS * 6);
-    long long *next_star = reinterpret_cast<long long *>(bars + 2);        // 2 slots
-    unsigned char *coff_base = reinterpret_cast<unsigned char *>(next_star + 2);
+// Shared memory (dynamic): [ NSLOT x (EvalShared | scratch 2*NWARPS*6 doubles) | mbarriers NSLOT x 8 B, padded to 16 |
+//   coff NSLOT x stride | crops NSLOT x n_a*pitch doubles | profile plane n_a*pitch doubles (shared by the slots) ]
+template <int THREADS, int NSLOT, int MINB>
+__global__ void __launch_bounds__(THREADS + 32 * NSLOT, MINB) fit_kernel(const FitArgs a) {
+    unsigned char *p = smem_raw + NSLOT * slot_stride<THREADS>();
+    uint64_t *bars = reinterpret_cast<uint64_t *>(p);
+    unsigned char *coff_base = p + ((NSLOT * 8 + 15) & ~15);
     const int coff_stride = (a.n_a + 15) & ~15;
-    double *crop_base = reinterpret_cast<double *>(coff_base + (size_t)a.nbuf * coff_stride);
+    double *crop_base = reinterpret_cast<double *>(coff_base + (size_t)NSLOT * coff_stride);
     const size_t crop_stride = (size_t)a.n_a * a.pitch;
-    double *fplane = crop_base + (size_t)a.nbuf * crop_stride;
+    double *fplane = crop_base + (size_t)NSLOT * crop_stride;
 
     if (threadIdx.x == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
+        for (int k = 0; k < NSLOT; k++) mbar_init(&bars[k], 1);
         mbar_fence_init();
-        next_star[0] = (long long)atomicAdd(a.counter, 1ULL);
-        if (next_star[0] < a.N) stage_issue(a, next_star[0], crop_base, coff_base, &bars[0]);
     }
     __syncthreads();
-    long long cur = next_star[0];
-    int b = 0, slot = 0;
-    uint32_t phase[2] = {0u, 0u};
+    if (threadIdx.x < THREADS) {
+        worker_loop<THREADS, NSLOT>(bars);
+        return;
+    }
+    // ---- master warp of slot `slot`: its own star loop; every lane runs the scalar state machine redundantly ----
+    const int slot = master_slot<THREADS>(), lane = threadIdx.x & 31;
+    EvalShared &es = eval_shared<THREADS>(slot);
+    double *crop = crop_base + slot * crop_stride;
+    unsigned char *coff = coff_base + slot * coff_stride;
     const int r0 = (a.r - a.n_a) / 2, c0 = (a.c - a.n_a) / 2;
     const int mis0 = (int)(((uintptr_t)a.stamps >> 3) & 1);
-    while (cur < a.N) {
-        // grab the next star and (double-buffered) start its copies before fitting the current one
-        if (threadIdx.x == 0) {
-            const long long nx = (long long)atomicAdd(a.counter, 1ULL);
-            next_star[slot ^ 1] = nx;
-            if (a.nbuf == 2 && nx < a.N)
-                stage_issue(a, nx, crop_base + (b ^ 1) * crop_stride, coff_base + (b ^ 1) * coff_stride, &bars[b ^ 1]);
+    uint32_t phase = 0u;
+    long long nx = 0;
+    if (lane == 0) {
+        nx = (long long)atomicAdd(a.counter, 1ULL);
+        if (nx < a.N) stage_issue(a, nx, crop, coff, &bars[slot]);
+    }
+    for (;;) {
+        const long long cur = __shfl_sync(0xffffffffu, nx, 0);
+        if (cur >= a.N) break;
+        if (lane == 0) {
             const long long base = cur * (long long)a.r * a.c + r0 + (long long)c0 * a.r;
-            es.crop_s = smem_u32(crop_base + b * crop_stride); es.fbuf_s = smem_u32(fplane);
+            es.crop_s = smem_u32(crop); es.fbuf_s = smem_u32(fplane);
             es.n_a = a.n_a; es.pitch = a.pitch; es.TV = THREADS / a.n_a;      // n_a <= THREADS (checked at launch)
             es.m0 = (int)((base + mis0) & 1); es.rodd = a.r & 1; es.plane = a.plane;
-            es.have_last = 0; es.cmd = 0;
+            es.have_last = 0; es.cmd = 0; es.newstar = 1; es.parity = (int)phase;
         }
-        double *crop = crop_base + b * crop_stride;
-        mbar_wait(&bars[b], phase[b]);
-        phase[b] ^= 1u;
+        mbar_wait(&bars[slot], phase);
+        phase ^= 1u;
         load_edges(a, cur, crop);
-        __syncthreads();   // edge columns, next_star and the evaluator state visible
-
-        if (threadIdx.x < THREADS) {
-            worker_loop<THREADS>();
-        } else {   // master warp: the scalar LBFGS / HagerZhang state machine, every lane redundantly
-            const double x0[3] = {a.x0[3 * cur + 0], a.x0[3 * cur + 1], a.x0[3 * cur + 2]};
-            double p[3];
-            int iters = 0;
-            if (a.f_out) {   // cost(x0), g!(G, x0) only
-                const FG r = eval_fg<THREADS>(x0[0], x0[1], x0[2]);
-                if (threadIdx.x == THREADS) {
-                    a.f_out[cur] = r.f;
-                    a.g_out[3 * cur + 0] = r.g0; a.g_out[3 * cur + 1] = r.g1; a.g_out[3 * cur + 2] = r.g2;
-                }
+        __syncwarp();
+        const double x0[3] = {a.x0[3 * cur + 0], a.x0[3 * cur + 1], a.x0[3 * cur + 2]};
+        double pr[3];
+        int iters = 0;
+        if (a.f_out) {   // cost(x0), g!(G, x0) only
+            const FG r = eval_fg<THREADS>(x0[0], x0[1], x0[2]);
+            if (lane == 0) {
+                a.f_out[cur] = r.f;
+                a.g_out[3 * cur + 0] = r.g0; a.g_out[3 * cur + 1] = r.g1; a.g_out[3 * cur + 2] = r.g2;
             }
-            const int st = a.f_out ? 0 : lbfgs_fit<THREADS>(x0, a.g_tol, a.max_iter, p, iters);
-            if (threadIdx.x == THREADS) {
-                if (!a.f_out) {
-                    a.s[cur] = p[0]; a.g1[cur] = p[1]; a.g2[cur] = p[2];
-                    if (a.status) a.status[cur] = st;
-                    if (a.iters) a.iters[cur] = iters;
-                }
-                eval_shared().cmd = CMD_EXIT;
-            }
-            bar_eval<THREADS>();   // releases the workers
         }
-        __syncthreads();   // everyone is done with crop[b], scratch and the evaluator state
-        const long long nx = next_star[slot ^ 1];
-        slot ^= 1;
-        if (a.nbuf == 2) {
-            b ^= 1;
-        } else if (nx < a.N) {
-            if (threadIdx.x == 0) {
+        const int st = a.f_out ? 0 : lbfgs_fit<THREADS>(x0, a.g_tol, a.max_iter, pr, iters);
+        if (lane == 0) {
+            if (!a.f_out) {
+                a.s[cur] = pr[0]; a.g1[cur] = pr[1]; a.g2[cur] = pr[2];
+                if (a.status) a.status[cur] = st;
+                if (a.iters) a.iters[cur] = iters;
+            }
+            // the workers left this slot's crop at the last evaluation's final barrier: the next star may land on it
+            nx = (long long)atomicAdd(a.counter, 1ULL);
+            if (nx < a.N) {
                 fence_proxy_async();
-                stage_issue(a, nx, crop_base, coff_base, &bars[0]);
+                stage_issue(a, nx, crop, coff, &bars[slot]);
             }
         }
-        cur = nx;
+        __syncwarp();
     }
+    if (lane == 0) es.cmd = CMD_EXIT;
+    __syncwarp();
+    bar_eval<THREADS>(slot);   // tells the workers this slot is finished
 }
 
 // ---- launch ---------------------------------------------------------------------------------
-static size_t fit_smem_bytes(int nwarps, int n_a, int pitch, int nbuf, int plane) {
+template <int THREADS>
+static size_t fit_smem_bytes(int nslot, int n_a, int pitch, int plane) {
     const size_t coff_stride = (size_t)((n_a + 15) & ~15);
-    return ES_BYTES + 32 + (size_t)(2 * nwarps * 6) * sizeof(double) + nbuf * coff_stride +
-           (size_t)(nbuf + plane) * n_a * pitch * sizeof(double);
+    return (size_t)nslot * slot_stride<THREADS>() + (size_t)((nslot * 8 + 15) & ~15) + nslot * coff_stride +
+           (size_t)(nslot + plane) * n_a * pitch * sizeof(double);
 }
 
-template <int THREADS, int MINB>
-static int launch_fit(FitArgs a, cudaStream_t stream) {
-    const int nw = THREADS / 32;
+template <int THREADS, int NSLOT, int MINB>
+static int launch_fit_cfg(FitArgs a, cudaStream_t stream, bool probe_only, int *per_sm_out) {
     if (a.n_a > THREADS) return SHOPT_E_UNSUPPORTED;
     a.pitch = (a.n_a + 2 + 1) & ~1;
-    auto kern = fit_kernel<THREADS, MINB>;
-    // double-buffer the crop only when that does not cost a resident CTA (the prefetch hides ~1 us of a ~50 us fit)
-    // the profile plane is dropped (pass B recomputes exp) when crop + plane do not fit one SM
-    a.plane = fit_smem_bytes(nw, a.n_a, a.pitch, 1, 1) <= 227 * 1024 ? 1 : 0;
-    int best_nbuf = 0, best_per_sm = 0;
-    size_t best_smem = 0;
-    for (int nbuf = 2; nbuf >= 1; nbuf--) {
-        const size_t smem = fit_smem_bytes(nw, a.n_a, a.pitch, nbuf, a.plane);
-        if (smem > 227 * 1024) continue;
-        SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        int per_sm = 0;
-        SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS + 32, smem));
-        if (per_sm > best_per_sm) { best_per_sm = per_sm; best_nbuf = nbuf; best_smem = smem; }
-    }
-    if (best_per_sm < 1) return SHOPT_E_UNSUPPORTED;
-    a.nbuf = best_nbuf;
-    SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)best_smem));
-    long long grid = (long long)sm_count() * best_per_sm;
-    if (grid > a.N) grid = a.N;
+    auto kern = fit_kernel<THREADS, NSLOT, MINB>;
+    // the profile plane is dropped (pass B recomputes exp) when crops + plane do not fit one SM
+    a.plane = fit_smem_bytes<THREADS>(NSLOT, a.n_a, a.pitch, 1) <= 227 * 1024 ? 1 : 0;
+    const size_t smem = fit_smem_bytes<THREADS>(NSLOT, a.n_a, a.pitch, a.plane);
+    if (smem > 227 * 1024) return SHOPT_E_UNSUPPORTED;
+    SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS + 32 * NSLOT, smem));
+    if (per_sm_out) *per_sm_out = per_sm * (a.plane ? 2 : 1);    // a configuration that keeps the plane is preferred
+    if (per_sm < 1) return SHOPT_E_UNSUPPORTED;
+    if (probe_only) return SHOPT_OK;
+    long long grid = (long long)sm_count() * per_sm;
+    const long long want = (a.N + NSLOT - 1) / NSLOT;
+    if (grid > want) grid = want;
     SHOPT_CUDA_TRY(cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream));
-    kern<<<(unsigned)grid, THREADS + 32, best_smem, stream>>>(a);
+    kern<<<(unsigned)grid, THREADS + 32 * NSLOT, smem, stream>>>(a);
     count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
+}
+// two stars per CTA when two crops and the plane fit, else one
+template <int THREADS, int MINB2, int MINB1>
+static int launch_fit(FitArgs a, cudaStream_t stream) {
+    static const int force = getenv("SHOPT_FIT_NSLOT") ? atoi(getenv("SHOPT_FIT_NSLOT")) : 0;   // measurement switch
+    int p2 = 0, p1 = 0;
+    const int r2 = (force == 1) ? SHOPT_E_UNSUPPORTED : launch_fit_cfg<THREADS, 2, MINB2>(a, stream, true, &p2);
+    const int r1 = (force == 2) ? SHOPT_E_UNSUPPORTED : launch_fit_cfg<THREADS, 1, MINB1>(a, stream, true, &p1);
+    if (r2 == SHOPT_OK && (r1 != SHOPT_OK || 2 * p2 >= p1)) return launch_fit_cfg<THREADS, 2, MINB2>(a, stream, false, nullptr);
+    if (r1 == SHOPT_OK) return launch_fit_cfg<THREADS, 1, MINB1>(a, stream, false, nullptr);
+    return SHOPT_E_UNSUPPORTED;
 }
 
 int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n_a, const double *d_x0, double g_tol,
@@ -977,14 +998,9 @@ int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n
     a.stamps = d_stamps; a.r = r; a.c = c; a.n_a = n_a; a.N = N; a.x0 = d_x0; a.g_tol = g_tol; a.max_iter = max_iter;
     a.s = d_s; a.g1 = d_g1; a.g2 = d_g2; a.status = d_status; a.iters = d_iters; a.counter = d_counter;
     a.nbuf = 2; a.pitch = 0; a.plane = 1; a.f_out = d_f; a.g_out = d_g;
-    const int npix = n_a * n_a;
-    (void)npix;
-    if (n_a <= 32) return launch_fit<128, 6>(a, stream);
-    if (n_a <= 80) {
-        static const int minb = getenv("SHOPT_FIT_MINB") ? atoi(getenv("SHOPT_FIT_MINB")) : 3;   // measurement switch
-        return minb == 2 ? launch_fit<256, 2>(a, stream) : launch_fit<256, 3>(a, stream);
-    }
-    if (n_a <= 160) return launch_fit<512, 1>(a, stream);
+    if (n_a <= 32) return launch_fit<128, 4, 6>(a, stream);
+    if (n_a <= 80) return launch_fit<256, 2, 3>(a, stream);
+    if (n_a <= 160) return launch_fit<512, 1, 1>(a, stream);
     return SHOPT_E_UNSUPPORTED;
 }
 
