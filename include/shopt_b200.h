@@ -335,6 +335,18 @@ typedef struct shopt_stage_io {
 int64_t shopt_training_split(const int32_t *flags, int64_t n_global, const int64_t *perm, double training_ratio,
                              int64_t *train_out);
 
+/* HOST restatement of the sharded stage's exchange protocol (the device path runs the same steps as kernels,
+ * csrc/select.cu): survivor bits along the permutation + 3 counters in ONE sum-all-reduce, then the training list of
+ * this shard; worst_10_percent (shopt.jl:513-520) as an 8-pass radix select whose 4096-bin histogram is the only thing
+ * ranks exchange.  Usable without a device: the world_size-2 gloo tests drive them.  allreduce: in-place sum over the
+ * ranks of a HOST buffer of `count` elements, dtype 0 = float64, 1 = int32; NULL = single rank. */
+typedef int (*shopt_host_allreduce_fn)(void *buf, int64_t count, int dtype, void *user);
+int64_t shopt_training_split_sharded_host(const int32_t *flags_local, int64_t n_local, int64_t offset, int64_t n_global,
+                                          const int64_t *perm, double training_ratio, shopt_host_allreduce_fn allreduce,
+                                          void *user, int64_t *train_idx_out, uint32_t *train_pos_out, int64_t *counts_out);
+int64_t shopt_select_worst_sharded_host(const double *err_local, const uint32_t *pos_local, int64_t n_local, int64_t m,
+                                        shopt_host_allreduce_fn allreduce, void *user, uint8_t *reject_out);
+
 /* device-resident shard; comm == NULL runs a single GPU.  Blocks until the stage is done; the control flow between
  * the kernels (survivor counts, training split, worst_10_percent, list compaction) runs on the device, the call
  * synchronises the stream twice and allocates nothing after the first call of a given size.

@@ -51,6 +51,7 @@ class StageIO(C.Structure):
 
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p)
+HOST_ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p)
 MODE_PCA, MODE_SMOOTH, MODE_CHISQ = 0, 1, 2
 FLAG_BLACKLISTED, FLAG_PCA_FAILED, FLAG_LEARNED_OOB, FLAG_TRAINING, FLAG_REJECTED = 1, 2, 4, 8, 16
 POLY_RANK_DEFICIENT, POLY_NONFINITE, POLY_ILL_CONDITIONED = 1, 2, 4
@@ -109,6 +110,10 @@ SIGNATURES = {
     "shopt_psf_at_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int64, vp, vp]),
     "shopt_default_params": (None, [C.POINTER(Params)]),
     "shopt_training_split": (C.c_int64, [ip, C.c_int64, lp, C.c_double, lp]),
+    "shopt_training_split_sharded_host": (C.c_int64, [ip, C.c_int64, C.c_int64, C.c_int64, lp, C.c_double, vp, vp, lp,
+                                                      C.POINTER(C.c_uint32), lp]),
+    "shopt_select_worst_sharded_host": (C.c_int64, [dp, C.POINTER(C.c_uint32), C.c_int64, C.c_int64, vp, vp,
+                                                    C.POINTER(C.c_uint8)]),
     "shopt_stage_run_dev": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO), C.c_void_p, C.c_void_p, C.c_void_p]),
     "shopt_stage_run": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO)]),
     "shopt_stage_run_comm": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO), C.c_void_p, C.c_void_p]),

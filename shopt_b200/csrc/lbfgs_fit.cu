@@ -151,37 +151,31 @@ __device__ __forceinline__ void e_to_g(double e1, double e2, double &g1, double 
 // The dual-number scalar section (the manifold reparameterisation, ~10 IEEE divisions/square roots on 4-vectors)
 // is evaluated by warp 0 only and broadcast through shared memory.
 // ---------------------------------------------------------------------------------------------
-// exp(x) for the profile, x = -kappa q <= 0: 26 instructions against the library's 50 (which was 42 % of everything the
+// exp(x) for the profile, x = -kappa q <= 0: 25 instructions against the library's 50 (which was 42 % of everything the
 // kernel executed).  n = rint(x log2 e) by the 1.5 * 2^52 shift, r = x - n ln2 in two pieces (|r| <= 0.3466), Taylor
-// polynomial of degree 13 (remainder r^14 / 14! < 5e-18), scaling by 2^n through the exponent field.  Like the library's,
-// the result is within one ulp.  Results below the smallest normal (x < -708) are flushed to 0: they enter sums of O(1).
-// Branch-free, so that the four pixels a thread works on at a time interleave: the loops are latency-bound otherwise
-// (one dependent chain of ~25 FP64 operations per pixel).  NaN stays NaN; arguments above 709 (never produced by a
-// profile, whose exponent is <= 0) saturate at exp(709).
+// polynomial of degree 13 (remainder r^14 / 14! < 5e-18; coefficients come from the constant bank as instruction
+// operands), scaling by a multiplication with 2^n built in the exponent field (so NaN propagates and results below the
+// normal range round like the hardware rounds them; below 2^-1075 they are 0).  Like the library's, the result is within
+// one ulp.  Branch-free, so that the four pixels a thread works on at a time interleave: the loops are latency-bound
+// otherwise (one dependent chain of ~25 FP64 operations per pixel).  Valid for x <= 709 (the callers route evaluations
+// whose kappa is negative, infinite or NaN -- never produced by a finite profile -- to the library's exp).
+__constant__ double EXP_C[16] = {1.0, 1.0, 0.5, 1.6666666666666666e-01, 4.1666666666666664e-02, 8.333333333333333e-03,
+                                 1.3888888888888889e-03, 1.984126984126984e-04, 2.48015873015873e-05,
+                                 2.7557319223985893e-06, 2.755731922398589e-07, 2.505210838544172e-08,
+                                 2.08767569878681e-09, 1.6059043836821613e-10, 1.4426950408889634,
+                                 6755399441055744.0};
 __device__ __forceinline__ double exp_profile(double x) {
-    const double xc = fmin(fmax(x, -740.0), 709.0);
-    const double SHIFT = 6755399441055744.0;
-    const double sft = fma(xc, 1.4426950408889634, SHIFT);
+    const double xc = (x < -745.0) ? -745.0 : x;
+    const double sft = fma(xc, EXP_C[14], EXP_C[15]);
     const int n = __double2loint(sft);
-    const double nd = sft - SHIFT;
+    const double nd = sft - EXP_C[15];
     double r = fma(nd, -6.93147180369123816490e-01, xc);
     r = fma(nd, -1.90821492927058770002e-10, r);
-    double p = 1.6059043836821613e-10;                  // 1/13!
-    p = fma(p, r, 2.08767569878681e-09);                // 1/12!
-    p = fma(p, r, 2.505210838544172e-08);               // 1/11!
-    p = fma(p, r, 2.755731922398589e-07);               // 1/10!
-    p = fma(p, r, 2.7557319223985893e-06);              // 1/9!
-    p = fma(p, r, 2.48015873015873e-05);                // 1/8!
-    p = fma(p, r, 1.984126984126984e-04);               // 1/7!
-    p = fma(p, r, 1.3888888888888889e-03);              // 1/6!
-    p = fma(p, r, 8.333333333333333e-03);               // 1/5!
-    p = fma(p, r, 4.1666666666666664e-02);              // 1/4!
-    p = fma(p, r, 1.6666666666666666e-01);              // 1/3!
-    p = fma(p, r, 0.5);
-    p = fma(p, r, 1.0);
-    p = fma(p, r, 1.0);
-    const double scaled = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
-    return (x < -708.0) ? 0.0 : ((x != x) ? x : scaled);
+    double p = EXP_C[13];
+#pragma unroll
+    for (int k = 12; k >= 0; k--) p = fma(p, r, EXP_C[k]);
+    const double scale = __hiloint2double((max(n, -1023) + 1023) << 20, 0);
+    return p * scale;
 }
 
 __device__ __forceinline__ double lds_f64(uint32_t addr) {
@@ -281,6 +275,7 @@ __device__ __forceinline__ double warp_reduce5(double v0, double v1, double v2, 
 template <int THREADS>
 __device__ __forceinline__ void eval_pixels(int slot) {
     constexpr int NWARPS = THREADS / 32;
+    constexpr int UA = 8;                                             // pixels in flight per thread in pass A
     EvalShared &es = eval_shared<THREADS>(slot);
     double *scrA = eval_scratch<THREADS>(slot);                       // NWARPS x 4
     double *scrB = scrA + NWARPS * 4;                                  // NWARPS x 5
@@ -298,6 +293,7 @@ __device__ __forceinline__ void eval_pixels(int slot) {
     const double qa = A11 * A11 + G2 * G2, qb = 2.0 * (G2 * (A11 + A22)), qc = G2 * G2 + A22 * A22;
     const double c0 = (MS * qa) * (du * du), c1 = (MS * qb) * du, cc = MS * qc;
     const double step = (double)TV;
+    const bool tame = MS >= 0.0 && MS <= 1e300;        // else (never for a finite profile): the library's exp, simple loops
     // byte offset of pixel (tu, v) in the staged crop / the profile plane: (v pitch + ((m0 + v rodd) & 1) + tu) 8; along
     // v -> v + TV it advances by TV pitch 8, plus or minus 8 when the column's alignment bit flips (odd r and odd TV)
     const uint32_t o0 = (uint32_t)((tv * pitch + ((m0 + tv * rodd) & 1) + tu) * 8);
@@ -310,18 +306,18 @@ __device__ __forceinline__ void eval_pixels(int slot) {
         uint32_t o = o0;
         int inc = inc0;
         int v = tv;
-        for (; v + 3 * TV < n_a; v += 4 * TV) {        // four pixels at a time: independent exp chains interleave
-            double dvj[4], fv[4];
-            uint32_t oj[4];
+        for (; tame && v + (UA - 1) * TV < n_a; v += UA * TV) {    // UA pixels at a time: independent exp chains interleave
+            double dvj[UA], fv[UA];
+            uint32_t oj[UA];
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
+            for (int j = 0; j < UA; j++) {
                 dvj[j] = dv; oj[j] = o;
                 dv += step; o += inc; inc = incsum - inc;
             }
 #pragma unroll
-            for (int j = 0; j < 4; j++) fv[j] = exp_profile(-fma(dvj[j], fma(cc, dvj[j], c1), c0));
+            for (int j = 0; j < UA; j++) fv[j] = exp_profile(-fma(dvj[j], fma(cc, dvj[j], c1), c0));
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
+            for (int j = 0; j < UA; j++) {
                 if (plane) sts_f64(fbuf_s + oj[j], fv[j]);
                 const double fd = fv[j] * dvj[j];
                 S0 += fv[j];
@@ -330,7 +326,8 @@ __device__ __forceinline__ void eval_pixels(int slot) {
             }
         }
         for (; v < n_a; v += TV) {
-            const double fv = exp_profile(-fma(dv, fma(cc, dv, c1), c0));
+            const double xa = -fma(dv, fma(cc, dv, c1), c0);
+            const double fv = tame ? exp_profile(xa) : exp(xa);
             if (plane) sts_f64(fbuf_s + o, fv);
             o += inc; inc = incsum - inc;
             const double fd = fv * dv;
@@ -381,7 +378,8 @@ __device__ __forceinline__ void eval_pixels(int slot) {
         for (; v < n_a; v += TV) {
             const double d = lds_f64(crop_s + o);
             if (!isnan(d)) {
-                const double fv = plane ? lds_f64(fbuf_s + o) : exp_profile(-fma(dv, fma(cc, dv, c1), c0));
+                const double xa = -fma(dv, fma(cc, dv, c1), c0);
+                const double fv = plane ? lds_f64(fbuf_s + o) : (tame ? exp_profile(xa) : exp(xa));
                 const double rho = fma(A, fv, -d);
                 const double t = rho * fv, td = t * dv;
                 R0 = fma(rho, rho, R0);

@@ -1,17 +1,21 @@
-"""CPU, world_size 2 over gloo: the host-side protocol of a sharded run (shopt_stage_run_dev with an all-reduce
-callback).  Stars shard contiguously; the only exchanges are sum-all-reduces: zero-padded gathers of the survivor
-flags and of the per-star errors, and the [V'V | V'P] partial sums.  The test drives the SAME host functions the
-library uses (shopt_training_split, shopt_worst_10_percent, shard_bounds) on two ranks and checks that both ranks
-derive exactly the single-process training set and rejection sequence, and that shard partial sums add up."""
+"""CPU, world_size 2 and 3 over gloo: the exchange protocol of a sharded run.  Stars shard contiguously; the ranks
+exchange only sum-all-reduces of small buffers: the survivor bits along the permutation (+ 3 counters), and one 4096-bin
+histogram per pass of the worst-10 % radix select.  The test drives the library's HOST restatement of that protocol
+(shopt_training_split_sharded_host / shopt_select_worst_sharded_host: the same order relations and messages as the
+device kernels of csrc/select.cu) on several ranks with torch.distributed(gloo) as the all-reduce, and checks that every
+rank derives exactly the single-process training set (shopt.jl:472-478) and rejection sequence (shopt.jl:513-520,
+557-575) -- including the stable order under many exact ties and NaN errors."""
+import ctypes as C
 import os
 import socket
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from shopt_b200 import pipeline, stage
+from shopt_b200 import _lib, pipeline, stage
 
 
 def free_port():
@@ -23,6 +27,7 @@ def free_port():
 
 
 def single_process(flags, err0, perm, ratio, rounds):
+    """The reference's own order of operations on one process (host functions of the C ABI)."""
     train = pipeline.training_split(flags, perm, ratio)
     cur = train.copy()
     sizes = []
@@ -41,8 +46,57 @@ def make_inputs(n):
     rng = np.random.default_rng(123)
     flags = np.where(rng.uniform(size=n) < 0.05, 1, 0).astype(np.int32) | np.where(rng.uniform(size=n) < 0.03, 4, 0).astype(np.int32)
     err = np.round(rng.uniform(0, 1, n), 2)             # many exact ties: the stable order must survive sharding
+    err[rng.choice(n, 5, replace=False)] = np.nan       # NaN errors sort first (isless)
+    err[rng.choice(n, 3, replace=False)] = -0.0
     perm = rng.permutation(n).astype(np.int64)
     return flags, err, perm
+
+
+def host_allreduce():
+    def _cb(buf, count, dtype, user):
+        try:
+            ct = C.c_double if dtype == 0 else C.c_int32
+            arr = np.ctypeslib.as_array(C.cast(buf, C.POINTER(ct)), shape=(count,))
+            t = torch.from_numpy(arr)
+            dist.all_reduce(t)                            # in place on the library's buffer
+            return 0
+        except Exception as e:                            # never let an exception cross the C boundary
+            print("all-reduce failed:", e)
+            return 1
+    return _lib.HOST_ALLREDUCE_FN(_cb)
+
+
+def sharded_protocol(flags, err0, perm, ratio, rounds, a, b, cb):
+    """One rank's view: returns (global ids of its training stars, of its survivors after the rounds, global sizes)."""
+    L = _lib.lib()
+    n, nl = len(flags), b - a
+    fl = np.ascontiguousarray(flags[a:b])
+    idx = np.zeros(max(nl, 1), np.int64)
+    pos = np.zeros(max(nl, 1), np.uint32)
+    counts = np.zeros(4, np.int64)
+    fn = C.cast(cb, C.c_void_p) if cb is not None else None
+    m = L.shopt_training_split_sharded_host(fl.ctypes.data_as(_lib.ip), nl, a, n, perm.ctypes.data_as(_lib.lp), ratio, fn, None,
+                                            idx.ctypes.data_as(_lib.lp), pos.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                            counts.ctypes.data_as(_lib.lp))
+    assert m >= 0
+    idx, pos = idx[:m].copy(), pos[:m].copy()
+    train = idx + a
+    nc = int(counts[3])
+    sizes = []
+    for t in range(rounds):
+        sizes.append(nc)
+        if t == rounds - 1:
+            break
+        e = np.ascontiguousarray(err0[idx + a] * (1.0 + 0.01 * t))
+        mrej = int(np.ceil(0.10 * nc))
+        rej = np.zeros(max(len(idx), 1), np.uint8)
+        r = L.shopt_select_worst_sharded_host(e.ctypes.data_as(_lib.dp), pos.ctypes.data_as(C.POINTER(C.c_uint32)), len(idx),
+                                              mrej, fn, None, rej.ctypes.data_as(C.POINTER(C.c_uint8)))
+        assert r >= 0
+        keep = rej[:len(idx)] == 0
+        idx, pos = idx[keep], pos[keep]
+        nc -= mrej
+    return train, idx + a, sizes, counts
 
 
 def worker(rank, world, port, n, ratio, rounds, q):
@@ -51,41 +105,16 @@ def worker(rank, world, port, n, ratio, rounds, q):
     try:
         flags, err0, perm = make_inputs(n)
         a, b = pipeline.shard_bounds(n, world, rank)
-        # survivor flags: zero-padded gather through a sum-all-reduce (+32 marks "reported", as in api_stage.cu)
-        g = torch.zeros(n, dtype=torch.int32)
-        g[a:b] = torch.from_numpy(flags[a:b]) + 32
-        dist.all_reduce(g)
-        assert bool((g >= 32).all()), "every star is reported by exactly one rank"
-        gflags = (g.numpy() & 31).astype(np.int32)
-        train = pipeline.training_split(gflags, perm, ratio)
-        cur = train.copy()
-        sizes = []
-        acc_total = None
-        for t in range(rounds):
-            sizes.append(len(cur))
-            mine = (cur >= a) & (cur < b)
-            # normal-equation partials of this shard (a stand-in payload with the same additive structure)
-            part = torch.zeros(4, dtype=torch.float64)
-            part[0] = float(mine.sum())
-            part[1] = float(err0[cur[mine]].sum())
-            dist.all_reduce(part)
-            acc_total = part
-            # per-star errors: each rank fills the positions of its own stars, zeros elsewhere; x + 0 is exact
-            e = torch.zeros(len(cur), dtype=torch.float64)
-            e[torch.from_numpy(np.nonzero(mine)[0])] = torch.from_numpy(err0[cur[mine]] * (1.0 + 0.01 * t))
-            dist.all_reduce(e)
-            if t < rounds - 1:
-                bad = stage.worst_10_percent(e.numpy())
-                keep = np.ones(len(cur), bool)
-                keep[bad] = False
-                cur = cur[keep]
-        q.put((rank, train.tolist(), cur.tolist(), sizes, float(acc_total[0])))
+        cb = host_allreduce()
+        train, cur, sizes, counts = sharded_protocol(flags, err0, perm, ratio, rounds, a, b, cb)
+        q.put((rank, train.tolist(), cur.tolist(), sizes, counts.tolist()))
     finally:
         dist.destroy_process_group()
 
 
-def test_two_rank_protocol_matches_single_process():
-    n, ratio, rounds, world = 1003, 0.8, 3, 2
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_protocol_matches_single_process(world):
+    n, ratio, rounds = 1003, 0.8, 4
     flags, err0, perm = make_inputs(n)
     want_train, want_cur, want_sizes = single_process(flags, err0, perm, ratio, rounds)
     ctx = mp.get_context("spawn")
@@ -98,11 +127,28 @@ def test_two_rank_protocol_matches_single_process():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, train, cur, sizes, cnt in res:
-        assert train == want_train.tolist()
-        assert cur == want_cur.tolist()
+    pos_of = {int(g): i for i, g in enumerate(perm)}
+    train_all, cur_all = [], []
+    for rank, train, cur, sizes, counts in sorted(res):
+        a, b = pipeline.shard_bounds(n, world, rank)
+        assert all(a <= g < b for g in train)
+        assert train == sorted(train, key=pos_of.get)                    # training order = permutation order
         assert sizes == want_sizes
-        assert cnt == want_sizes[-1]                      # shard partial sums add up to the whole
+        assert counts[3] == len(want_train) and counts[2] == int(((flags & 7) == 0).sum())
+        train_all += train
+        cur_all += cur
+    assert sorted(train_all, key=pos_of.get) == want_train.tolist()       # the union is the single-process split ...
+    assert sorted(cur_all, key=pos_of.get) == want_cur.tolist()           # ... and so are the survivors of the rejections
+
+
+def test_single_rank_protocol_is_the_reference_order():
+    """world of one, no all-reduce: the radix select equals the stable descending sort of shopt.jl:513-520."""
+    for n in (1, 9, 10, 11, 64, 257, 1003):
+        flags, err0, perm = make_inputs(max(n, 12))
+        flags, err0, perm = flags[:n], err0[:n], np.argsort(np.argsort(perm[:n])).astype(np.int64)
+        want_train, want_cur, want_sizes = single_process(flags, err0, perm, 0.9, 3)
+        train, cur, sizes, _ = sharded_protocol(flags, err0, perm, 0.9, 3, 0, n, None)
+        assert train.tolist() == want_train.tolist() and cur.tolist() == want_cur.tolist() and sizes == want_sizes
 
 
 def test_shard_bounds_cover_and_split_rule():
