@@ -407,6 +407,94 @@ __device__ void rayleigh_ritz(const double *Z, double *T, int c, double *Q, doub
     __syncthreads();
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fastest path: ONE component.  A star stamp over a noise floor has one principal component carrying > pratio of the
+// variance (every star of the benchmark catalogues); then pca_image keeps exactly k = 1 and all that is needed is the
+// leading left singular vector u and t = Z'u.  Plain power iteration  q <- Z Z' q / |.|  from the central column
+// converges by (sigma_2 / sigma_1)^2 ~ 1e-5 per step and needs no small-matrix work at all (the block path spends 180k
+// cycles per star in its Cholesky-QRs and 8 x 8 eigenproblem; this one ~10k).  It is ACCEPTED only when the answer is
+// provably the full SVD's:  theta = |Z'q|^2 (a lower bound of sigma_1^2) already reaches pratio of |Z|_F^2 with the same
+// 1e-11 guard band as choose_pcadim's comparison in the block path, and  |Z Z'q - theta q| <= 1e-13 |Z|_F^2.
+// Anything else returns 0 with Z untouched and the block path takes over.  q, qn: r doubles; t: c doubles;
+// sc2: 4 NW doubles of scratch.  On acceptance q = u (unit), t = Z'u, *theta_out = theta.
+// ---------------------------------------------------------------------------------------------
+template <int NW>
+__device__ int power_pca(const double *Z, int r, int c, double fro, double pratio, double *q, double *qn, double *t,
+                         double *sc2, double *theta_out, int *dbg_it) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
+    const int sub = lane & 7, part = lane >> 3;
+    int buf = 0;
+    double v2[2];
+    {   // start: the central column, normalised
+        const double *z0 = Z + (size_t)(c / 2) * r;
+        double s = 0.0;
+        for (int i = tid; i < r; i += nthr) { const double z = z0[i]; s = fma(z, z, s); }
+        v2[0] = s; v2[1] = 0.0;
+        cta_sum<2, NW>(v2, sc2, buf);
+        if (!(v2[0] > 0.0) || !isfinite(v2[0])) return 0;
+        const double inv = 1.0 / sqrt(v2[0]);
+        for (int i = tid; i < r; i += nthr) q[i] = z0[i] * inv;
+        __syncthreads();
+    }
+    const double den = (double)(c - 1), thres = (fro / den) * pratio, tol = 1e-13 * fro;
+    for (int it = 1; it <= 8; it++) {
+        // t = Z' q : eight columns of Z per warp, lanes = (column sub, row part)
+        for (int j0 = warp * 8; j0 < c; j0 += NW * 8) {
+            const int j = j0 + sub;
+            const bool live = j < c;
+            const double *zc = Z + (size_t)(live ? j : 0) * r;
+            double a0 = 0.0, a1 = 0.0;
+            int i = part;
+            for (; i + 4 < r; i += 8) { a0 = fma(zc[i], q[i], a0); a1 = fma(zc[i + 4], q[i + 4], a1); }
+            if (i < r) a0 = fma(zc[i], q[i], a0);
+            double acc = live ? a0 + a1 : 0.0;
+            acc += __shfl_xor_sync(0xffffffffu, acc, 8);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+            if (part == 0 && live) t[j] = acc;
+        }
+        __syncthreads();
+        // qn = Z t : eight rows of Z per warp, lanes = (row sub, column part); theta = |t|^2
+        for (int i0 = warp * 8; i0 < r; i0 += NW * 8) {
+            const int i = i0 + sub;
+            const bool live = i < r;
+            const double *zr = Z + (live ? i : 0);
+            double a0 = 0.0, a1 = 0.0;
+            int j = part;
+            for (; j + 4 < c; j += 8) { a0 = fma(zr[(size_t)j * r], t[j], a0); a1 = fma(zr[(size_t)(j + 4) * r], t[j + 4], a1); }
+            if (j < c) a0 = fma(zr[(size_t)j * r], t[j], a0);
+            double acc = live ? a0 + a1 : 0.0;
+            acc += __shfl_xor_sync(0xffffffffu, acc, 8);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+            if (part == 0 && live) qn[i] = acc;
+        }
+        double th = 0.0;
+        for (int j = tid; j < c; j += nthr) th = fma(t[j], t[j], th);
+        v2[0] = th; v2[1] = 0.0;
+        cta_sum<2, NW>(v2, sc2, buf);                               // also publishes qn
+        const double theta = v2[0];
+        double rs = 0.0, nn = 0.0;
+        for (int i = tid; i < r; i += nthr) {
+            const double x = qn[i], d = x - theta * q[i];
+            rs = fma(d, d, rs);
+            nn = fma(x, x, nn);
+        }
+        v2[0] = rs; v2[1] = nn;
+        cta_sum<2, NW>(v2, sc2, buf);
+        const double acc1 = theta / den;
+        if (!(acc1 < thres) && !(fabs(acc1 - thres) <= 1e-11 * thres) && v2[0] <= tol * tol && theta > 0.0 && isfinite(fro)) {
+            if (dbg_it) *dbg_it = 50 + it;
+            *theta_out = theta;
+            return 1;
+        }
+        // a Rayleigh quotient well below the threshold after two steps will not reach it: this is not a one-component star
+        if (!(v2[1] > 0.0) || !isfinite(v2[1]) || (it >= 2 && acc1 < 0.97 * thres)) return 0;
+        const double inv = 1.0 / sqrt(v2[1]);
+        for (int i = tid; i < r; i += nthr) q[i] = qn[i] * inv;
+        __syncthreads();
+    }
+    return 0;
+}
+
 // returns k >= 1 on acceptance (ford[0..k) = block columns of the kept components, Q = Ritz vectors, T = Z'Q), else 0
 template <int NW, int RT>
 __device__ int fast_pca(const double *Z, int r, int c, double fro, int ncomp, double pratio, double *Q, double *Qn,
@@ -653,7 +741,13 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         if (prof && tid == 0) prof[1] = clock64();
         // ---- fast path: block subspace iteration with a-posteriori acceptance ----
         int k = 0, status = SHOPT_PCA_OK, dbg_it = 0;
-        if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
+        if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr && a.kmax >= 1 && !(a.debug & 32)) {
+            // one component: q, qn, t in the block path's buffers (column 0 of Q, Qn, T); scratch in its Gram area
+            k = power_pca<NW>(W, r, c, fro, a.pratio, FQ, FQn, FT, FG, fth, &dbg_it);
+            if (k == 1 && tid == 0) ford[0] = 0;
+            __syncthreads();
+        }
+        if (k == 0 && a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
             k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag, &dbg_it, a.debug & 4, (a.debug & 8) ? 2 : 3);
         const bool fastk = k > 0;
         if (prof && tid == 0) prof[2] = clock64();
