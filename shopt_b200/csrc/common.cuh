@@ -29,12 +29,13 @@ extern std::atomic<long long> g_launches;
 inline void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 // ---- deterministic CTA-wide sum of NV doubles ----------------------------------------------
-// Every thread returns with the same bits in v[]: xor-butterfly inside the warp (commutative, so all
-// lanes agree), one partial per warp in shared memory, then every thread adds the warp partials in
-// warp order.  `buf` alternates between two scratch areas so that one __syncthreads per call is
-// enough (a thread can only reach call n+2 after every thread has left call n).
+// Every thread returns with the same bits in v[]: xor-butterfly inside the warp (commutative, so all lanes agree), one
+// partial per warp in shared memory, then every warp adds the warp partials with a second butterfly (lane w holds
+// warp w's partial; NWARPS <= 32) -- a fixed tree, independent of timing.  `buf` alternates between two scratch areas so
+// that one __syncthreads per call is enough (a thread can only reach call n+2 after every thread has left call n).
 template <int NV, int NWARPS>
 __device__ __forceinline__ void cta_sum(double (&v)[NV], double *scratch /* 2*NWARPS*NV */, int &buf) {
+    static_assert(NWARPS <= 32, "one lane per warp partial");
 #pragma unroll
     for (int m = 16; m >= 1; m >>= 1) {
 #pragma unroll
@@ -49,9 +50,9 @@ __device__ __forceinline__ void cta_sum(double (&v)[NV], double *scratch /* 2*NW
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < NV; i++) {
-        double t = s[i];
+        double t = (lane < NWARPS) ? s[lane * NV + i] : 0.0;
 #pragma unroll
-        for (int w = 1; w < NWARPS; w++) t += s[w * NV + i];
+        for (int m = 16; m >= 1; m >>= 1) t += __shfl_xor_sync(0xffffffffu, t, m);
         v[i] = t;
     }
     buf ^= 1;

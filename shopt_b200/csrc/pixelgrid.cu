@@ -723,18 +723,40 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
             if (tid == 0) { if (a.k_out) a.k_out[star] = 0; if (a.status) a.status[star] = SHOPT_PCA_FAILED; *s_next = nxt; }
             continue;
         }
-        // ---- mean over the columns (sequential in j like mean(X, dims=2)), centre ----
-        for (int i = tid; i < r; i += nthr) {
+        // ---- mean over the columns, centre.  Thread = (row i, column segment): lanes run along i (conflict-free shared
+        //      reads), the segment sums of a row are added in segment order (the reference's mean(X, dims=2) adds the
+        //      columns in order; the two differ in the last bit of the mean only). ----
+        int nsg0 = nthr / r;
+        if (nsg0 < 1) nsg0 = 1;
+        if (nsg0 > c) nsg0 = c;
+        if (nsg0 > 2 * FB) nsg0 = 2 * FB;                       // the segment sums sit in the block path's Q buffers
+        const int sgl0 = (c + nsg0 - 1) / nsg0;
+        for (int unit = tid; unit < r * nsg0; unit += nthr) {
+            const int seg = unit / r, i = unit - seg * r;
+            const int j0 = seg * sgl0, j1 = (j0 + sgl0 < c) ? j0 + sgl0 : c;
             double s = 0.0;
-            for (int j = 0; j < c; j++) s += W[i + (size_t)j * r];
+            const double *w = W + i + (size_t)j0 * r;
+            for (int j = j0; j < j1; j++, w += r) s += *w;
+            Y[seg * r + i] = s;
+        }
+        __syncthreads();
+        for (int i = tid; i < r; i += nthr) {
+            double s = Y[i];
+            for (int seg = 1; seg < nsg0; seg++) s += Y[seg * r + i];
             mu[i] = s / c;
         }
         __syncthreads();
         double fro = 0.0;
-        for (long long p = tid; p < rc; p += nthr) {
-            const double z = W[p] - mu[(int)(p % r)];
-            W[p] = z;
-            fro = fma(z, z, fro);
+        for (int unit = tid; unit < r * nsg0; unit += nthr) {
+            const int seg = unit / r, i = unit - seg * r;
+            const int j0 = seg * sgl0, j1 = (j0 + sgl0 < c) ? j0 + sgl0 : c;
+            const double mui = mu[i];
+            double *w = W + i + (size_t)j0 * r;
+            for (int j = j0; j < j1; j++, w += r) {
+                const double z = *w - mui;
+                *w = z;
+                fro = fma(z, z, fro);
+            }
         }
         fro = block_sum1<NW>(fro, scratch, buf);                // |Z|_F^2; the block sum also publishes W
 
@@ -853,6 +875,72 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         // ---- reconstruct: R = U_k Y + mean.  Thread = (row i, column segment); the fast path leaves U and Y outside W,
         //      so R goes straight into W when it is smoothed next; the Jacobi path (U inside W) goes through `out` ----
         const bool smoothing = !a.unity_sum && a.lanczos_a > 0;
+        // ---- smooth(reconstruction) without ever forming the reconstruction.  R = mean 1' + U_k Y is a sum of k + 1 outer
+        //      products and smooth() (dataPreprocessing.jl:112-139, NaN-free image) is a separable linear map with a
+        //      separable normalisation:  out(i,j) = sum_di sum_dj kz(di) kz(dj) R(i+di, j+dj) / (A_i B_j),  A_i, B_j = sums of
+        //      the taps inside the image.  Hence  out = M 1' + U' Y'  with the 1-D smoothed factors
+        //          M(i) = sum_di kz(di) mean(i+di) / A_i,  U'_a(i) = sum_di kz(di) u_a(i+di) / A_i,  Y'_a(j) = sum_dj kz(dj) y_a(j+dj) / B_j
+        //      -- the same algebra, k FMAs per pixel instead of a reconstruction pass plus a 2 (2a+1)-tap stencil pass
+        //      (51 % of the instructions of a one-component star).  W is free by now on these two paths. ----
+        bool fused = false;
+        if (smoothing && (fastk || eigk) && a.lanczos_a <= 7 &&
+            (size_t)(eigk ? k * c : 0) + (size_t)(k + 1) * r + (size_t)k * c <= (size_t)rc) {
+            const int la = a.lanczos_a, kw = 2 * la + 1;
+            double *Ms = W + (eigk ? k * c : 0), *Us = Ms + r, *Ys = Us + (size_t)k * r;
+            int nf = 0;
+            for (int e = tid; e < (k + 1) * r; e += nthr) {          // vertical factors: the mean and the k columns of U
+                const int aa = e / r, i = e - aa * r;
+                const double *src = (aa == 0) ? mu : W + uoff[aa - 1];
+                double acc = 0.0, A = 0.0;
+                for (int t = 0; t < kw; t++) {
+                    const int ii = i + t - la;
+                    if (ii >= 0 && ii < r) { acc = fma(a.kz[t], src[ii], acc); A += a.kz[t]; }
+                }
+                const double val = acc / A;
+                if (!isfinite(val)) nf = 1;
+                Ms[e] = val;
+            }
+            for (int e = tid; e < k * c; e += nthr) {                // horizontal factors: the k rows of Y
+                const int aa = e / c, j = e - aa * c;
+                const double *src = W + yoff[aa];
+                double acc = 0.0, B = 0.0;
+                for (int t = 0; t < kw; t++) {
+                    const int jj = j + t - la;
+                    if (jj >= 0 && jj < c) { acc = fma(a.kz[t], src[jj], acc); B += a.kz[t]; }
+                }
+                const double val = acc / B;
+                if (!isfinite(val)) nf = 1;
+                Ys[e] = val;
+            }
+            nf = __syncthreads_or(nf);                               // also publishes the factors
+            if (!nf) {
+                fused = true;
+                int nsg = nthr / r;
+                if (nsg < 1) nsg = 1;
+                if (nsg > c) nsg = c;
+                const int sgl = (c + nsg - 1) / nsg;
+                for (int unit = tid; unit < r * nsg; unit += nthr) {
+                    const int seg = unit / r, i = unit - seg * r;
+                    const int j0 = seg * sgl, j1 = (j0 + sgl < c) ? j0 + sgl : c;
+                    const double m = Ms[i];
+                    double *o = out + i + (size_t)j0 * r;
+                    if (k == 1) {
+                        const double u0 = Us[i];
+                        for (int j = j0; j < j1; j++, o += r) *o = fma(u0, Ys[j], m);
+                    } else if (k == 2) {
+                        const double u0 = Us[i], u1 = Us[r + i];
+                        for (int j = j0; j < j1; j++, o += r) *o = fma(u1, Ys[c + j], fma(u0, Ys[j], m));
+                    } else {
+                        for (int j = j0; j < j1; j++, o += r) {
+                            double sacc = m;
+                            for (int aa = 0; aa < k; aa++) sacc = fma(Us[(size_t)aa * r + i], Ys[(size_t)aa * c + j], sacc);
+                            *o = sacc;
+                        }
+                    }
+                }
+            }
+        }
+        if (!fused) {
         double *Rdst = (fastk && smoothing) ? W : out;
         int nseg = nthr / r;
         if (nseg < 1) nseg = 1;
@@ -929,6 +1017,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
                 }
             }
         }
+        }   // !fused
         if (prof) {
             __syncthreads();
             if (tid == 0) {
