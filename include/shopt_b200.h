@@ -212,6 +212,19 @@ int shopt_polyfit_factor_host(const double *G, int degree, const double *centre,
 int shopt_polyfit_mse_dev(const double *d_pgf, int r, int c, const double *d_u, const double *d_v,
                           const int64_t *d_idx, int64_t n, int degree, const double *d_poly,
                           double *d_mse, void *stream);
+/* shopt_polyfit_mse_dev for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernels and bit-identical results, but the per-tile partial sums live in a static
+ * __device__ array of SHOPT_NOALLOC_MSE_SCRATCH_BYTES (held by every GPU that loads the library until exit) and the call
+ * performs no cudaMalloc / cudaFree and creates no library context.  A list of more than
+ * shopt_polyfit_mse_noalloc_max_stars(r, c, degree) stars is rejected with SHOPT_E_UNSUPPORTED and a text in
+ * shopt_last_error(); 7 710 stars of 131 x 131 at degree <= 3.  All calls share the array: calls that overlap on the GPU
+ * (two streams, concurrent graph replays) race and must be serialised by the caller. */
+#define SHOPT_NOALLOC_MSE_SCRATCH_BYTES (8 << 20)
+int64_t shopt_polyfit_mse_noalloc_max_stars(int r, int c, int degree);
+int shopt_polyfit_mse_noalloc_dev(const double *d_pgf, int r, int c, const double *d_u, const double *d_v,
+                                  const int64_t *d_idx, int64_t n, int degree, const double *d_poly,
+                                  double *d_mse, void *stream);
 /* worst_10_percent on host arrays: returns count, idx_out = positions in err (stable descending). */
 int64_t shopt_worst_10_percent(const double *err, int64_t n, int sigma_clip, int64_t *idx_out);
 

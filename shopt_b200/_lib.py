@@ -105,6 +105,8 @@ SIGNATURES = {
     "shopt_polyfit_solve_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int64, vp, vp, vp]),
     "shopt_polyfit_factor_host": (C.c_int, [dp, C.c_int, dp, C.c_int64, dp, C.c_int, dp, ip]),
     "shopt_polyfit_mse_dev": (C.c_int, [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_int, vp, vp, vp]),
+    "shopt_polyfit_mse_noalloc_dev": (C.c_int, [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_int, vp, vp, vp]),
+    "shopt_polyfit_mse_noalloc_max_stars": (C.c_int64, [C.c_int, C.c_int, C.c_int]),
     "shopt_worst_10_percent": (C.c_int64, [dp, C.c_int64, C.c_int, lp]),
     "shopt_psf_at_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int, dp, dp, C.c_int64, dp]),
     "shopt_psf_at_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int64, vp, vp]),

@@ -22,6 +22,7 @@ struct StarList {
 struct PolyFactor;
 struct Exchange;
 size_t polyfit_scratch_bytes(long long rc, long long n, int degree);
+size_t polyfit_mse_part_len(long long rc, long long n, int degree);   // doubles of scratch of polyfit_mse_launch alone
 // ctr: device {u0, 1/su, v0, 1/sv} of the centred basis, or null = raw monomials (polyfit_factor.h)
 int polyfit_normal_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
                           const double *ctr, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st);

@@ -709,6 +709,12 @@ size_t polyfit_scratch_bytes(long long rc, long long n, int degree) {
     const size_t b = (size_t)tiles * (n > 0 ? n : 1) * 8;
     return a > b ? a : b;
 }
+// doubles of per-tile partial sums that polyfit_mse_launch needs for n stars (the smaller pixel tile of its variants)
+size_t polyfit_mse_part_len(long long rc, long long n, int degree) {
+    const int px = poly_px(num_terms(degree), 1);
+    const long long tiles = (rc + POLY_THREADS * px - 1) / (POLY_THREADS * px);
+    return (size_t)tiles * (size_t)(n > 0 ? n : 0);
+}
 int polyfit_normal_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
                           const double *ctr, double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
 #define CALL(D) normal_launch_t<D>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st)
