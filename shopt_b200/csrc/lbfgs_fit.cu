@@ -151,31 +151,55 @@ __device__ __forceinline__ void e_to_g(double e1, double e2, double &g1, double 
 // The dual-number scalar section (the manifold reparameterisation, ~10 IEEE divisions/square roots on 4-vectors)
 // is evaluated by warp 0 only and broadcast through shared memory.
 // ---------------------------------------------------------------------------------------------
-// exp(x) for the profile, x = -kappa q <= 0: 25 instructions against the library's 50 (which was 42 % of everything the
-// kernel executed).  n = rint(x log2 e) by the 1.5 * 2^52 shift, r = x - n ln2 in two pieces (|r| <= 0.3466), Taylor
-// polynomial of degree 13 (remainder r^14 / 14! < 5e-18; coefficients come from the constant bank as instruction
-// operands), scaling by a multiplication with 2^n built in the exponent field (so NaN propagates and results below the
-// normal range round like the hardware rounds them; below 2^-1075 they are 0).  Like the library's, the result is within
-// one ulp.  Branch-free, so that the four pixels a thread works on at a time interleave: the loops are latency-bound
-// otherwise (one dependent chain of ~25 FP64 operations per pixel).  Valid for x <= 709 (the callers route evaluations
-// whose kappa is negative, infinite or NaN -- never produced by a finite profile -- to the library's exp).
-__constant__ double EXP_C[16] = {1.0, 1.0, 0.5, 1.6666666666666666e-01, 4.1666666666666664e-02, 8.333333333333333e-03,
-                                 1.3888888888888889e-03, 1.984126984126984e-04, 2.48015873015873e-05,
-                                 2.7557319223985893e-06, 2.755731922398589e-07, 2.505210838544172e-08,
-                                 2.08767569878681e-09, 1.6059043836821613e-10, 1.4426950408889634,
-                                 6755399441055744.0};
-__device__ __forceinline__ double exp_profile(double x) {
+// exp(x) for the profile, x = -kappa q <= 0, table-driven: 12 FP64 operations against 19 for a table-free Taylor form
+// and ~35 for the library's (the FP64 pipe is what bounds this kernel: profiles/).  n = rint(x 64 / ln 2) by the
+// 1.5 * 2^52 shift, r = x - n ln2/64 in two pieces (|r| <= 0.00542), exp(x) = 2^(n >> 6) T[n & 63] (1 + r + r^2 P(r))
+// with T[i] = 2^(i/64) correctly rounded and P the degree-3 interpolant of (e^r - 1 - r) / r^2 at Chebyshev nodes
+// (relative error of the polynomial 4.4e-18).  Scaling by a multiplication with 2^e built in the exponent field, so NaN
+// propagates; results below the normal range are flushed to 0.  Within one ulp, like the library's.  Branch-free, so
+// that the pixels a thread has in flight interleave.  Valid for x <= 709 (the callers route evaluations whose kappa is
+// negative, infinite or NaN -- never produced by a finite profile -- to the library's exp).
+// The table lives in shared memory, replicated 16 times so that lane l reads copy l & 15 -- bank l & 15 of 16 eight-byte
+// banks: two wavefronts per warp whatever the indices (an unreplicated table costs 4-5 on these effectively random n).
+constexpr int EXP_TAB_N = 64, EXP_TAB_REP = 16, EXP_TAB_BYTES = EXP_TAB_N * EXP_TAB_REP * 8;
+__device__ const double EXP_T64[EXP_TAB_N] = {
+    1, 1.0108892860517005, 1.0218971486541166, 1.0330248790212284,
+    1.0442737824274138, 1.0556451783605572, 1.0671404006768237, 1.0787607977571199,
+    1.0905077326652577, 1.1023825833078409, 1.1143867425958924, 1.1265216186082418,
+    1.1387886347566916, 1.1511892299529827, 1.1637248587775775, 1.1763969916502812,
+    1.189207115002721, 1.2021567314527031, 1.215247359980469, 1.22848053610687,
+    1.241857812073484, 1.2553807570246911, 1.2690509571917332, 1.2828700160787783,
+    1.2968395546510096, 1.3109612115247644, 1.3252366431597413, 1.3396675240533029,
+    1.3542555469368927, 1.3690024229745905, 1.383909881963832, 1.3989796725383112,
+    1.4142135623730951, 1.42961333839197, 1.4451808069770467, 1.460917794180647,
+    1.4768261459394993, 1.4929077282912648, 1.5091644275934228, 1.5255981507445384,
+    1.5422108254079407, 1.5590044002378369, 1.5759808451078865, 1.593142151342267,
+    1.6104903319492543, 1.6280274218573478, 1.6457554781539649, 1.6636765803267364,
+    1.681792830507429, 1.7001063537185235, 1.7186192981224779, 1.7373338352737062,
+    1.7562521603732995, 1.7753764925265212, 1.7947090750031072, 1.8142521755003989,
+    1.8340080864093424, 1.8539791250833855, 1.8741676341103, 1.8945759815869656,
+    1.9152065613971474, 1.9360617934922943, 1.9571441241754002, 1.9784560263879509,
+};
+__device__ __forceinline__ double lds_const_f64(uint32_t addr) {   // read-only shared data: free to be scheduled
+    double v;
+    asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+// tab = shared-space byte address of this lane's copy of the table (table base + 8 (lane & 15))
+__device__ __forceinline__ double exp_profile(double x, uint32_t tab) {
     const double xc = (x < -745.0) ? -745.0 : x;
-    const double sft = fma(xc, EXP_C[14], EXP_C[15]);
+    const double sft = fma(xc, 92.33248261689366, 6755399441055744.0);
     const int n = __double2loint(sft);
-    const double nd = sft - EXP_C[15];
-    double r = fma(nd, -6.93147180369123816490e-01, xc);
-    r = fma(nd, -1.90821492927058770002e-10, r);
-    double p = EXP_C[13];
-#pragma unroll
-    for (int k = 12; k >= 0; k--) p = fma(p, r, EXP_C[k]);
-    const double scale = __hiloint2double((max(n, -1023) + 1023) << 20, 0);
-    return p * scale;
+    const double nd = sft - 6755399441055744.0;
+    double r = fma(nd, -0.010830424696905538, xc);
+    r = fma(nd, 6.563929801064195e-13, r);
+    const double t = lds_const_f64(tab + (uint32_t)((n & (EXP_TAB_N - 1)) * (EXP_TAB_REP * 8)));
+    double q = fma(r, 0.008333339152857227, 0.041666707403338075);
+    q = fma(r, q, 0.16666666666664534);
+    q = fma(r, q, 0.4999999999998506);
+    const double p = fma(r * r, q, r);
+    const double scale = __hiloint2double((max(n >> 6, -1023) + 1023) << 20, 0);
+    return fma(t, p, t) * scale;
 }
 
 __device__ __forceinline__ double lds_f64(uint32_t addr) {
@@ -213,6 +237,7 @@ struct EvalShared {
     double vx[3], vxp[3], vg[3], vgp[3], vs[3], vdx[3], vdg[3];   // LBFGS iterate, gradient, direction, differences
     LsShared ls;                       // line-search points and base point / direction
     uint32_t crop_s, fbuf_s;           // shared-space byte addresses: staged crop, profile plane (same indexing)
+    uint32_t tab_s;                    // ... and the exp table
     int n_a, pitch, TV, m0, rodd, plane, have_last, cmd;
     int newstar, parity;               // first evaluation of a star: the workers look at the crop's mbarrier phase too
 };
@@ -283,7 +308,7 @@ __device__ __forceinline__ void eval_pixels(int slot) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_a = es.n_a, pitch = es.pitch, TV = es.TV, m0 = es.m0, rodd = es.rodd;
     const bool plane = es.plane != 0;
-    const uint32_t crop_s = es.crop_s, fbuf_s = es.fbuf_s;
+    const uint32_t crop_s = es.crop_s, fbuf_s = es.fbuf_s, tab = es.tab_s + 8u * (lane & 15);
     const int tv = threadIdx.x / n_a, tu = threadIdx.x - tv * n_a;
     const bool active = tv < TV;
     const double du = (double)(tu + 1) - n_a / 2.0;    // analyticLBFGS.jl:28,41: the centre is (r/2, c/2) of the crop
@@ -315,7 +340,7 @@ __device__ __forceinline__ void eval_pixels(int slot) {
                 dv += step; o += inc; inc = incsum - inc;
             }
 #pragma unroll
-            for (int j = 0; j < UA; j++) fv[j] = exp_profile(-fma(dvj[j], fma(cc, dvj[j], c1), c0));
+            for (int j = 0; j < UA; j++) fv[j] = exp_profile(-fma(dvj[j], fma(cc, dvj[j], c1), c0), tab);
 #pragma unroll
             for (int j = 0; j < UA; j++) {
                 if (plane) sts_f64(fbuf_s + oj[j], fv[j]);
@@ -327,7 +352,7 @@ __device__ __forceinline__ void eval_pixels(int slot) {
         }
         for (; v < n_a; v += TV) {
             const double xa = -fma(dv, fma(cc, dv, c1), c0);
-            const double fv = tame ? exp_profile(xa) : exp(xa);
+            const double fv = tame ? exp_profile(xa, tab) : exp(xa);
             if (plane) sts_f64(fbuf_s + o, fv);
             o += inc; inc = incsum - inc;
             const double fd = fv * dv;
@@ -379,7 +404,7 @@ __device__ __forceinline__ void eval_pixels(int slot) {
             const double d = lds_f64(crop_s + o);
             if (!isnan(d)) {
                 const double xa = -fma(dv, fma(cc, dv, c1), c0);
-                const double fv = plane ? lds_f64(fbuf_s + o) : (tame ? exp_profile(xa) : exp(xa));
+                const double fv = plane ? lds_f64(fbuf_s + o) : (tame ? exp_profile(xa, tab) : exp(xa));
                 const double rho = fma(A, fv, -d);
                 const double t = rho * fv, td = t * dv;
                 R0 = fma(rho, rho, R0);
@@ -863,7 +888,8 @@ __device__ __forceinline__ void load_edges(const FitArgs &a, long long star, dou
 }
 
 // Shared memory (dynamic): [ NSLOT x (EvalShared | scratch 2*NWARPS*6 doubles) | mbarriers NSLOT x 8 B, padded to 16 |
-//   coff NSLOT x stride | crops NSLOT x n_a*pitch doubles | profile plane n_a*pitch doubles (shared by the slots) ]
+//   coff NSLOT x stride | crops NSLOT x n_a*pitch doubles | profile plane n_a*pitch doubles (shared by the slots) |
+//   exp table 64 x 16 doubles ]
 template <int THREADS, int NSLOT, int MINB>
 __global__ void __launch_bounds__(THREADS + 32 * NSLOT, MINB) fit_kernel(const FitArgs a) {
     unsigned char *p = smem_raw + NSLOT * slot_stride<THREADS>();
@@ -873,6 +899,8 @@ __global__ void __launch_bounds__(THREADS + 32 * NSLOT, MINB) fit_kernel(const F
     double *crop_base = reinterpret_cast<double *>(coff_base + (size_t)NSLOT * coff_stride);
     const size_t crop_stride = (size_t)a.n_a * a.pitch;
     double *fplane = crop_base + (size_t)NSLOT * crop_stride;
+    double *exp_tab = fplane + (size_t)a.plane * crop_stride;
+    for (int i = threadIdx.x; i < EXP_TAB_N * EXP_TAB_REP; i += blockDim.x) exp_tab[i] = EXP_T64[i / EXP_TAB_REP];
 
     if (threadIdx.x == 0) {
         for (int k = 0; k < NSLOT; k++) mbar_init(&bars[k], 1);
@@ -901,7 +929,7 @@ __global__ void __launch_bounds__(THREADS + 32 * NSLOT, MINB) fit_kernel(const F
         if (cur >= a.N) break;
         if (lane == 0) {
             const long long base = cur * (long long)a.r * a.c + r0 + (long long)c0 * a.r;
-            es.crop_s = smem_u32(crop); es.fbuf_s = smem_u32(fplane);
+            es.crop_s = smem_u32(crop); es.fbuf_s = smem_u32(fplane); es.tab_s = smem_u32(exp_tab);
             es.n_a = a.n_a; es.pitch = a.pitch; es.TV = THREADS / a.n_a;      // n_a <= THREADS (checked at launch)
             es.m0 = (int)((base + mis0) & 1); es.rodd = a.r & 1; es.plane = a.plane;
             es.have_last = 0; es.cmd = 0; es.newstar = 1; es.parity = (int)phase;
@@ -946,7 +974,7 @@ template <int THREADS>
 static size_t fit_smem_bytes(int nslot, int n_a, int pitch, int plane) {
     const size_t coff_stride = (size_t)((n_a + 15) & ~15);
     return (size_t)nslot * slot_stride<THREADS>() + (size_t)((nslot * 8 + 15) & ~15) + nslot * coff_stride +
-           (size_t)(nslot + plane) * n_a * pitch * sizeof(double);
+           (size_t)(nslot + plane) * n_a * pitch * sizeof(double) + EXP_TAB_BYTES;
 }
 
 template <int THREADS, int NSLOT, int MINB>
