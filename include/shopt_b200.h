@@ -113,6 +113,27 @@ int shopt_fit_analytic_batch_dev(const double *d_stamps, int r, int c, int64_t N
                                  double *d_s, double *d_g1, double *d_g2,
                                  int32_t *d_status, int32_t *d_iters, void *stream);
 
+/* The same fit with the radial profile as an argument.  SHOPT_PROFILE_GAUSSIAN is fGaussian (radialProfiles.jl:5-9),
+ * the only profile the reference's cost ever calls; SHOPT_PROFILE_KOLMOGOROV is fkolmogorov (radialProfiles.jl:11-24,
+ * defined but unreachable in the reference) in the same cost: sum-normalised over all crop pixels, residuals over the
+ * non-NaN ones.  Fkolmogorov(k, 1) as written is exp(-C k), C = (24 gamma(6.5) 0.2)^(5/6) / (2 pi)^(5/3) = 19.3531...,
+ * so the quadgk integral of :21-23 has the closed form (1 / 2 pi) C / (C^2 + squareRadius)^(3/2), which is what the
+ * kernel evaluates (no quadrature).  n_a <= 160 for either profile (SHOPT_E_UNSUPPORTED beyond: the crop of one star,
+ * and of two when they fit, is staged in one SM's shared memory). */
+#define SHOPT_PROFILE_GAUSSIAN   0
+#define SHOPT_PROFILE_KOLMOGOROV 1
+int shopt_fit_profile_batch(int profile, const double *stamps, int r, int c, int64_t N, int n_a,
+                            const double *x0, double g_tol, int max_iter,
+                            double *s, double *g1, double *g2, int32_t *status, int32_t *iters);
+int shopt_fit_profile_batch_dev(int profile, const double *d_stamps, int r, int c, int64_t N, int n_a,
+                                const double *d_x0, double g_tol, int max_iter,
+                                double *d_s, double *d_g1, double *d_g2,
+                                int32_t *d_status, int32_t *d_iters, void *stream);
+int shopt_profile_cost_grad_batch(int profile, const double *stamps, int r, int c, int64_t N, int n_a,
+                                  const double *x, double *f, double *g);
+int shopt_profile_cost_grad_batch_dev(int profile, const double *d_stamps, int r, int c, int64_t N, int n_a,
+                                      const double *d_x, double *d_f, double *d_g, void *stream);
+
 /* cost(params) / g!(storage, params) of analyticLBFGS.jl:8-46, 89-94 (costD / gD! :49-87, 96-101 on
  * pixel-grid fits) for one parameter vector [sigma, e1, e2] per star:  f (N), g (3,N). */
 int shopt_analytic_cost_grad_batch(const double *stamps, int r, int c, int64_t N, int n_a,
@@ -249,8 +270,8 @@ int shopt_field_interp(const double *u, const double *v, const double *const *va
 int shopt_field_eval(const double *coef, const double *u, const double *v, int64_t n, double *out);
 
 /* ---- summary.shopt: the stage's on-disk product ---------------------------------------------------
- * Writer for the truncated summary file (truncate_summary_file: true, the shipped default) of
- * dataOutprocessing.jl:52-84 and reader for read_shopt of reader.jl:13-38, as a self-contained FITS implementation
+ * Writers for the truncated summary file (truncate_summary_file: true, the shipped default; dataOutprocessing.jl:52-84)
+ * and the full one (:86-168), and reader for read_shopt of reader.jl:13-38, as a self-contained FITS implementation
  * (astropy is what the reference calls through PyCall):
  *   HDU 0 image POLYNOMIAL_MATRIX  float64, numpy shape (r, c, K);  HDU 1 BINTABLE SUMMARY_STATISTICS, column
  *   POLYNOMIAL_DEGREE;  HDU 2 BINTABLE ANALYTIC_PROFILE, columns s_MATRIX, g1_MATRIX, g2_MATRIX (10 rows each, the
@@ -259,6 +280,24 @@ int shopt_field_eval(const double *coef, const double *u, const double *v, int64
  * so the reference's full layout (ANALYTIC_PROFILE = HDU 6) reads too; poly may be NULL to query r, c, degree. */
 int shopt_summary_write(const char *path, const double *poly, int r, int c, int degree, const double *sC,
                         const double *g1C, const double *g2C);
+/* The full file (truncate_summary_file: false, dataOutprocessing.jl:86-168): seven HDUs -- POLYNOMIAL_MATRIX,
+ * SUMMARY_STATISTICS (per-star columns U_COORDINATES ... g2_DATA, the training / validation coordinates and
+ * POLYNOMIAL_DEGREE, zero-padded to the longest column as astropy does), VIGNETS (numpy (r, c, N)), PIXEL_GRID_FITS and
+ * VALIDATION_STARS (numpy (N, r, c): the reference hands astropy the Vector{Matrix}, not the stacked cube), FLAGS,
+ * ANALYTIC_PROFILE.  Cubes are (r, c, n) column-major as everywhere in this interface; flag arrays hold the reference's
+ * 1-based star numbers as doubles (it stores them with format 'D').  Arrays of length 0 may be NULL. */
+typedef struct shopt_summary_full {
+    const double *poly; int r, c, degree;                 /* (r, c, K) PolynomialMatrix                               */
+    const double *sC, *g1C, *g2C;                         /* 10 each: the cubic field fits                            */
+    int64_t n_stars;                                      /* stars left after the splices                             */
+    const double *u, *v, *s_model, *g1_model, *g2_model, *s_data, *g1_data, *g2_data;   /* n_stars each             */
+    const double *stars, *pgf;                            /* (r, c, n_stars): starCatalog, pixelGridFits              */
+    int64_t n_train; const double *train_u, *train_v;     /* training set after the last applied rejection            */
+    int64_t n_valid; const double *valid_u, *valid_v, *valid_stars;   /* validation split; valid_stars (r, c, n_valid) */
+    int64_t n_flag_snr, n_flag_blacklist, n_flag_failed;
+    const double *flag_snr, *flag_blacklist, *flag_failed;            /* outlier_indices, s_blacklist, failedStars     */
+} shopt_summary_full;
+int shopt_summary_write_full(const char *path, const shopt_summary_full *f);
 int shopt_summary_read(const char *path, double *poly, int64_t poly_capacity, int *r, int *c, int *degree, double *sC,
                        double *g1C, double *g2C);
 
@@ -284,6 +323,7 @@ typedef struct shopt_params {
     int    sigma_clip;          /* outlier_sigma_clipping                                        */
     int    mode;                /* mode: SHOPT_MODE_PCA / _SMOOTH / _CHISQ (pixel-grid fit)      */
     double chisq_fill;          /* mode chisq without a start cube: value of the pixels that have no finite term */
+    int    profile;             /* SHOPT_PROFILE_* of the model and learned fits (the reference: Gaussian)       */
 } shopt_params;
 #define SHOPT_MODE_PCA    0     /* shopt.jl:281-314 */
 #define SHOPT_MODE_SMOOTH 1     /* shopt.jl:316-348 (the shipped shopt.yml default) */

@@ -96,6 +96,46 @@ static inline dual fgaussian_dual(double du, double dv, dual a11, dual g2, dual 
     return d_exp(d_neg(d_mul(ms, q)));
 }
 
+/* radialProfiles.jl:11-24  fkolmogorov(u, v, g1, g2, s, uc, vc) with Fk = Fkolmogorov, lambda = 1, r0 = 1.
+ * Fkolmogorov(k, 1) = exp(-(24 gamma(6.5) 0.2)^(5/6) * (k / (2 pi)^(5/3))) = exp(-C k)            (:11-14, as written)
+ * result = quadgk(k -> Fk(k) besselj0(k rho) k, 0, Inf), rho = squareRadius^0.5                      (:21-22)
+ *        = C / (C^2 + rho^2)^(3/2)          (Laplace transform of k J0(rho k): Gradshteyn-Ryzhik 6.623.2)
+ * returned value (1 / 2 pi) * result                                                                   (:23)
+ * The quadrature is replaced by its closed form; C is evaluated from the reference's expression. */
+static double kolmogorov_c(void) {
+    static double c = 0.0;
+    if (c == 0.0) c = pow(24.0 * tgamma(6.5) * 0.2, 5.0 / 6.0) / pow(2.0 * M_PI, 5.0 / 3.0);
+    return c;
+}
+double orc_fkolmogorov(double u, double v, double g1, double g2, double s, double uc, double vc) {
+    double du = u - uc, dv = v - vc;
+    double w1 = (1.0 + g1) * du + g2 * dv;
+    double w2 = g2 * du + (1.0 - g1) * dv;
+    double q = w1 * w1 + w2 * w2;
+    double ms = (s * s) / (1.0 - g1 * g1 - g2 * g2);
+    double rho2 = q * ms;                          /* squareRadius = squareRadiusFactor * matrixScalar */
+    double C = kolmogorov_c(), t = C * C + rho2;
+    return (1.0 / (2.0 * M_PI)) * (C / (t * sqrt(t)));
+}
+static inline dual fkolmogorov_dual(double du, double dv, dual a11, dual g2, dual a22, dual ms) {
+    dual w1 = d_add(d_rmul(du, a11), d_rmul(dv, g2));
+    dual w2 = d_add(d_rmul(du, g2), d_rmul(dv, a22));
+    dual q = d_add(d_sq(w1), d_sq(w2));
+    double C = kolmogorov_c();
+    dual t = d_radd(C * C, d_mul(q, ms));
+    return d_rmul(1.0 / (2.0 * M_PI), d_rdiv(C, d_mul(t, d_sqrt(t))));
+}
+/* which radial profile cost / g! use: 0 fGaussian (the reference's only call site), 1 fkolmogorov */
+static int g_profile = 0;
+void orc_set_profile(int profile) { g_profile = profile; }
+int orc_get_profile(void) { return g_profile; }
+static inline double profile_val(double u, double v, double g1, double g2, double s, double uc, double vc) {
+    return g_profile ? orc_fkolmogorov(u, v, g1, g2, s, uc, vc) : orc_fgaussian(u, v, g1, g2, s, uc, vc);
+}
+static inline dual profile_dual(double du, double dv, dual a11, dual g2, dual a22, dual ms) {
+    return g_profile ? fkolmogorov_dual(du, dv, a11, g2, a22, ms) : fgaussian_dual(du, dv, a11, g2, a22, ms);
+}
+
 /* analyticLBFGS.jl:10-18 (and shopt.jl:145-153): [e1,e2] -> [g1,g2], op for op */
 void orc_e_to_g(double e1, double e2, double *g1, double *g2) {
     double ell = sqrt(e1 * e1 + e2 * e2);
@@ -128,14 +168,14 @@ double orc_cost(const double *stamp, int r, int c, int n_a, const double x[3]) {
     double sum = 0.0;
     for (int u = 1; u <= n_a; u++)
         for (int v = 1; v <= n_a; v++)
-            sum += orc_fgaussian(u, v, g1, g2, sg, uc, vc);
+            sum += profile_val(u, v, g1, g2, sg, uc, vc);
     double A = 1.0 / sum;
     double total = 0.0;
     for (int u = 1; u <= n_a; u++)
         for (int v = 1; v <= n_a; v++) {
             double d = stamp[(size_t)(r0 + u - 1) + (size_t)(c0 + v - 1) * r];
             if (isnan(d)) continue;
-            double t = A * orc_fgaussian(u, v, g1, g2, sg, uc, vc) - d;
+            double t = A * profile_val(u, v, g1, g2, sg, uc, vc) - d;
             total += 0.5 * (t * t);
         }
     return total;
@@ -154,14 +194,14 @@ static double grad_val(const double *stamp, int r, int c, int n_a, const double 
     dual sum = d_const(0.0);
     for (int u = 1; u <= n_a; u++)
         for (int v = 1; v <= n_a; v++)
-            sum = d_add(sum, fgaussian_dual(u - uc, v - vc, a11, g2, a22, ms));
+            sum = d_add(sum, profile_dual(u - uc, v - vc, a11, g2, a22, ms));
     dual A = d_rdiv(1.0, sum);
     dual total = d_const(0.0);
     for (int u = 1; u <= n_a; u++)
         for (int v = 1; v <= n_a; v++) {
             double d = stamp[(size_t)(r0 + u - 1) + (size_t)(c0 + v - 1) * r];
             if (isnan(d)) continue;
-            dual t = d_subr(d_mul(A, fgaussian_dual(u - uc, v - vc, a11, g2, a22, ms)), d);
+            dual t = d_subr(d_mul(A, profile_dual(u - uc, v - vc, a11, g2, a22, ms)), d);
             total = d_add(total, d_rmul(0.5, d_sq(t)));
         }
     g[0] = total.d[0]; g[1] = total.d[1]; g[2] = total.d[2];

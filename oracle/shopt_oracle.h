@@ -36,6 +36,11 @@ extern "C" {
 
 /* ---- analytic profile: radialProfiles.jl:5-9, analyticLBFGS.jl:8-101 ---- */
 double orc_fgaussian(double u, double v, double g1, double g2, double s, double uc, double vc);
+/* radialProfiles.jl:11-24 with the quadgk integral in closed form */
+double orc_fkolmogorov(double u, double v, double g1, double g2, double s, double uc, double vc);
+/* radial profile used by orc_cost / orc_grad / orc_lbfgs_fit: 0 fGaussian (default; the reference's), 1 fkolmogorov */
+void orc_set_profile(int profile);
+int orc_get_profile(void);
 double orc_cost(const double *stamp, int r, int c, int n_a, const double x[3]);
 void   orc_grad(const double *stamp, int r, int c, int n_a, const double x[3], double g[3]);
 void   orc_e_to_g(double e1, double e2, double *g1, double *g2);

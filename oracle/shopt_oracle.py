@@ -100,6 +100,12 @@ def lib():
         L.orc_psf_at.restype = None
         L.orc_psf_at.argtypes = [_dp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _dp]
         L.orc_max_threads.restype = C.c_int
+        L.orc_fkolmogorov.restype = C.c_double
+        L.orc_fkolmogorov.argtypes = [C.c_double] * 7
+        L.orc_set_profile.restype = None
+        L.orc_set_profile.argtypes = [C.c_int]
+        L.orc_get_profile.restype = C.c_int
+        L.orc_get_profile.argtypes = []
         L.orc_set_reference_shaped.restype = None
         L.orc_set_reference_shaped.argtypes = [C.c_int]
         _LIB = L
@@ -116,6 +122,15 @@ def max_threads():
 
 def set_reference_shaped(on):
     lib().orc_set_reference_shaped(int(bool(on)))
+
+
+def set_profile(profile):
+    """0: fGaussian (default), 1: fkolmogorov -- the profile orc_cost / orc_grad / lbfgs_fit evaluate."""
+    lib().orc_set_profile(int(profile))
+
+
+def fkolmogorov(u, v, g1, g2, s, uc, vc):
+    return lib().orc_fkolmogorov(u, v, g1, g2, s, uc, vc)
 
 
 def fgaussian(u, v, g1, g2, s, uc, vc):

@@ -104,6 +104,7 @@ def run_stage(p, stamps, u, v, x0_model, x0_learned, perm, nthreads=1, fit_only=
     polyfit (the reference's only @threads loop, shopt.jl:543); default: nthreads."""
     N = stamps.shape[0]
     nthreads_poly = nthreads if nthreads_poly is None else nthreads_poly
+    orc.set_profile(getattr(p, "profile", 0))     # radial profile of both analytic fits (0: the reference's fGaussian)
     s, g1, g2, mst, mit = orc.fit_analytic_batch(stamps, p.n_a, x0_model, p.g_tol_model, p.max_iter, nthreads)
     model = np.stack([s, g1, g2])
     if fit_only:

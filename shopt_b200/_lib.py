@@ -36,7 +36,7 @@ class Params(C.Structure):
                 ("max_iter", C.c_int), ("s_lo", C.c_double), ("s_hi", C.c_double), ("pca_terms", C.c_int),
                 ("pratio", C.c_double), ("lanczos", C.c_int), ("unity_sum", C.c_int), ("degree", C.c_int),
                 ("iterations", C.c_int), ("training_ratio", C.c_double), ("median_constraint", C.c_int),
-                ("sigma_clip", C.c_int), ("mode", C.c_int), ("chisq_fill", C.c_double)]
+                ("sigma_clip", C.c_int), ("mode", C.c_int), ("chisq_fill", C.c_double), ("profile", C.c_int)]
 
 
 class StageIO(C.Structure):
@@ -50,9 +50,21 @@ class StageIO(C.Structure):
                 ("model_status", vp), ("model_iters", vp), ("learned_status", vp), ("learned_iters", vp)]
 
 
+class SummaryFull(C.Structure):
+    """struct shopt_summary_full."""
+    _fields_ = [("poly", dp), ("r", C.c_int), ("c", C.c_int), ("degree", C.c_int), ("sC", dp), ("g1C", dp), ("g2C", dp),
+                ("n_stars", C.c_int64), ("u", dp), ("v", dp), ("s_model", dp), ("g1_model", dp), ("g2_model", dp),
+                ("s_data", dp), ("g1_data", dp), ("g2_data", dp), ("stars", dp), ("pgf", dp),
+                ("n_train", C.c_int64), ("train_u", dp), ("train_v", dp),
+                ("n_valid", C.c_int64), ("valid_u", dp), ("valid_v", dp), ("valid_stars", dp),
+                ("n_flag_snr", C.c_int64), ("n_flag_blacklist", C.c_int64), ("n_flag_failed", C.c_int64),
+                ("flag_snr", dp), ("flag_blacklist", dp), ("flag_failed", dp)]
+
+
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p)
 HOST_ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p)
 MODE_PCA, MODE_SMOOTH, MODE_CHISQ = 0, 1, 2
+PROFILE_GAUSSIAN, PROFILE_KOLMOGOROV = 0, 1
 FLAG_BLACKLISTED, FLAG_PCA_FAILED, FLAG_LEARNED_OOB, FLAG_TRAINING, FLAG_REJECTED = 1, 2, 4, 8, 16
 POLY_RANK_DEFICIENT, POLY_NONFINITE, POLY_ILL_CONDITIONED = 1, 2, 4
 UNIQUE_ID_BYTES = 128
@@ -77,6 +89,12 @@ SIGNATURES = {
                                            dp, dp, dp, ip, ip]),
     "shopt_fit_analytic_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, C.c_double, C.c_int,
                                                vp, vp, vp, vp, vp, vp]),
+    "shopt_fit_profile_batch": (C.c_int, [C.c_int, dp, C.c_int, C.c_int, C.c_int64, C.c_int, dp, C.c_double, C.c_int,
+                                          dp, dp, dp, ip, ip]),
+    "shopt_fit_profile_batch_dev": (C.c_int, [C.c_int, vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, C.c_double, C.c_int,
+                                              vp, vp, vp, vp, vp, vp]),
+    "shopt_profile_cost_grad_batch": (C.c_int, [C.c_int, dp, C.c_int, C.c_int, C.c_int64, C.c_int, dp, dp, dp]),
+    "shopt_profile_cost_grad_batch_dev": (C.c_int, [C.c_int, vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, vp, vp, vp]),
     "shopt_analytic_cost_grad_batch": (C.c_int, [dp, C.c_int, C.c_int, C.c_int64, C.c_int, dp, dp, dp]),
     "shopt_analytic_cost_grad_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, C.c_int, vp, vp, vp, vp]),
     "shopt_s_out_of_bounds": (C.c_int64, [dp, C.c_int64, C.c_double, C.c_double, lp]),
@@ -93,6 +111,7 @@ SIGNATURES = {
     "shopt_ingest_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, vp, vp]),
     "shopt_snr_cut": (C.c_int64, [C.POINTER(C.c_float), C.c_int64, C.c_double, lp, dp]),
     "shopt_summary_write": (C.c_int, [C.c_char_p, dp, C.c_int, C.c_int, C.c_int, dp, dp, dp]),
+    "shopt_summary_write_full": (C.c_int, [C.c_char_p, C.POINTER(SummaryFull)]),
     "shopt_summary_read": (C.c_int, [C.c_char_p, dp, C.c_int64, C.POINTER(C.c_int), C.POINTER(C.c_int),
                                      C.POINTER(C.c_int), dp, dp, dp]),
     "shopt_field_interp": (C.c_int, [dp, dp, C.POINTER(dp), C.c_int, C.c_int64, dp]),

@@ -194,20 +194,31 @@ void shopt_default_params(shopt_params *p) {
     p->n_a = 64; p->g_tol_model = 1e-6; p->g_tol_learned = 1e-6; p->max_iter = 1000;
     p->s_lo = 0.075; p->s_hi = 1.0; p->pca_terms = 50; p->pratio = 0.99; p->lanczos = 3; p->unity_sum = 0;
     p->degree = 3; p->iterations = 3; p->training_ratio = 0.8; p->median_constraint = 0; p->sigma_clip = 0;
-    p->mode = SHOPT_MODE_PCA; p->chisq_fill = 0.0;
+    p->mode = SHOPT_MODE_PCA; p->chisq_fill = 0.0; p->profile = SHOPT_PROFILE_GAUSSIAN;
 }
 
 // ---- (1) analytic fit ---------------------------------------------------------------------
+int shopt_fit_profile_batch_dev(int profile, const double *d_stamps, int r, int c, int64_t N, int n_a, const double *d_x0,
+                                double g_tol, int max_iter, double *d_s, double *d_g1, double *d_g2,
+                                int32_t *d_status, int32_t *d_iters, void *stream) {
+    Ctx *ctx; TRY(get_ctx(&ctx));
+    return fit_analytic_launch(d_stamps, r, c, (long long)N, n_a, d_x0, g_tol, max_iter, d_s, d_g1, d_g2, d_status,
+                               d_iters, ctx->next_counter(), (cudaStream_t)stream, nullptr, nullptr, profile);
+}
 int shopt_fit_analytic_batch_dev(const double *d_stamps, int r, int c, int64_t N, int n_a, const double *d_x0,
                                  double g_tol, int max_iter, double *d_s, double *d_g1, double *d_g2,
                                  int32_t *d_status, int32_t *d_iters, void *stream) {
-    Ctx *ctx; TRY(get_ctx(&ctx));
-    return fit_analytic_launch(d_stamps, r, c, (long long)N, n_a, d_x0, g_tol, max_iter, d_s, d_g1, d_g2, d_status,
-                               d_iters, ctx->next_counter(), (cudaStream_t)stream);
+    return shopt_fit_profile_batch_dev(SHOPT_PROFILE_GAUSSIAN, d_stamps, r, c, N, n_a, d_x0, g_tol, max_iter, d_s, d_g1, d_g2,
+                                       d_status, d_iters, stream);
 }
 
 int shopt_fit_analytic_batch(const double *stamps, int r, int c, int64_t N, int n_a, const double *x0, double g_tol,
                              int max_iter, double *s, double *g1, double *g2, int32_t *status, int32_t *iters) {
+    return shopt_fit_profile_batch(SHOPT_PROFILE_GAUSSIAN, stamps, r, c, N, n_a, x0, g_tol, max_iter, s, g1, g2, status, iters);
+}
+int shopt_fit_profile_batch(int profile, const double *stamps, int r, int c, int64_t N, int n_a, const double *x0, double g_tol,
+                            int max_iter, double *s, double *g1, double *g2, int32_t *status, int32_t *iters) {
+    if (profile < 0 || profile > 1) return SHOPT_E_BADARG;
     if (!stamps || !x0 || !s || !g1 || !g2) return SHOPT_E_BADARG;
     if (r < 1 || c < 1 || n_a < 1 || n_a > r || n_a > c || N < 0 || max_iter < 0) return SHOPT_E_BADARG;
     Ctx *ctx; TRY(get_ctx(&ctx));
@@ -223,7 +234,7 @@ int shopt_fit_analytic_batch(const double *stamps, int r, int c, int64_t N, int 
     double *ds = dout.as<double>();
     int32_t *di = dint.as<int32_t>();
     TRY(fit_analytic_launch(dst.as<double>(), r, c, (long long)N, n_a, dx0.as<double>(), g_tol, max_iter, ds, ds + n,
-                            ds + 2 * n, di, di + n, ctx->next_counter(), st));
+                            ds + 2 * n, di, di + n, ctx->next_counter(), st, nullptr, nullptr, profile));
     SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[2], st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(s, ds, n * 8, cudaMemcpyDeviceToHost, st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(g1, ds + n, n * 8, cudaMemcpyDeviceToHost, st));
@@ -234,16 +245,25 @@ int shopt_fit_analytic_batch(const double *stamps, int r, int c, int64_t N, int 
     return finish_timing(ctx);
 }
 
-int shopt_analytic_cost_grad_batch_dev(const double *d_stamps, int r, int c, int64_t N, int n_a, const double *d_x,
-                                       double *d_f, double *d_g, void *stream) {
+int shopt_profile_cost_grad_batch_dev(int profile, const double *d_stamps, int r, int c, int64_t N, int n_a,
+                                      const double *d_x, double *d_f, double *d_g, void *stream) {
     if (!d_f || !d_g) return SHOPT_E_BADARG;
     Ctx *ctx; TRY(get_ctx(&ctx));
     return fit_analytic_launch(d_stamps, r, c, (long long)N, n_a, d_x, 0.0, 0, nullptr, nullptr, nullptr, nullptr,
-                               nullptr, ctx->next_counter(), (cudaStream_t)stream, d_f, d_g);
+                               nullptr, ctx->next_counter(), (cudaStream_t)stream, d_f, d_g, profile);
+}
+int shopt_analytic_cost_grad_batch_dev(const double *d_stamps, int r, int c, int64_t N, int n_a, const double *d_x,
+                                       double *d_f, double *d_g, void *stream) {
+    return shopt_profile_cost_grad_batch_dev(SHOPT_PROFILE_GAUSSIAN, d_stamps, r, c, N, n_a, d_x, d_f, d_g, stream);
 }
 
 int shopt_analytic_cost_grad_batch(const double *stamps, int r, int c, int64_t N, int n_a, const double *x, double *f,
                                    double *g) {
+    return shopt_profile_cost_grad_batch(SHOPT_PROFILE_GAUSSIAN, stamps, r, c, N, n_a, x, f, g);
+}
+int shopt_profile_cost_grad_batch(int profile, const double *stamps, int r, int c, int64_t N, int n_a, const double *x,
+                                  double *f, double *g) {
+    if (profile < 0 || profile > 1) return SHOPT_E_BADARG;
     if (!stamps || !x || !f || !g) return SHOPT_E_BADARG;
     if (r < 1 || c < 1 || n_a < 1 || n_a > r || n_a > c || N < 0) return SHOPT_E_BADARG;
     Ctx *ctx; TRY(get_ctx(&ctx));
@@ -256,7 +276,7 @@ int shopt_analytic_cost_grad_batch(const double *stamps, int r, int c, int64_t N
     SHOPT_CUDA_TRY(cudaMemcpyAsync(dx.p, x, n * 24, cudaMemcpyHostToDevice, st));
     double *df = dout.as<double>();
     TRY(fit_analytic_launch(dst.as<double>(), r, c, (long long)N, n_a, dx.as<double>(), 0.0, 0, nullptr, nullptr,
-                            nullptr, nullptr, nullptr, ctx->next_counter(), st, df, df + n));
+                            nullptr, nullptr, nullptr, ctx->next_counter(), st, df, df + n, profile));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(f, df, n * 8, cudaMemcpyDeviceToHost, st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(g, df + n, n * 24, cudaMemcpyDeviceToHost, st));
     SHOPT_CUDA_TRY(cudaStreamSynchronize(st));

@@ -171,6 +171,7 @@ static int stage_check_args(const shopt_params *p, const shopt_stage_io *io) {
     if (p->degree < 0 || p->degree > 8 || p->iterations < 0 || p->n_a < 1 || p->n_a > r || p->n_a > c) return SHOPT_E_BADARG;
     if (p->iterations > 16 && p->sigma_clip) return SHOPT_E_UNSUPPORTED;
     if (p->mode < SHOPT_MODE_PCA || p->mode > SHOPT_MODE_CHISQ) return SHOPT_E_BADARG;
+    if (p->profile < SHOPT_PROFILE_GAUSSIAN || p->profile > SHOPT_PROFILE_KOLMOGOROV) return SHOPT_E_BADARG;
     if (p->mode == SHOPT_MODE_CHISQ && !io->weights) return SHOPT_E_BADARG;
     if (p->mode == SHOPT_MODE_SMOOTH && p->lanczos > 7) return SHOPT_E_BADARG;
     return SHOPT_OK;
@@ -207,7 +208,7 @@ static int stage_per_star(const shopt_params *p, const shopt_stage_io *io, long 
     const double *stamps = io->stamps + first * rc;
     double *pgf = io->pgf + first * rc;
     TRY(fit_analytic_launch(stamps, r, c, count, p->n_a, io->x0_model + 3 * first, p->g_tol_model, p->max_iter, m + first,
-                            m + n + first, m + 2 * n + first, d_mst, d_mit, ctx->next_counter(), st));
+                            m + n + first, m + 2 * n + first, d_mst, d_mit, ctx->next_counter(), st, nullptr, nullptr, p->profile));
     if (p->mode == SHOPT_MODE_PCA) {
         TRY(pca_launch(stamps, r, c, count, p->pca_terms, p->pratio, p->lanczos, p->unity_sum, pgf,
                        io->pca_k ? io->pca_k + first : nullptr, d_pst, ctx->next_counter(), (double *)ctx->scratch,
@@ -224,7 +225,7 @@ static int stage_per_star(const shopt_params *p, const shopt_stage_io *io, long 
         if (io->pca_k) SHOPT_CUDA_TRY(cudaMemsetAsync(io->pca_k + first, 0, (size_t)count * 4, st));
     }
     TRY(fit_analytic_launch(pgf, r, c, count, p->n_a, io->x0_learned + 3 * first, p->g_tol_learned, p->max_iter, l + first,
-                            l + n + first, l + 2 * n + first, d_lst, d_lit, ctx->next_counter(), st));
+                            l + n + first, l + 2 * n + first, d_lst, d_lit, ctx->next_counter(), st, nullptr, nullptr, p->profile));
     return SHOPT_OK;
 }
 

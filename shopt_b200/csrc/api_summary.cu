@@ -5,8 +5,15 @@
 //   HDU 0  primary image  POLYNOMIAL_MATRIX   float64, numpy shape (r, c, K)  ->  NAXIS1 = K, NAXIS2 = c, NAXIS3 = r
 //   HDU 1  BINTABLE       SUMMARY_STATISTICS  column POLYNOMIAL_DEGREE (D), one row
 //   HDU 2  BINTABLE       ANALYTIC_PROFILE    columns s_MATRIX, g1_MATRIX, g2_MATRIX (D), ten rows: the cubic field fits
+// shopt_summary_write_full writes the seven-HDU layout of dataOutprocessing.jl:86-168 (truncate_summary_file: false):
+//   0 POLYNOMIAL_MATRIX | 1 SUMMARY_STATISTICS (13 columns, zero-padded to the longest, like astropy's from_columns)
+//   2 VIGNETS, numpy (r, c, N) -- the catalogue was stacked into array_3d first (:29-34)
+//   3 PIXEL_GRID_FITS, numpy (N, r, c) -- the py block interpolates the Vector{Matrix} `pixelGridFits`, not the stacked
+//     `pixelgridfits` of :36-40 (different spelling), so numpy stacks the matrices along a NEW FIRST axis
+//   4 VALIDATION_STARS, numpy (N_valid, r, c), same reason | 5 FLAGS (3 columns, zero-padded) | 6 ANALYTIC_PROFILE
 // FITS: 2880-byte blocks, 80-character header cards, big-endian data.  The reader locates columns by NAME in whatever
 // HDU carries them, so the reference's full (non-truncated) layout -- ANALYTIC_PROFILE is HDU 6 there -- reads too.
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -154,6 +161,51 @@ static bool read_column(const std::vector<unsigned char> &f, const std::vector<H
     return false;
 }
 
+
+// ---- the full layout ------------------------------------------------------------------------------------------
+struct FileOut {
+    FILE *fp = nullptr;
+    std::string buf;
+    bool ok = true;
+    size_t total = 0;
+    void flush() {
+        if (!buf.empty() && ok) ok = fwrite(buf.data(), 1, buf.size(), fp) == buf.size();
+        total += buf.size();
+        buf.clear();
+    }
+    void put(const std::string &x) { buf += x; if (buf.size() >= (8u << 20)) flush(); }
+    void put_f64(double x) { put_be64(buf, x); if (buf.size() >= (8u << 20)) flush(); }
+    void pad() { flush(); std::string z((2880 - total % 2880) % 2880, '\0'); put(z); flush(); }
+};
+static std::string image_header(const char *extname, bool primary, long long n1, long long n2, long long n3) {
+    std::string h;
+    if (primary) put_card(h, "SIMPLE", "T");
+    else put_card(h, "XTENSION", "IMAGE", true);
+    put_card(h, "BITPIX", "-64");
+    put_card(h, "NAXIS", "3");
+    put_card(h, "NAXIS1", std::to_string(n1));
+    put_card(h, "NAXIS2", std::to_string(n2));
+    put_card(h, "NAXIS3", std::to_string(n3));
+    if (primary) put_card(h, "EXTEND", "T");
+    else { put_card(h, "PCOUNT", "0"); put_card(h, "GCOUNT", "1"); }
+    put_card(h, "EXTNAME", extname, true);
+    end_header(h);
+    return h;
+}
+// columns of differing lengths: rows = the longest, shorter ones zero-filled (astropy FITS_rec.from_columns)
+static std::string bintable_ragged(const char *extname, const std::vector<std::pair<std::string, std::pair<const double *, long long>>> &cols) {
+    long long rows = 0;
+    for (auto &c : cols) rows = std::max(rows, c.second.second);
+    std::vector<std::vector<double>> padded(cols.size());
+    std::vector<std::pair<std::string, const double *>> flat;
+    for (size_t i = 0; i < cols.size(); i++) {
+        padded[i].assign((size_t)std::max<long long>(rows, 1), 0.0);
+        for (long long r = 0; r < cols[i].second.second; r++) padded[i][(size_t)r] = cols[i].second.first[r];
+        flat.push_back({cols[i].first, padded[i].data()});
+    }
+    return bintable(extname, flat, rows);
+}
+
 }  // namespace shopt
 
 using namespace shopt;
@@ -188,6 +240,65 @@ int shopt_summary_write(const char *path, const double *poly, int r, int c, int 
     const bool ok = fwrite(h.data(), 1, h.size(), fp) == h.size() && fwrite(d.data(), 1, d.size(), fp) == d.size() &&
                     fwrite(t1.data(), 1, t1.size(), fp) == t1.size() && fwrite(t2.data(), 1, t2.size(), fp) == t2.size();
     if (fclose(fp) != 0 || !ok) { set_last_error_text("short write on summary file"); return SHOPT_E_CUDA; }
+    return SHOPT_OK;
+}
+
+int shopt_summary_write_full(const char *path, const shopt_summary_full *f) {
+    if (!path || !f || !f->poly || !f->sC || !f->g1C || !f->g2C || f->r < 1 || f->c < 1 || f->degree < 0 || f->degree > 8)
+        return SHOPT_E_BADARG;
+    const long long N = f->n_stars, NV = f->n_valid, NT = f->n_train;
+    if (N < 0 || NV < 0 || NT < 0 || f->n_flag_snr < 0 || f->n_flag_blacklist < 0 || f->n_flag_failed < 0) return SHOPT_E_BADARG;
+    if (N > 0 && (!f->u || !f->v || !f->s_model || !f->g1_model || !f->g2_model || !f->s_data || !f->g1_data || !f->g2_data ||
+                  !f->stars || !f->pgf)) return SHOPT_E_BADARG;
+    if (NT > 0 && (!f->train_u || !f->train_v)) return SHOPT_E_BADARG;
+    if (NV > 0 && (!f->valid_u || !f->valid_v || !f->valid_stars)) return SHOPT_E_BADARG;
+    if ((f->n_flag_snr && !f->flag_snr) || (f->n_flag_blacklist && !f->flag_blacklist) || (f->n_flag_failed && !f->flag_failed))
+        return SHOPT_E_BADARG;
+    const int r = f->r, c = f->c, K = (f->degree + 1) * (f->degree + 2) / 2;
+    const size_t rc = (size_t)r * c;
+    FileOut out;
+    out.fp = fopen(path, "wb");
+    if (!out.fp) { set_last_error_text("cannot open summary file for writing"); return SHOPT_E_BADARG; }
+    // HDU 0: numpy (r, c, K), K fastest
+    out.put(image_header("POLYNOMIAL_MATRIX", true, K, c, r));
+    for (int a = 0; a < r; a++)
+        for (int b = 0; b < c; b++)
+            for (int k = 0; k < K; k++) out.put_f64(f->poly[(size_t)a + (size_t)b * r + (size_t)k * rc]);
+    out.pad();
+    // HDU 1
+    const double deg = (double)f->degree;
+    out.put(bintable_ragged("SUMMARY_STATISTICS", {
+        {"U_COORDINATES", {f->u, N}}, {"V_COORDINATES", {f->v, N}}, {"TRAINING_U_COORDS", {f->train_u, NT}},
+        {"TRAINING_V_COORDS", {f->train_v, NT}}, {"VALIDATION_U_COORDS", {f->valid_u, NV}},
+        {"VALIDATION_V_COORDS", {f->valid_v, NV}}, {"S_MODEL", {f->s_model, N}}, {"g1_MODEL", {f->g1_model, N}},
+        {"g2_MODEL", {f->g2_model, N}}, {"s_DATA", {f->s_data, N}}, {"g1_DATA", {f->g1_data, N}}, {"g2_DATA", {f->g2_data, N}},
+        {"POLYNOMIAL_DEGREE", {&deg, 1}}}));
+    out.pad();
+    // HDU 2: VIGNETS numpy (r, c, N): star index fastest
+    out.put(image_header("VIGNETS", false, N, c, r));
+    for (int a = 0; a < r; a++)
+        for (int b = 0; b < c; b++)
+            for (long long i = 0; i < N; i++) out.put_f64(f->stars[(size_t)a + (size_t)b * r + (size_t)i * rc]);
+    out.pad();
+    // HDU 3 / 4: numpy (N, r, c): column index fastest
+    for (int which = 0; which < 2; which++) {
+        const long long n = which ? NV : N;
+        const double *cube = which ? f->valid_stars : f->pgf;
+        out.put(image_header(which ? "VALIDATION_STARS" : "PIXEL_GRID_FITS", false, c, r, n));
+        for (long long i = 0; i < n; i++)
+            for (int a = 0; a < r; a++)
+                for (int b = 0; b < c; b++) out.put_f64(cube[(size_t)a + (size_t)b * r + (size_t)i * rc]);
+        out.pad();
+    }
+    // HDU 5, 6
+    out.put(bintable_ragged("FLAGS", {{"FLAG_SNR", {f->flag_snr, f->n_flag_snr}},
+                                      {"FLAG_S_BLACKLIST_MODEL", {f->flag_blacklist, f->n_flag_blacklist}},
+                                      {"FLAG_PIXEL_GRID_OR_S_BLACKLIST_LEARNED", {f->flag_failed, f->n_flag_failed}}}));
+    out.pad();
+    out.put(bintable("ANALYTIC_PROFILE", {{"s_MATRIX", f->sC}, {"g1_MATRIX", f->g1C}, {"g2_MATRIX", f->g2C}}, 10));
+    out.pad();
+    const bool ok = out.ok;
+    if (fclose(out.fp) != 0 || !ok) { set_last_error_text("short write on summary file"); return SHOPT_E_CUDA; }
     return SHOPT_OK;
 }
 

@@ -9,7 +9,8 @@ namespace shopt {
 int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n_a, const double *d_x0, double g_tol,
                         int max_iter, double *d_s, double *d_g1, double *d_g2, int *d_status, int *d_iters,
                         unsigned long long *d_counter, cudaStream_t stream, double *d_f = nullptr,
-                        double *d_g = nullptr);   // d_f/d_g non-null: evaluate cost and gradient at x0 only
+                        double *d_g = nullptr,    // d_f/d_g non-null: evaluate cost and gradient at x0 only
+                        int profile = 0);         // SHOPT_PROFILE_*
 
 // polyfit.cu  (rc = r*c; scratch: polyfit_scratch_bytes(rc, n, degree))
 // A list of stars: idx may be null = stars 0..n-1.  When n_dev is set the ACTUAL length lives on the device and n is

@@ -240,6 +240,7 @@ struct EvalShared {
     uint32_t tab_s;                    // ... and the exp table
     int n_a, pitch, TV, m0, rodd, plane, have_last, cmd;
     int newstar, parity;               // first evaluation of a star: the workers look at the crop's mbarrier phase too
+    int profile;                       // SHOPT_PROFILE_GAUSSIAN / _KOLMOGOROV
 };
 struct FG {
     double f, g0, g1, g2;
@@ -292,6 +293,85 @@ __device__ __forceinline__ double warp_reduce5(double v0, double v1, double v2, 
     k += __shfl_xor_sync(0xffffffffu, k, 2);
     k += __shfl_xor_sync(0xffffffffu, k, 1);
     return k;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kolmogorov profile (radialProfiles.jl:11-24).  Fkolmogorov(k, 1) as written is exp(-C k) with
+// C = (24 gamma(6.5) 0.2)^(5/6) / (2 pi)^(5/3), so fkolmogorov's Hankel transform has the closed form
+//     f(x) = (1 / 2 pi) C / (C^2 + x)^(3/2),   x = squareRadius = kappa q        (no quadrature)
+// and -df/dx = h(x) = 1.5 f / (C^2 + x).  With f replaced by h in the DERIVATIVE sums (d f / d eta = -h d x / d eta where
+// the Gaussian has -f d x / d eta) the master's chain rule is unchanged: pass A delivers sum f and the du^2, du dv, dv^2
+// moments of h, pass B delivers the cost, sum rho f and the three moments of rho h, in the slots the Gaussian passes use.
+// The reference never calls this profile (dead code), so it is a plain two-pass loop: no plane, no unrolling.
+// ---------------------------------------------------------------------------------------------
+constexpr double KOLMO_C2 = 374.54292214306446;    // C^2, C = 19.353111433127864
+constexpr double KOLMO_CN = 3.0801433487905743;    // C / (2 pi)
+template <int THREADS>
+__device__ __noinline__ void eval_pixels_kolmogorov(int slot) {
+    constexpr int NWARPS = THREADS / 32;
+    EvalShared &es = eval_shared<THREADS>(slot);
+    double *scrA = eval_scratch<THREADS>(slot);
+    double *scrB = scrA + NWARPS * 4;
+    const double *s = es.sc;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_a = es.n_a, pitch = es.pitch, TV = es.TV, m0 = es.m0, rodd = es.rodd;
+    const uint32_t crop_s = es.crop_s;
+    const int tv = threadIdx.x / n_a, tu = threadIdx.x - tv * n_a;
+    const bool active = tv < TV;
+    const double du = (double)(tu + 1) - n_a / 2.0;
+    const double dv0 = (double)(tv + 1) - n_a / 2.0;
+    const double A11 = s[0], A22 = s[1], G2 = s[2], MS = s[3];
+    const double qa = A11 * A11 + G2 * G2, qb = 2.0 * (G2 * (A11 + A22)), qc = G2 * G2 + A22 * A22;
+    const double c0 = (MS * qa) * (du * du), c1 = (MS * qb) * du, cc = MS * qc;
+    const double step = (double)TV;
+    double S0 = 0.0, H0 = 0.0, H1 = 0.0, H2 = 0.0;
+    if (active) {
+        double dv = dv0;
+        for (int v = tv; v < n_a; v += TV) {
+            const double t = KOLMO_C2 + fma(dv, fma(cc, dv, c1), c0);
+            const double f = KOLMO_CN / (t * sqrt(t)), h = 1.5 * (f / t), hd = h * dv;
+            S0 += f;
+            H0 += h;
+            H1 += hd;
+            H2 = fma(hd, dv, H2);
+            dv += step;
+        }
+    }
+    {
+        const double k = warp_reduce4(S0, (du * du) * H0, du * H1, H2);
+        if ((lane & 7) == 0) scrA[warp * 4 + (lane >> 3)] = k;
+    }
+    bar_eval<THREADS>(slot);
+    double sumf = scrA[0];
+#pragma unroll
+    for (int w = 1; w < NWARPS; w++) sumf += scrA[w * 4];
+    const double A = 1.0 / sumf;
+    double R0 = 0.0, P0 = 0.0, Q0 = 0.0, Q1 = 0.0, Q2 = 0.0;
+    if (active) {
+        double dv = dv0;
+        for (int v = tv; v < n_a; v += TV) {
+            const uint32_t o = (uint32_t)((v * pitch + ((m0 + v * rodd) & 1) + tu) * 8);
+            const double d = lds_f64(crop_s + o);
+            if (!isnan(d)) {
+                const double t = KOLMO_C2 + fma(dv, fma(cc, dv, c1), c0);
+                const double f = KOLMO_CN / (t * sqrt(t)), h = 1.5 * (f / t);
+                const double rho = fma(A, f, -d);
+                const double th = rho * h, td = th * dv;
+                R0 = fma(rho, rho, R0);
+                P0 = fma(rho, f, P0);
+                Q0 += th;
+                Q1 += td;
+                Q2 = fma(td, dv, Q2);
+            }
+            dv += step;
+        }
+    }
+    {
+        const double k = warp_reduce5(P0, (du * du) * Q0, du * Q1, Q2, 0.5 * R0);
+        if ((lane & 7) == 0) scrB[warp * 5 + 1 + (lane >> 3)] = k;
+        else if (lane == 4) scrB[warp * 5] = k;
+    }
+    bar_eval<THREADS>(slot);
 }
 
 // The pixel passes of one evaluation, executed by the worker warps between the evaluation's first barrier (value block
@@ -512,7 +592,8 @@ __device__ __forceinline__ void worker_loop(uint64_t *bars) {
         const int cmd = *reinterpret_cast<volatile int *>(&es.cmd);
         if (cmd == CMD_EXIT) { alive &= ~(1 << k); continue; }
         if (es.newstar) mbar_wait(&bars[k], (uint32_t)es.parity);   // the crop's bulk copies, observed by this thread too
-        eval_pixels<THREADS>(k);
+        if (es.profile) eval_pixels_kolmogorov<THREADS>(k);
+        else eval_pixels<THREADS>(k);
     }
 }
 
@@ -846,6 +927,7 @@ struct FitArgs {
     unsigned long long *counter;   // device work counter, zeroed before launch
     int nbuf, pitch, plane;
     double *f_out, *g_out;         // non-null: evaluate cost / gradient at x0 only (cost, g! of analyticLBFGS.jl)
+    int profile;                   // 0: fGaussian (radialProfiles.jl:5-9), 1: fkolmogorov (:16-24)
 };
 
 // Issue the bulk copies of one star's crop (thread 0 only).  A column whose 16-byte-aligned superset would
@@ -932,7 +1014,7 @@ __global__ void __launch_bounds__(THREADS + 32 * NSLOT, MINB) fit_kernel(const F
             es.crop_s = smem_u32(crop); es.fbuf_s = smem_u32(fplane); es.tab_s = smem_u32(exp_tab);
             es.n_a = a.n_a; es.pitch = a.pitch; es.TV = THREADS / a.n_a;      // n_a <= THREADS (checked at launch)
             es.m0 = (int)((base + mis0) & 1); es.rodd = a.r & 1; es.plane = a.plane;
-            es.have_last = 0; es.cmd = 0; es.newstar = 1; es.parity = (int)phase;
+            es.have_last = 0; es.cmd = 0; es.newstar = 1; es.parity = (int)phase; es.profile = a.profile;
         }
         mbar_wait(&bars[slot], phase);
         phase ^= 1u;
@@ -1015,15 +1097,15 @@ static int launch_fit(FitArgs a, cudaStream_t stream) {
 
 int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n_a, const double *d_x0, double g_tol,
                         int max_iter, double *d_s, double *d_g1, double *d_g2, int *d_status, int *d_iters,
-                        unsigned long long *d_counter, cudaStream_t stream, double *d_f, double *d_g) {
-    if (!d_stamps || !d_x0 || !d_counter) return SHOPT_E_BADARG;
+                        unsigned long long *d_counter, cudaStream_t stream, double *d_f, double *d_g, int profile) {
+    if (!d_stamps || !d_x0 || !d_counter || profile < 0 || profile > 1) return SHOPT_E_BADARG;
     if (d_f ? !d_g : (!d_s || !d_g1 || !d_g2)) return SHOPT_E_BADARG;
     if (r < 1 || c < 1 || n_a < 1 || n_a > r || n_a > c || N < 0 || max_iter < 0) return SHOPT_E_BADARG;
     if (N == 0) return SHOPT_OK;
     FitArgs a;
     a.stamps = d_stamps; a.r = r; a.c = c; a.n_a = n_a; a.N = N; a.x0 = d_x0; a.g_tol = g_tol; a.max_iter = max_iter;
     a.s = d_s; a.g1 = d_g1; a.g2 = d_g2; a.status = d_status; a.iters = d_iters; a.counter = d_counter;
-    a.nbuf = 2; a.pitch = 0; a.plane = 1; a.f_out = d_f; a.g_out = d_g;
+    a.nbuf = 2; a.pitch = 0; a.plane = 1; a.f_out = d_f; a.g_out = d_g; a.profile = profile;
     if (n_a <= 32) return launch_fit<128, 4, 6>(a, stream);
     if (n_a <= 80) return launch_fit<256, 2, 3>(a, stream);
     if (n_a <= 160) return launch_fit<512, 1, 1>(a, stream);

@@ -49,7 +49,7 @@ struct PcaArgs {
 };
 
 // SHOPT_PCA_DEBUG bit 16: cycles per phase of pca_kernel, summed over the stars (thread 0 of every CTA), printed by pca_launch
-__device__ unsigned long long g_pca_phase[16];
+static __device__ unsigned long long g_pca_phase[16];   // one copy per translation unit (see SHOPT_PCA_RT below)
 
 __device__ __forceinline__ double nan_to_zero(double x) { return isnan(x) ? 0.001 : x; }   // masks.jl:43
 
@@ -294,7 +294,7 @@ __device__ void cholqr(const double *Qsrc, double *Qdst, int r, int ldq, double 
 // cumulative variance is below pratio of the total, so a kept component carries at least (1 - pratio) total / min(r,c);
 // with cut an eighth of that, the principal block of the "small" indices has trace < 7 cut and cannot hide a component
 // that would be kept, and the sum of the Ritz values (all that is used of the small ones) is rotation-invariant.  Gt: lower triangle, e = i(i+1)/2 + j;  Vout[a * 8 + b] = V_ab.
-__device__ void eig8_warp(const double *Gt, double *Vout, double cut) {
+static __device__ void eig8_warp(const double *Gt, double *Vout, double cut) {
     const int lane = threadIdx.x & 31, i = lane & 7;
     double a[FB], v[FB], dg;
 #pragma unroll
@@ -1037,6 +1037,7 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
     }
 }
 
+#ifndef SHOPT_PCA_RT   // the non-template kernels and their launchers live in the main translation unit only
 // ---------------------------------------------------------------------------------------------
 // smooth(data, a) alone (dataPreprocessing.jl:112-139); mode "smooth" applies it to nanToZero(star) (shopt.jl:316-348).
 // One CTA per star; taps come straight from global memory (the 8 r c bytes of a stamp stay in L1/L2).
@@ -1162,6 +1163,8 @@ int elem_pgf_launch(const double *d_in, const double *d_w, const double *d_x0, d
     return SHOPT_OK;
 }
 
+#endif  // !SHOPT_PCA_RT
+
 // dataPreprocessing.jl:94-110: a*sinc(pi x)*sinc(pi x / a) at integer offsets, outer product, normalised by the sum
 static void lanczos_kernel2d(int a, double *kernel, double *kz = nullptr) {
     const int w = 2 * a + 1;
@@ -1184,6 +1187,7 @@ static size_t pca_w_doubles(int r, int c, int kmax) {      // W plus the region 
     const size_t y = (size_t)kmax * c, f = (size_t)2 * FB * ((r + 1) & ~1) + (size_t)FB * c + 192;
     return (size_t)r * c + (y > f ? y : f);
 }
+#ifndef SHOPT_PCA_RT
 size_t pca_scratch_bytes(int r, int c, int ncomp) {
     int kmax = ncomp < r ? ncomp : r; if (c < kmax) kmax = c; if (kmax < 1) kmax = 1;
     const size_t wdoubles = pca_w_doubles(r, c, kmax);
@@ -1191,6 +1195,7 @@ size_t pca_scratch_bytes(int r, int c, int ncomp) {
         return (r <= c && r >= 16) ? (size_t)sm_count() * 2 * r * r * 8 : 0;       // direct path: Gram matrix + reflectors
     return (size_t)sm_count() * wdoubles * 8;
 }
+#endif
 
 template <int NW, int RT>
 static int pca_launch_t(PcaArgs a, double *scratch, size_t scratch_bytes, cudaStream_t st) {
@@ -1246,6 +1251,25 @@ static int pca_launch_nw(const PcaArgs &a, double *scratch, size_t scratch_bytes
     return pca_launch_t<16, RT>(a, scratch, scratch_bytes, st);
 }
 
+// pca_kernel has ~20 instantiations (7 row-tile counts RT x up to 3 warp counts x 2 buffer placements), minutes of
+// compile time each time this file changes.  The Makefile therefore compiles this file once per RT with -DSHOPT_PCA_RT=<RT>
+// (objects pixelgrid_rt<RT>.o, built in parallel): such a translation unit emits only pca_launch_rt<RT>, the main one
+// (no macro) everything else and no pca_kernel at all.
+#ifdef SHOPT_PCA_RT
+#define SHOPT_PCA_RT_FN2(rt) pca_launch_rt##rt
+#define SHOPT_PCA_RT_FN(rt) SHOPT_PCA_RT_FN2(rt)
+int SHOPT_PCA_RT_FN(SHOPT_PCA_RT)(const PcaArgs &a, double *scratch, size_t scratch_bytes, cudaStream_t st) {
+    return pca_launch_nw<SHOPT_PCA_RT>(a, scratch, scratch_bytes, st);
+}
+#else
+int pca_launch_rt1(const PcaArgs &a, double *scratch, size_t scratch_bytes, cudaStream_t st);
+int pca_launch_rt2(const PcaArgs &a, double *scratch, size_t scratch_bytes, cudaStream_t st);
+int pca_launch_rt3(const PcaArgs &a, double *scratch, size_t scratch_bytes, cudaStream_t st);
+int pca_launch_rt4(const PcaArgs &a, double *scratch, size_t scratch_bytes, cudaStream_t st);
+int pca_launch_rt5(const PcaArgs &a, double *scratch, size_t scratch_bytes, cudaStream_t st);
+int pca_launch_rt7(const PcaArgs &a, double *scratch, size_t scratch_bytes, cudaStream_t st);
+int pca_launch_rt10(const PcaArgs &a, double *scratch, size_t scratch_bytes, cudaStream_t st);
+
 int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, double pratio, int lanczos_a, int unity_sum,
                double *d_pgf, int *d_k, int *d_status, unsigned long long *d_counter, double *scratch,
                size_t scratch_bytes, cudaStream_t st) {
@@ -1263,13 +1287,13 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
     if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern, a.kz);
     const int rt = ((r > c ? r : c) + 31) / 32;
     switch (rt) {
-        case 1: return pca_launch_nw<1>(a, scratch, scratch_bytes, st);
-        case 2: return pca_launch_nw<2>(a, scratch, scratch_bytes, st);
-        case 3: return pca_launch_nw<3>(a, scratch, scratch_bytes, st);
-        case 4: return pca_launch_nw<4>(a, scratch, scratch_bytes, st);
-        case 5: return pca_launch_nw<5>(a, scratch, scratch_bytes, st);
-        case 6: case 7: return pca_launch_nw<7>(a, scratch, scratch_bytes, st);
-        default: return pca_launch_nw<10>(a, scratch, scratch_bytes, st);
+        case 1: return pca_launch_rt1(a, scratch, scratch_bytes, st);
+        case 2: return pca_launch_rt2(a, scratch, scratch_bytes, st);
+        case 3: return pca_launch_rt3(a, scratch, scratch_bytes, st);
+        case 4: return pca_launch_rt4(a, scratch, scratch_bytes, st);
+        case 5: return pca_launch_rt5(a, scratch, scratch_bytes, st);
+        case 6: case 7: return pca_launch_rt7(a, scratch, scratch_bytes, st);
+        default: return pca_launch_rt10(a, scratch, scratch_bytes, st);
     }
 }
 
@@ -1296,5 +1320,6 @@ int smooth_launch(const double *d_in, int r, int c, long long N, int lanczos_a, 
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
 }
+#endif  // SHOPT_PCA_RT
 
 }  // namespace shopt

@@ -42,8 +42,9 @@ def _dev_check(t, dtype):
 # ------------------------------------------------------------------------------------------------
 # (1) analytic profile fit: shopt.jl:130-164 (model stars) / :357-397 (learned stars)
 # ------------------------------------------------------------------------------------------------
-def fit_analytic_batch(stamps, n_a, x0, g_tol=1e-6, max_iter=1000):
+def fit_analytic_batch(stamps, n_a, x0, g_tol=1e-6, max_iter=1000, profile=0):
     """Optim.optimize(cost, g!, x0, LBFGS(), Options(g_tol)) for every star of the batch.
+    profile: 0 = fGaussian (what the reference's cost calls), 1 = fkolmogorov (radialProfiles.jl:11-24, closed form).
 
     stamps (N, c, r); x0 (N, 3) start points [sigma, e1, e2] (the reference draws rand(3), shopt.jl:134).
     Returns s, g1, g2, status, iters.  Failed stars (status == FIT_THREW) carry s = g1 = g2 = 0 like the
@@ -59,7 +60,7 @@ def fit_analytic_batch(stamps, n_a, x0, g_tol=1e-6, max_iter=1000):
         g2 = torch.empty_like(s)
         status = torch.empty(N, dtype=torch.int32, device=dev)
         iters = torch.empty_like(status)
-        check(L.shopt_fit_analytic_batch_dev(_dev_check(stamps, torch.float64), r, c, N, n_a,
+        check(L.shopt_fit_profile_batch_dev(profile, _dev_check(stamps, torch.float64), r, c, N, n_a,
                                              _dev_check(x0, torch.float64), g_tol, max_iter,
                                              _dev_check(s, torch.float64), _dev_check(g1, torch.float64),
                                              _dev_check(g2, torch.float64), _dev_check(status, torch.int32),
@@ -71,19 +72,24 @@ def fit_analytic_batch(stamps, n_a, x0, g_tol=1e-6, max_iter=1000):
     assert x0.shape == (N, 3)
     s, g1, g2 = np.zeros(N), np.zeros(N), np.zeros(N)
     status, iters = np.zeros(N, np.int32), np.zeros(N, np.int32)
-    check(L.shopt_fit_analytic_batch(_ptr(stamps), r, c, N, n_a, _ptr(x0), g_tol, max_iter, _ptr(s), _ptr(g1),
-                                     _ptr(g2), _ptr(status, ip), _ptr(iters, ip)))
+    fit = L.shopt_fit_profile_batch if profile else L.shopt_fit_analytic_batch      # both spellings stay exercised
+    args = (_ptr(stamps), r, c, N, n_a, _ptr(x0), g_tol, max_iter, _ptr(s), _ptr(g1), _ptr(g2), _ptr(status, ip),
+            _ptr(iters, ip))
+    check(fit(profile, *args) if profile else fit(*args))
     return s, g1, g2, status, iters
 
 
-def analytic_cost_grad_batch(stamps, n_a, x):
+def analytic_cost_grad_batch(stamps, n_a, x, profile=0):
     """cost(x_i) and g!(., x_i) of analyticLBFGS.jl:8-46, 89-94 for every star i; host arrays. Returns f (N), g (N,3)."""
     stamps = _f64(stamps)
     x = _f64(x)
     N, c, r = stamps.shape
     assert x.shape == (N, 3)
     f, g = np.zeros(N), np.zeros((N, 3))
-    check(_lib.lib().shopt_analytic_cost_grad_batch(_ptr(stamps), r, c, N, n_a, _ptr(x), _ptr(f), _ptr(g)))
+    if profile:
+        check(_lib.lib().shopt_profile_cost_grad_batch(profile, _ptr(stamps), r, c, N, n_a, _ptr(x), _ptr(f), _ptr(g)))
+    else:
+        check(_lib.lib().shopt_analytic_cost_grad_batch(_ptr(stamps), r, c, N, n_a, _ptr(x), _ptr(f), _ptr(g)))
     return f, g
 
 
@@ -269,6 +275,35 @@ def write_summary(path, poly, degree, field):
     K, c, r = poly.shape
     check(_lib.lib().shopt_summary_write(str(path).encode(), _ptr(poly), r, c, degree, _ptr(field[0]), _ptr(field[1]),
                                          _ptr(field[2])))
+
+
+def write_summary_full(path, poly, degree, field, u, v, model, learned, stars, pgf, train_u, train_v, valid_stars, valid_u,
+                       valid_v, flag_snr=(), flag_blacklist=(), flag_failed=()):
+    """The untruncated summary.shopt (dataOutprocessing.jl:86-168).  poly (K, c, r); field (3, 10); model / learned (3, n)
+    = s, g1, g2 per star; stars / pgf (n, c, r); valid_stars (n_valid, c, r); flags: 1-based star numbers."""
+    import ctypes as C
+    keep = []
+
+    def arr(a):
+        a = np.ascontiguousarray(np.asarray(a, dtype=np.float64))
+        keep.append(a)
+        return _ptr(a) if a.size else None
+    poly, field, model, learned = _f64(poly), _f64(field), _f64(model), _f64(learned)
+    stars, pgf, valid_stars = _f64(stars), _f64(pgf), _f64(valid_stars)
+    K, c, r = poly.shape
+    f = _lib.SummaryFull()
+    f.poly, f.r, f.c, f.degree = _ptr(poly), r, c, degree
+    f.sC, f.g1C, f.g2C = _ptr(field[0]), _ptr(field[1]), _ptr(field[2])
+    f.n_stars = stars.shape[0]
+    f.u, f.v = arr(u), arr(v)
+    f.s_model, f.g1_model, f.g2_model = arr(model[0]), arr(model[1]), arr(model[2])
+    f.s_data, f.g1_data, f.g2_data = arr(learned[0]), arr(learned[1]), arr(learned[2])
+    f.stars, f.pgf = arr(stars), arr(pgf)
+    f.n_train, f.train_u, f.train_v = len(train_u), arr(train_u), arr(train_v)
+    f.n_valid, f.valid_u, f.valid_v, f.valid_stars = valid_stars.shape[0], arr(valid_u), arr(valid_v), arr(valid_stars)
+    f.n_flag_snr, f.n_flag_blacklist, f.n_flag_failed = len(flag_snr), len(flag_blacklist), len(flag_failed)
+    f.flag_snr, f.flag_blacklist, f.flag_failed = arr(flag_snr), arr(flag_blacklist), arr(flag_failed)
+    check(_lib.lib().shopt_summary_write_full(str(path).encode(), C.byref(f)))
 
 
 def read_summary(path):

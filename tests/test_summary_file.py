@@ -114,6 +114,63 @@ def test_reads_the_full_untruncated_layout(stage, tmp_path):
     assert deg == degree and np.array_equal(poly, cube.transpose(2, 1, 0)) and np.array_equal(got_field, field)
 
 
+def test_full_layout_writer(stage, tmp_path):
+    """shopt_summary_write_full against dataOutprocessing.jl:86-168 read through the independent parser: HDU order and
+    names, the ragged zero-padded tables, and the axis order of each cube (VIGNETS is the stacked (r, c, N) array,
+    PIXEL_GRID_FITS / VALIDATION_STARS are numpy stacks (N, r, c) of the Julia matrices)."""
+    rng = np.random.default_rng(5)
+    degree, r, c, n, nv, nt = 2, 5, 4, 9, 3, 6
+    K = 6
+    poly = rng.normal(size=(K, c, r))
+    field = rng.normal(size=(3, 10))
+    u, v = rng.normal(size=n), rng.normal(size=n)
+    model, learned = rng.normal(size=(3, n)), rng.normal(size=(3, n))
+    stars, pgf, vstars = rng.normal(size=(n, c, r)), rng.normal(size=(n, c, r)), rng.normal(size=(nv, c, r))
+    tu, tv, vu, vv = rng.normal(size=nt), rng.normal(size=nt), rng.normal(size=nv), rng.normal(size=nv)
+    path = tmp_path / "full.shopt"
+    stage.write_summary_full(path, poly, degree, field, u, v, model, learned, stars, pgf, tu, tv, vstars, vu, vv,
+                             flag_snr=[3.0, 8.0, 11.0], flag_blacklist=[2.0], flag_failed=[])
+    hdus = parse_fits(path)
+    assert [h["EXTNAME"] for h, _ in hdus] == ["POLYNOMIAL_MATRIX", "SUMMARY_STATISTICS", "VIGNETS", "PIXEL_GRID_FITS",
+                                               "VALIDATION_STARS", "FLAGS", "ANALYTIC_PROFILE"]
+    assert [h.get("XTENSION", "PRIMARY") for h, _ in hdus] == ["PRIMARY", "BINTABLE", "IMAGE", "IMAGE", "IMAGE", "BINTABLE",
+                                                                "BINTABLE"]
+    h0, d0 = hdus[0]
+    assert np.array_equal(np.frombuffer(d0, dtype=">f8").reshape(r, c, K), poly.transpose(2, 1, 0))
+    h1, d1 = hdus[1]
+    names = ["U_COORDINATES", "V_COORDINATES", "TRAINING_U_COORDS", "TRAINING_V_COORDS", "VALIDATION_U_COORDS",
+             "VALIDATION_V_COORDS", "S_MODEL", "g1_MODEL", "g2_MODEL", "s_DATA", "g1_DATA", "g2_DATA", "POLYNOMIAL_DEGREE"]
+    assert [h1["TTYPE%d" % (i + 1)] for i in range(13)] == names and int(h1["NAXIS2"]) == n and int(h1["NAXIS1"]) == 104
+    tab = np.frombuffer(d1, dtype=">f8").reshape(n, 13)
+    pad = lambda a: np.concatenate([a, np.zeros(n - len(a))])
+    want = [u, v, tu, tv, vu, vv, model[0], model[1], model[2], learned[0], learned[1], learned[2], np.array([float(degree)])]
+    for j, w in enumerate(want):
+        assert np.array_equal(tab[:, j], pad(w)), names[j]
+    # numpy shapes as astropy would report them (reversed NAXISn)
+    shape = lambda h: tuple(int(h["NAXIS%d" % a]) for a in (3, 2, 1))
+    assert shape(hdus[2][0]) == (r, c, n) and shape(hdus[3][0]) == (n, r, c) and shape(hdus[4][0]) == (nv, r, c)
+    vig = np.frombuffer(hdus[2][1], dtype=">f8").reshape(r, c, n)
+    assert np.array_equal(vig, stars.transpose(2, 1, 0))                   # starCatalog[a, b, i]
+    pg = np.frombuffer(hdus[3][1], dtype=">f8").reshape(n, r, c)
+    assert np.array_equal(pg, pgf.transpose(0, 2, 1))                      # pixelGridFits[i][a, b]
+    va = np.frombuffer(hdus[4][1], dtype=">f8").reshape(nv, r, c)
+    assert np.array_equal(va, vstars.transpose(0, 2, 1))
+    h5, d5 = hdus[5]
+    assert [h5["TTYPE%d" % i] for i in (1, 2, 3)] == ["FLAG_SNR", "FLAG_S_BLACKLIST_MODEL",
+                                                      "FLAG_PIXEL_GRID_OR_S_BLACKLIST_LEARNED"]
+    fl = np.frombuffer(d5, dtype=">f8").reshape(3, 3)
+    assert np.array_equal(fl, np.array([[3.0, 2.0, 0.0], [8.0, 0.0, 0.0], [11.0, 0.0, 0.0]]))
+    h6, d6 = hdus[6]
+    assert np.array_equal(np.frombuffer(d6, dtype=">f8").reshape(10, 3).T, field)
+    # and the library's reader takes the file back (read_shopt: f[0], f[1]['POLYNOMIAL_DEGREE'][0], f[6])
+    got_poly, got_deg, got_field = stage.read_summary(path)
+    assert got_deg == degree and np.array_equal(got_poly, poly) and np.array_equal(got_field, field)
+    # an empty catalogue still writes a well-formed file
+    stage.write_summary_full(tmp_path / "empty.shopt", poly, degree, field, [], [], np.zeros((3, 0)), np.zeros((3, 0)),
+                             np.zeros((0, c, r)), np.zeros((0, c, r)), [], [], np.zeros((0, c, r)), [], [])
+    assert len(parse_fits(tmp_path / "empty.shopt")) == 7
+
+
 def test_bad_files_are_refused(stage, tmp_path):
     import pytest
     from shopt_b200 import _lib

@@ -38,7 +38,10 @@ def num(x):
 def main():
     rep, config = sys.argv[1], sys.argv[2]
     label = sys.argv[3] if len(sys.argv) > 3 else os.path.basename(rep)
-    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    if rep.endswith(".csv"):      # already exported on the GPU box (`ncu -i X.ncu-rep --page raw --csv`): the report
+        txt = open(rep).read()    # itself is too large to travel back
+    else:
+        txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
     rows = list(csv.reader(txt.splitlines()))
     head, units, body = rows[0], rows[1], rows[2:]
     col = {k: (head.index(v) if v in head else None) for k, v in COLS.items()}
