@@ -42,99 +42,8 @@ __device__ void gram_rows(const double *Z, int r, int c, double *Cg) {
     }
 }
 
-// Householder reduction of the symmetric A (n x n, ld n, full storage, shared memory) to tridiagonal (d, e).  Reflector
-// k is H_k = I - tau[k] u u' with u stored in Hg[k+1.., k] (global); A = H_0 ... H_{n-3} T H_{n-3} ... H_0.
-// u, q: n doubles each, pp: NP n doubles (shared scratch).  n <= NW*32.
-template <int NW, int RT>
-__device__ void tridiagonalise(double *A, int n, double *d, double *e, double *tau, double *u, double *q, double *pp,
-                               double *Hg) {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
-    int NP = nthr / n;
-    if (NP > 8) NP = 8;
-    const int prow = tid % n, ppart = tid / n;
-    for (int k = 0; k < n - 2; k++) {
-        const int m0 = k + 1, len = n - m0;
-        const double *xk = A + (size_t)k * n;
-        if (warp == 0) {
-            double ss = 0.0;
-            for (int i = m0 + 1 + lane; i < n; i += 32) ss = fma(xk[i], xk[i], ss);
-            ss = warp_sum_all(ss);
-            const double x0 = xk[m0];
-            double alpha = x0, beta = 0.0, u0 = 0.0;
-            if (ss > DBL_MIN) {
-                const double nrm = sqrt(fma(x0, x0, ss));
-                alpha = x0 > 0.0 ? -nrm : nrm;
-                u0 = x0 - alpha;
-                beta = 2.0 / fma(u0, u0, ss);
-            }
-            for (int i = lane; i < n; i += 32) u[i] = (i < m0 || beta == 0.0) ? 0.0 : (i == m0 ? u0 : xk[i]);
-            if (lane == 0) { d[k] = xk[k]; e[k] = alpha; tau[k] = beta; }
-        }
-        __syncthreads();
-        const double beta = tau[k];
-        if (beta != 0.0) {                                       // uniform over the CTA
-            if (ppart < NP && prow >= m0) {                      // partial products of A22 u
-                const int seg = (len + NP - 1) / NP, j0 = m0 + ppart * seg, j1 = j0 + seg < n ? j0 + seg : n;
-                double s = 0.0;
-                for (int j = j0; j < j1; j++) s = fma(A[prow + (size_t)j * n], u[j], s);
-                pp[ppart * n + prow] = s;
-            }
-            __syncthreads();
-            if (warp == 0) {                                     // p = beta A22 u,  q = p - (beta u'p / 2) u
-                double pv[RT];
-                double up = 0.0;
-#pragma unroll
-                for (int t = 0; t < RT; t++) {
-                    const int i = lane + 32 * t;
-                    pv[t] = 0.0;
-                    if (i >= m0 && i < n) {
-                        double x[8];                             // NP <= 8 partial sums, loaded together
-#pragma unroll
-                        for (int part = 0; part < 8; part++) x[part] = part < NP ? pp[part * n + i] : 0.0;
-                        const double s = ((x[0] + x[1]) + (x[2] + x[3])) + ((x[4] + x[5]) + (x[6] + x[7]));
-                        pv[t] = beta * s;
-                        up = fma(u[i], pv[t], up);
-                    }
-                }
-                up = warp_sum_all(up);
-                const double K = 0.5 * beta * up;
-#pragma unroll
-                for (int t = 0; t < RT; t++) {
-                    const int i = lane + 32 * t;
-                    if (i < n) q[i] = (i >= m0) ? pv[t] - K * u[i] : 0.0;
-                }
-            }
-            __syncthreads();
-            {                                                    // A22 -= u q' + q u'   (both triangles)
-                const int row = tid % len, col0 = tid / len, cstep = nthr / len;
-                if (col0 < cstep) {
-                    const int i = m0 + row;
-                    const double ui = u[i], qi = q[i];
-                    for (int j = m0 + col0; j < n; j += cstep) {
-                        const double t2 = __dadd_rn(__dmul_rn(ui, q[j]), __dmul_rn(qi, u[j]));
-                        A[i + (size_t)j * n] -= t2;
-                    }
-                }
-            }
-            for (int i = m0 + tid; i < n; i += nthr) Hg[i + (size_t)k * n] = u[i];
-        }
-        __syncthreads();
-    }
-    if (tid == 0) {
-        if (n >= 2) {
-            d[n - 2] = A[(n - 2) + (size_t)(n - 2) * n];
-            e[n - 2] = A[(n - 1) + (size_t)(n - 2) * n];
-            tau[n - 2] = 0.0;
-        }
-        d[n - 1] = A[(n - 1) + (size_t)(n - 1) * n];
-        e[n - 1] = 0.0;
-        tau[n - 1] = 0.0;
-    }
-    __syncthreads();
-}
-
-// 1/q to ~1 ulp for normal q: the 20-bit hardware seed and two Newton steps (the Sturm recurrence needs no IEEE division:
-// a relative error of a few ulp is a relative perturbation of e^2 of the same size)
+// 1/q to ~1 ulp for normal q: the 20-bit hardware seed and two Newton steps (the Sturm recurrence and the reflector
+// scaling need no IEEE division: a relative error of a few ulp is a relative perturbation of the same size)
 __device__ __forceinline__ double rcp_newton(double q) {
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(q));
@@ -143,24 +52,209 @@ __device__ __forceinline__ double rcp_newton(double q) {
     return r;
 }
 
-// number of eigenvalues of the tridiagonal (d, e) below x; e2[i] = e[i]^2; pivmin is a normal number
-__device__ __forceinline__ int sturm_count(const double *d, const double *e2, int n, double x, double pivmin) {
-    double q = d[0] - x;
-    if (fabs(q) < pivmin) q = -pivmin;
-    int cnt = q < 0.0;
-    for (int i = 1; i < n; i++) {
-        q = fma(-e2[i - 1], rcp_newton(q), d[i] - x);
-        if (fabs(q) < pivmin) q = -pivmin;
-        cnt += q < 0.0;
+// Householder reduction of the symmetric A (n x n, ld n, full storage, shared memory) to tridiagonal (d, e).  Reflector
+// k is H_k = I - tau[k] u u' with u stored in Hg[k+1.., k] (global); A = H_0 ... H_{n-3} T H_{n-3} ... H_0.
+// wk: 4 n doubles of shared scratch.  n <= 32 RT.
+//
+// One barrier and ONE pass over the trailing block per reflector:
+//   * the rank-2 update of step k-1 is DELAYED: A holds A_old and (u, q) of the previous step stay in registers
+//     (entry i on lane i & 31, register i >> 5, identical in every warp); whoever reads A applies  - (u_i q_j + q_i u_j)
+//     on the fly, in the symmetric rounded form, so (i, j) and (j, i) keep identical bits;
+//   * every warp forms column k and its reflector redundantly (same operations, same bits: no broadcast, no barrier);
+//   * warp w owns the columns j = k+1 + w, k+1 + w + NW, ...: it reads column j once, applies the pending update, writes
+//     it back and, the matrix being symmetric, dots it with the new u: that is row j of p = A u.  One warp reduction per
+//     column, no cross-warp partial sums;
+//   * after the step's only barrier every warp computes u'p and q = beta p - (beta^2 u'p / 2) u from the shared p.
+// u and p are ping-pong buffered so that a fast warp's writes of step k+1 cannot overtake a slow warp's reads of step k.
+// Measured on 131 x 131 (cycles per matrix, one CTA of 22 warps): 920k for the first version (four barrier-separated
+// phases per step: reflector in warp 0, partial products, q in warp 0, rank-2 update), 801k for this one.  Two further
+// restructurings were measured and dropped: the scalar work confined to warp 0 with a four-column pass over relative
+// row indices (872k), and that plus u'p folded into the pass, rsqrt/rcp instead of sqrt and division (941k).  Thread
+// 0's clock shows where a step's ~6k cycles go: ~2.4k in the reflector's scalar chain, ~3.6k in the pass, 30 cycles of
+// barrier wait -- the routine is bound by the latency of dependent FP64 operations along 129 sequential steps, which
+// only more independent work per SM (a second matrix; shared memory holds one) would hide.
+template <int NW, int RT>
+__device__ void tridiagonalise(double *A, int n, double *d, double *e, double *tau, double *wk, double *Hg) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = NW * 32;
+    // (buffers addressed as offsets from wk, never through an array of pointers: the compiler then keeps the address
+    //  space and emits LDS/STS instead of generic loads)
+    for (int i = tid; i < 4 * n; i += nthr) wk[i] = 0.0;
+    __syncthreads();
+    double uprev[RT], qprev[RT];
+#pragma unroll
+    for (int t = 0; t < RT; t++) uprev[t] = qprev[t] = 0.0;
+    double beta_prev = 0.0, K_prev = 0.0;
+    // entry j of the pending q, from the shared p of the previous step (the formula the registers were filled with)
+#define TRI_QPREV(j, upj) fma(-K_prev, (upj), beta_prev * pbp[(j)])
+#define TRI_UPD(a, ui, qj, qi, uj) ((a) - __dadd_rn(__dmul_rn((ui), (qj)), __dmul_rn((qi), (uj))))
+    for (int k = 0; k < n - 2; k++) {
+        const int m0 = k + 1, cur = k & 1;
+        const double *ubp = wk + (cur ^ 1) * n, *pbp = wk + (2 + (cur ^ 1)) * n;
+        double *ubc = wk + cur * n, *pbc = wk + (2 + cur) * n;
+        const double *colk = A + (size_t)k * n;
+        // ---- column k of the current matrix and its reflector (every warp, redundantly) ----
+        const double uk = ubp[k], qk = TRI_QPREV(k, uk);
+        const double um = ubp[m0], qm = TRI_QPREV(m0, um);
+        const double dk = TRI_UPD(colk[k], uk, qk, qk, uk);
+        const double x0 = TRI_UPD(colk[m0], um, qk, qm, uk);
+        double x[RT];
+        double ss = 0.0;
+#pragma unroll
+        for (int t = 0; t < RT; t++) {
+            const int i = lane + 32 * t;
+            x[t] = 0.0;
+            if (i > m0 && i < n) {
+                x[t] = TRI_UPD(colk[i], uprev[t], qk, qprev[t], uk);
+                ss = fma(x[t], x[t], ss);
+            }
+        }
+        ss = warp_sum_all(ss);
+        double alpha = x0, beta = 0.0, u0 = 0.0;
+        if (ss > DBL_MIN) {
+            const double nrm = sqrt(fma(x0, x0, ss));
+            alpha = x0 > 0.0 ? -nrm : nrm;
+            u0 = x0 - alpha;
+            beta = 2.0 / fma(u0, u0, ss);
+        }
+        double ucur[RT];
+#pragma unroll
+        for (int t = 0; t < RT; t++) {
+            const int i = lane + 32 * t;
+            ucur[t] = (beta == 0.0 || i < m0 || i >= n) ? 0.0 : (i == m0 ? u0 : x[t]);
+        }
+        if (warp == 0) {
+            if (lane == 0) { d[k] = dk; e[k] = alpha; tau[k] = beta; }
+#pragma unroll
+            for (int t = 0; t < RT; t++) {
+                const int i = lane + 32 * t;
+                if (i < n) ubc[i] = ucur[t];
+                if (beta != 0.0 && i >= m0 && i < n) Hg[i + (size_t)k * n] = ucur[t];
+            }
+        }
+        // ---- the pass: pending update applied to the owned columns, p_j = (column j) . u ----
+        for (int j = m0 + warp; j < n; j += 2 * NW) {
+            const int j2 = j + NW;
+            const bool two = j2 < n;
+            const double upj = ubp[j], qpj = TRI_QPREV(j, upj);
+            const double upj2 = two ? ubp[j2] : 0.0, qpj2 = two ? TRI_QPREV(j2, upj2) : 0.0;
+            double *cj = A + (size_t)j * n, *cj2 = A + (size_t)(two ? j2 : j) * n;
+            double acc = 0.0, acc2 = 0.0;
+#pragma unroll
+            for (int t = 0; t < RT; t++) {
+                const int i = lane + 32 * t;
+                if (i >= m0 && i < n) {
+                    const double a1 = TRI_UPD(cj[i], uprev[t], qpj, qprev[t], upj);
+                    cj[i] = a1;
+                    acc = fma(a1, ucur[t], acc);
+                    if (two) {
+                        const double a2 = TRI_UPD(cj2[i], uprev[t], qpj2, qprev[t], upj2);
+                        cj2[i] = a2;
+                        acc2 = fma(a2, ucur[t], acc2);
+                    }
+                }
+            }
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) {
+                acc += __shfl_xor_sync(0xffffffffu, acc, o);
+                acc2 += __shfl_xor_sync(0xffffffffu, acc2, o);
+            }
+            if (lane == 0) { pbc[j] = acc; if (two) pbc[j2] = acc2; }
+        }
+        __syncthreads();
+        // ---- q of this step (every warp, redundantly) ----
+        double up = 0.0;
+#pragma unroll
+        for (int t = 0; t < RT; t++) {
+            const int i = lane + 32 * t;
+            qprev[t] = (i >= m0 && i < n) ? beta * pbc[i] : 0.0;       // beta p for now
+            up = fma(ucur[t], qprev[t], up);
+        }
+        up = warp_sum_all(up);
+        K_prev = 0.5 * beta * up;
+        beta_prev = beta;
+#pragma unroll
+        for (int t = 0; t < RT; t++) {
+            const int i = lane + 32 * t;
+            qprev[t] = (i >= m0 && i < n) ? fma(-K_prev, ucur[t], qprev[t]) : 0.0;
+            uprev[t] = ucur[t];
+        }
     }
+    if (tid == 0) {                                              // the last 2 x 2 block, pending update applied
+        if (n >= 3) {
+            const int last = (n - 3) & 1, a = n - 2, b = n - 1;
+            const double *ubp = wk + last * n, *pbp = wk + (2 + last) * n;
+            const double ua = ubp[a], ubb = ubp[b];
+            const double qa = TRI_QPREV(a, ua), qb = TRI_QPREV(b, ubb);
+            d[a] = TRI_UPD(A[a + (size_t)a * n], ua, qa, qa, ua);
+            e[a] = TRI_UPD(A[b + (size_t)a * n], ubb, qa, qb, ua);
+            d[b] = TRI_UPD(A[b + (size_t)b * n], ubb, qb, qb, ubb);
+            tau[a] = 0.0;
+        } else if (n == 2) {
+            d[0] = A[0]; e[0] = A[1]; d[1] = A[3]; tau[0] = 0.0;
+        } else {
+            d[0] = A[0];
+        }
+        e[n - 1] = 0.0;
+        tau[n - 1] = 0.0;
+    }
+#undef TRI_QPREV
+#undef TRI_UPD
+    __syncthreads();
+}
+
+// Number of eigenvalues of the tridiagonal (d, e) below x; e2[i] = e[i]^2.  Sturm sequence in its POLYNOMIAL form
+//   p_0 = 1,  p_1 = d_0 - x,  p_{i+1} = (d_i - x) p_i - e_{i-1}^2 p_{i-1}:   count = sign changes along p_0 .. p_n,
+// a zero taking the sign opposite to its predecessor's.  This loop runs on a few hundred threads whose only speed limit
+// is the chain of DEPENDENT operations per step (346k of a masked star's 1.9M cycles went here): the quotient form
+// q_i = p_i / p_{i-1} (LAPACK dstebz; the first version) has a reciprocal and ~6 dependent FP64 operations per step, the
+// polynomial form ONE fused multiply-add -- d_i - x, e^2 p_{i-1}, the sign bookkeeping and the loads all hang off the
+// chain and overlap once the loop is unrolled.  What the quotient form buys -- no overflow -- is recovered by rescaling
+// (p_i, p_{i-1}) by a common power of two every eight steps: signs and the recurrence are invariant under it, and the
+// caller hands over T scaled to |T| in [1, 2), so eight unscaled steps grow by at most 2^24 and can shrink by 2^-424.
+// The loads are software-pipelined by hand (block i+1 is fetched into registers while block i's chain runs): left to
+// itself the compiler issued each LDS right before its use, which put a shared-memory round trip on every step's chain.
+#define STURM_STEP(dv, ev) do {                                          \
+        const double c_ = fma((dv) - x, a, -((ev) * b));                 \
+        const int sc_ = (c_ == 0.0) ? ~sa : __double2hiint(c_);          \
+        cnt += (unsigned)(sc_ ^ sa) >> 31;                               \
+        sa = sc_; b = a; a = c_;                                         \
+    } while (0)
+__device__ __forceinline__ int sturm_count(const double *d, const double *e2, int n, double x) {
+    double b = 1.0, a = d[0] - x;                                // (p_{i-1}, p_i)
+    int sa = (a == 0.0) ? (int)0x80000000 : __double2hiint(a);   // sign word of p_i under the zero rule
+    int cnt = (unsigned)sa >> 31;
+    int i = 1;
+    if (n >= 9) {
+        double d0 = d[1], d1 = d[2], d2 = d[3], d3 = d[4], f0 = e2[0], f1 = e2[1], f2 = e2[2], f3 = e2[3];
+        for (; i + 11 < n; i += 8) {                             // steps i .. i+7; the block after them exists too
+            const double g0 = d[i + 4], g1 = d[i + 5], g2 = d[i + 6], g3 = d[i + 7];
+            const double h0 = e2[i + 3], h1 = e2[i + 4], h2 = e2[i + 5], h3 = e2[i + 6];
+            STURM_STEP(d0, f0); STURM_STEP(d1, f1); STURM_STEP(d2, f2); STURM_STEP(d3, f3);
+            d0 = d[i + 8]; d1 = d[i + 9]; d2 = d[i + 10]; d3 = d[i + 11];
+            f0 = e2[i + 7]; f1 = e2[i + 8]; f2 = e2[i + 9]; f3 = e2[i + 10];
+            STURM_STEP(g0, h0); STURM_STEP(g1, h1); STURM_STEP(g2, h2); STURM_STEP(g3, h3);
+            // common power-of-two rescale: max(|a|, |b|) -> [1, 2)
+            const int ea = __double2hiint(a) & 0x7ff00000, eb = __double2hiint(b) & 0x7ff00000;
+            const double scl = __hiloint2double(0x7fe00000 - (ea > eb ? ea : eb), 0);
+            a *= scl; b *= scl;
+        }
+        STURM_STEP(d0, f0); STURM_STEP(d1, f1); STURM_STEP(d2, f2); STURM_STEP(d3, f3);   // the block already in registers
+        i += 4;
+        const int ea = __double2hiint(a) & 0x7ff00000, eb = __double2hiint(b) & 0x7ff00000;
+        const double scl = __hiloint2double(0x7fe00000 - (ea > eb ? ea : eb), 0);
+        a *= scl; b *= scl;
+    }
+    for (; i < n; i++) STURM_STEP(d[i], e2[i - 1]);              // at most 11 steps
     return cnt;
 }
+#undef STURM_STEP
 
 // lam[j], j < m: the m largest eigenvalues in descending order.  Eight lanes per eigenvalue split the bracket into nine
 // parts per round (N(lo) < n - j <= N(hi) throughout).
 template <int NW>
 __device__ void top_eigenvalues(const double *d, const double *e2, int n, int m, double glo, double ghi, double pivmin,
                                 double *lam) {
+    // (pivmin only enters the stopping rule now)
     const int tid = threadIdx.x, lane = tid & 31, sub = tid & 7, ngrp = NW * 4, sh = lane & 24;
     const unsigned gmask = 0xffu << sh;
     for (int j = tid >> 3; j < m; j += ngrp) {
@@ -169,7 +263,7 @@ __device__ void top_eigenvalues(const double *d, const double *e2, int n, int m,
         for (int it = 0; it < 26; it++) {
             const double w = (hi - lo) * (1.0 / 9.0);
             const double x = fma(w, (double)(sub + 1), lo);
-            const int cnt = sturm_count(d, e2, n, x, pivmin);
+            const int cnt = sturm_count(d, e2, n, x);
             const unsigned b = (__ballot_sync(gmask, cnt >= want) >> sh) & 0xffu;
             const int s = b ? __ffs(b) - 1 : 8;
             const double nlo = s == 0 ? lo : fma(w, (double)s, lo);
@@ -277,7 +371,7 @@ __device__ int gram_eig_pca(double *W, int r, int c, int ncomp, double pratio, d
     for (int p = tid; p < n * n; p += nthr) W[p] = Cg[p];
     __syncthreads();
     EIG_TICK(3);
-    tridiagonalise<NW, RT>(W, n, d, e, tau, region, region + n, region + 2 * n, Hg);
+    tridiagonalise<NW, RT>(W, n, d, e, tau, region, Hg);
     EIG_TICK(4);
     // Gershgorin bracket, trace, norm
     double *e2 = region;
@@ -303,12 +397,20 @@ __device__ int gram_eig_pca(double *W, int r, int c, int ncomp, double pratio, d
             fth[3] = tn;
         }
     }
-    for (int i = tid; i < n; i += nthr) e2[i] = e[i] * e[i];
     __syncthreads();
     const double tnorm = fth[3];
+    if (!(tnorm > 1e-200 && tnorm < 1e200)) return 0;            // zero, non-finite or absurd: let the Jacobi SVD decide
+    // the eigenvalue search runs on T scaled by an exact power of two to |T| in [1, 2) (sturm_count's contract)
+    const int texp = __double2hiint(tnorm) & 0x7ff00000;
+    const double tsc = __hiloint2double(0x7fe00000 - texp, 0), tinv = __hiloint2double(texp, 0);
+    double *ds = region + n;
+    for (int i = tid; i < n; i += nthr) { const double es = e[i] * tsc; e2[i] = es * es; ds[i] = d[i] * tsc; }
+    __syncthreads();
     int m = ncomp < n ? ncomp : n;
     if (c < m) m = c;
-    top_eigenvalues<NW>(d, e2, n, m, fth[0], fth[1], DBL_MIN * fmax(1.0, tnorm * tnorm), lam);
+    top_eigenvalues<NW>(ds, e2, n, m, fth[0] * tsc, fth[1] * tsc, 4.0 * DBL_MIN, lam);
+    __syncthreads();
+    for (int i = tid; i < m; i += nthr) lam[i] *= tinv;
     __syncthreads();
     EIG_TICK(5);
     if (tid == 0) {                                              // choose_pcadim on lambda_i / (c - 1)

@@ -711,9 +711,11 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         if (prof && tid == 0) { for (int i = 0; i < 16; i++) prof[i] = 0; prof[0] = clock64(); }
 
         // ---- load, nanToZero, finiteness (LAPACK raises on Inf -> shopt.jl:305-309 zeros + failedStars) ----
-        int bad = 0;
+        int bad = 0, nrep = 0;
         for (long long p = tid; p < rc; p += nthr) {
-            const double x = nan_to_zero(__ldg(X + p));
+            const double x0 = __ldg(X + p);
+            const double x = nan_to_zero(x0);
+            nrep += isnan(x0);
             if (!isfinite(x)) bad = 1;
             W[p] = x;
         }
@@ -759,22 +761,29 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
             }
         }
         fro = block_sum1<NW>(fro, scratch, buf);                // |Z|_F^2; the block sum also publishes W
+        // Masked pixels become 0.001 (masks.jl:43), each an outlier in a direction of its own.  When their energy alone
+        // exceeds half of the variance the kept components may leave out, k runs into the tens and the subspace
+        // iterations below would only be abandoned (205k cycles per star on the masked BASELINE catalogue): such stars
+        // go straight to the direct path.  A scheduling decision only: both paths are checked a posteriori.
+        const bool direct_ok = !GW && a.eigscratch && r <= c && r >= 16 && r <= nthr && r <= 32 * RT;
+        const double nrep_all = (a.debug & 64) ? 0.0 : block_sum1<NW>((double)nrep, scratch, buf);
+        const bool flat = direct_ok && nrep_all * 1e-6 > 0.5 * (1.0 - a.pratio) * fro;
 
         if (prof && tid == 0) prof[1] = clock64();
         // ---- fast path: block subspace iteration with a-posteriori acceptance ----
         int k = 0, status = SHOPT_PCA_OK, dbg_it = 0;
-        if (a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr && a.kmax >= 1 && !(a.debug & 32)) {
+        if (!flat && a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr && a.kmax >= 1 && !(a.debug & 32)) {
             // one component: q, qn, t in the block path's buffers (column 0 of Q, Qn, T); scratch in its Gram area
             k = power_pca<NW>(W, r, c, fro, a.pratio, FQ, FQn, FT, FG, fth, &dbg_it);
             if (k == 1 && tid == 0) ford[0] = 0;
             __syncthreads();
         }
-        if (k == 0 && a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
+        if (k == 0 && !flat && a.fast && r >= 2 * FB && c >= 2 * FB && r <= nthr)
             k = fast_pca<NW, RT>(W, r, c, fro, a.ncomp, a.pratio, FQ, FQn, FT, ldq, FG, fth, ford, s_flag, &dbg_it, a.debug & 4, (a.debug & 8) ? 2 : 3);
         const bool fastk = k > 0;
         if (prof && tid == 0) prof[2] = clock64();
         bool eigk = false;
-        if (!GW && !fastk && a.eigscratch && r <= c && r >= 16 && r <= nthr && r <= 32 * RT) {
+        if (!fastk && direct_ok) {
             // ---- direct path: eigenvectors of the r x r Gram matrix (pca_eig.cuh); 0 = a check failed ----
             double *Cg = a.eigscratch + (size_t)blockIdx.x * a.eigstride;
             k = gram_eig_pca<NW, RT>(W, r, c, a.ncomp, a.pratio, Y, det, sv, fth, s_flag, Cg, Cg + (size_t)r * r, prof);
@@ -1283,7 +1292,7 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
     a.eigscratch = nullptr; a.eigstride = getenv("SHOPT_PCA_NO_EIG") ? 0 : (size_t)2 * r * r;
     a.kmax = ncomp < r ? ncomp : r; if (c < a.kmax) a.kmax = c;
     a.fast = (getenv("SHOPT_PCA_NO_FAST") == nullptr);
-    a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on, 8: first acceptance check after 2 iterations, 16: print cycles per phase
+    a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on, 8: first acceptance check after 2 iterations, 16: print cycles per phase, 32: no power path, 64: masked stars try the fast paths too
     if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern, a.kz);
     const int rt = ((r > c ? r : c) + 31) / 32;
     switch (rt) {
