@@ -403,8 +403,10 @@ int64_t shopt_select_worst_sharded_host(const double *err_local, const uint32_t 
 /* device-resident shard; comm == NULL runs a single GPU.  Blocks until the stage is done; the control flow between
  * the kernels (survivor counts, training split, worst_10_percent, list compaction) runs on the device, the call
  * synchronises the stream twice and allocates nothing after the first call of a given size.
- * Sharded runs: median_constraint and NaN pixel-grid values among the training stars (chisq mode with masked pixels)
- * need per-pixel medians across shards. */
+ * Sharded runs serve the same options as one GPU: median_constraint and the NaN -> median repair (interpolate.jl:118-130)
+ * take the per-pixel median over the training stars of EVERY shard by a radix select whose 256-bin histograms are the
+ * only thing ranks exchange (16 int32 sum-all-reduces per 16 384-pixel tile), and cost one extra stream synchronisation
+ * per round (every rank has to learn whether any pixel's all-reduced V'P is NaN). */
 int shopt_stage_run_dev(const shopt_params *p, shopt_stage_io *io, shopt_allreduce_fn comm, void *comm_user, void *stream);
 /* host buffers, one GPU: H2D (chunked on a copy stream, overlapped with the per-star kernels), stage, D2H */
 int shopt_stage_run(const shopt_params *p, shopt_stage_io *io);

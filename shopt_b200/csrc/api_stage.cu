@@ -115,6 +115,7 @@ struct StageBufs {
     int *blockcnt;
     long long *blockoff;
     double *acc, *rows, *med, *uvsums, *ctr, *clip;
+    void *shard_med;                // sharded runs: work space of the cross-shard per-pixel median (polyfit_median_sharded_launch)
     PolyFactor *fac, *fac_red, *fac_field;
     double *field_part, *field_acc, *field_poly, *field_out;
     int field_nb;
@@ -142,6 +143,7 @@ static StageBufs stage_carve(void *base, const shopt_params *p, const shopt_stag
     b.acc = a.take<double>(K * K + K * rc);
     b.rows = a.take<double>(4 * rc);
     b.med = a.take<double>(rc);
+    b.shard_med = sharded ? (void *)a.take<char>(polyfit_shard_median_bytes((long long)rc, p->degree)) : nullptr;
     b.uvsums = a.take<double>(8); b.ctr = a.take<double>(4); b.clip = a.take<double>(4);
     b.fac = a.take<PolyFactor>(1); b.fac_red = a.take<PolyFactor>(1); b.fac_field = a.take<PolyFactor>(1);
     b.field_nb = (int)std::min<long long>(64, std::max<long long>(1, (io->n_local + FIELD_CHUNK - 1) / FIELD_CHUNK));
@@ -157,6 +159,7 @@ struct StageResult {
     int field_head[4];
     double field[32];
     int bad_perm[4];
+    long long n_nan;        // sharded runs: pixels whose all-reduced V'P is NaN this round
     long long n_after[16];  // sigma clipping: the whole catalogue's training count after each round's rejection
 };
 
@@ -316,20 +319,32 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, const Excha
                                       ctx->scratch_bytes, st));
             if (ex.on()) {
                 TRY(ex.sum(b.acc, (long long)K * K + (long long)K * rc, 0));
-                // NaN pixel-grid values: the per-pixel median needs the values of every shard (sharded_median_*)
+                // NaN pixel-grid values (interpolate.jl:126-130): the per-pixel median needs the values of every shard.
+                // The all-reduced V'P tells every rank the same thing, so all of them enter the exchange or none does;
+                // the host has to know, which costs sharded runs one stream synchronisation per round.
                 if (!p->median_constraint) {
+                    SHOPT_CUDA_TRY(cudaMemsetAsync(&b.state->n_nan, 0, sizeof(long long), st));
                     nan_count_kernel<<<(unsigned)((rc + 255) / 256), 256, 0, st>>>(b.acc + (size_t)K * K, rc, &b.state->n_nan);
                     count_launches(1);
-                    nan_rounds++;
+                    SHOPT_CUDA_TRY(cudaMemcpyAsync(&res->n_nan, &b.state->n_nan, sizeof(long long), cudaMemcpyDeviceToHost, st));
+                    SHOPT_CUDA_TRY(cudaStreamSynchronize(st));
+                    if (res->n_nan > 0) {
+                        TRY(polyfit_median_sharded_launch(io->pgf, rc, io->u, io->v, sl, p->degree, b.ctr, 2, b.acc, b.med,
+                                                          b.shard_med, ex, st));
+                        nan_rounds++;
+                    }
                 }
             } else if (!p->median_constraint) {      // NaN values -> median before the solve (interpolate.jl:126-130)
                 TRY(polyfit_median_launch(io->pgf, rc, io->u, io->v, sl, p->degree, b.ctr, 2, b.acc, nullptr, st));
             }
             TRY(polyfit_factor_launch(b.acc, p->degree, b.ctr, nullptr, nc, 0, b.fac, st));
             if (p->median_constraint) {              // interpolate.jl:118-124, 139-141
-                if (ex.on()) { set_last_error_text("median_constraint is not available in sharded runs yet"); return SHOPT_E_UNSUPPORTED; }
                 TRY(polyfit_factor_launch(b.acc, p->degree, b.ctr, nullptr, nc, 1, b.fac_red, st));
-                TRY(polyfit_median_launch(io->pgf, rc, io->u, io->v, sl, p->degree, b.ctr, 1, nullptr, b.med, st));
+                if (ex.on())    // the median of z over the training stars of every shard: histogram exchange per radix pass
+                    TRY(polyfit_median_sharded_launch(io->pgf, rc, io->u, io->v, sl, p->degree, b.ctr, 1, nullptr, b.med,
+                                                      b.shard_med, ex, st));
+                else
+                    TRY(polyfit_median_launch(io->pgf, rc, io->u, io->v, sl, p->degree, b.ctr, 1, nullptr, b.med, st));
                 TRY(polyfit_solve_launch(b.acc, rc, p->degree, b.fac, b.fac_red, b.med, io->poly, st));
             } else {
                 TRY(polyfit_solve_launch(b.acc, rc, p->degree, b.fac, nullptr, nullptr, io->poly, st));
@@ -370,10 +385,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, const Excha
     io->polyfit_rank = (p->iterations > 0 && n_train >= 5) ? res->fac_head[2] : 0;
     io->polyfit_info = (p->iterations > 0 && n_train >= 5) ? res->fac_head[3] : 0;
     if (io->polyfit_info & SHOPT_POLY_NONFINITE) set_last_error_text("polyfit: non-finite normal equations (NaN in u, v or the pixel-grid fits): coefficients are NaN");
-    if (nan_rounds && res->state.n_nan > 0) {
-        set_last_error_text("sharded run: NaN pixel-grid values among the training stars need the cross-shard median repair");
-        return SHOPT_E_UNSUPPORTED;
-    }
+    (void)nan_rounds;
     return SHOPT_OK;
 }
 

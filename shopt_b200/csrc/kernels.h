@@ -37,6 +37,10 @@ int polyfit_mse_launch(const double *pgf, long long rc, const double *u, const d
 // for the pixels whose sums are NaN, with NaN values replaced by the median (interpolate.jl:126-130)
 int polyfit_median_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
                           const double *ctr, int mode, double *acc, double *med, cudaStream_t st);
+size_t polyfit_shard_median_bytes(long long rc, int degree);
+int polyfit_median_sharded_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
+                                  const double *ctr, int mode, double *acc, double *med, void *work, const Exchange &ex,
+                                  cudaStream_t st);
 int psf_at_launch(const double *poly, long long rc, int degree, const double *u, const double *v, long long M,
                   double *out, cudaStream_t st);
 int small_median_launch(const double *rows, long long rc, int n, int degree, double *poly, cudaStream_t st);

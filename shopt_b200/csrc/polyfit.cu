@@ -19,6 +19,7 @@
 //   solve_kernel   equilibrated Cholesky of G in shared memory, then one thread per pixel back-substitutes;
 //   mse_kernel     same tiling as normal_kernel with the K*PX coefficients of the thread's pixels in registers;
 //                  per-star partial sums per pixel tile, reduced in tile order by mse_reduce_kernel.
+#include <algorithm>
 #include <cstdlib>
 
 #include "api_ctx.h"
@@ -590,6 +591,143 @@ __global__ void __launch_bounds__(MED_THREADS) median_fix_kernel(const double *_
         }
     }
 }
+// ---------------------------------------------------------------------------------------------
+// The same per-pixel median when the training stars are SHARDED over ranks (one process per GPU): the radix select
+// runs on every rank with the same prefix; the only thing ranks exchange is the 256-bin histogram of each pass (one
+// int32 sum-all-reduce per pass), after which every rank takes the same bin.  Two selections per pixel -- the lower
+// and the upper middle order statistic -- so that an even count gives Statistics.middle(v1, v2) = v1/2 + v2/2 without a
+// min-reduction.  Integer arithmetic only: exact, and identical on every rank.  Pixels are processed in tiles so that
+// the histogram buffer stays bounded (SHARD_MED_TILE pixels x 256 bins).
+// ---------------------------------------------------------------------------------------------
+__global__ void shard_med_init_kernel(const double *__restrict__ b0, long long rc, int mode, int *__restrict__ need,
+                                      unsigned long long *__restrict__ prefix, unsigned *__restrict__ kleft,
+                                      unsigned *__restrict__ total) {
+    const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (px >= rc) return;
+    need[px] = (mode == 1) ? 1 : (isnan(b0[px]) ? 1 : 0);       // mode 2: V'P of the constant term is NaN iff z has a NaN
+    prefix[px] = 0ULL; prefix[rc + px] = 0ULL; kleft[px] = 0u; kleft[rc + px] = 0u; total[px] = 0u;
+}
+__global__ void __launch_bounds__(MED_THREADS) shard_med_hist_kernel(const double *__restrict__ pgf, long long rc,
+                                                                     const long long *__restrict__ idx, long long n_bound,
+                                                                     const long long *__restrict__ n_ptr, long long px0,
+                                                                     long long npx, int pass, const int *__restrict__ need,
+                                                                     const unsigned long long *__restrict__ prefix,
+                                                                     unsigned *__restrict__ hist) {
+    const long long n = n_ptr ? *n_ptr : n_bound;
+    extern __shared__ __align__(16) unsigned char med_smem[];
+    unsigned int *sh = reinterpret_cast<unsigned int *>(med_smem);              // [256][MED_PX]
+    __shared__ int s_need[MED_PX];
+    const int pl = threadIdx.x % MED_PX, lane = threadIdx.x / MED_PX;
+    const long long loc = (long long)blockIdx.x * MED_PX + pl, px = px0 + loc;
+    if (lane == 0) s_need[pl] = (loc < npx && px < rc) ? need[px] : 0;
+    for (int e = threadIdx.x; e < 256 * MED_PX; e += MED_THREADS) sh[e] = 0u;
+    __syncthreads();
+    int any = 0;
+    for (int i = 0; i < MED_PX; i++) any |= s_need[i];
+    if (!any) return;                                                           // (hist was zeroed by the host)
+    const int shift = 56 - 8 * pass;
+    if (s_need[pl]) {
+        const unsigned long long pre = prefix[px];
+        for (long long t = lane; t < n; t += MED_LANES) {
+            const long long star = idx ? idx[t] : t;
+            const double z = __ldg(pgf + star * rc + px);
+            if (isnan(z)) continue;
+            const unsigned long long key = order_key(z);
+            if (pass == 0 || (key >> (shift + 8)) == (pre >> (shift + 8)))
+                atomicAdd(&sh[(unsigned)((key >> shift) & 255ULL) * MED_PX + pl], 1u);
+        }
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < 256 * MED_PX; e += MED_THREADS) {
+        const int b = e / MED_PX, q = e % MED_PX;
+        const long long l2 = (long long)blockIdx.x * MED_PX + q;
+        if (l2 < npx && s_need[q]) hist[(size_t)l2 * 256 + b] = sh[e];
+    }
+}
+// which = 0: order statistic (total - 1) / 2, which = 1: total / 2 (0-based, over the whole catalogue's finite values)
+__global__ void shard_med_pick_kernel(const unsigned *__restrict__ hist, long long rc, long long px0, long long npx, int pass,
+                                      int which, const int *__restrict__ need, unsigned long long *__restrict__ prefix,
+                                      unsigned *__restrict__ kleft, unsigned *__restrict__ total) {
+    const long long loc = (long long)blockIdx.x * blockDim.x + threadIdx.x, px = px0 + loc;
+    if (loc >= npx || px >= rc || !need[px]) return;
+    const unsigned *h = hist + (size_t)loc * 256;
+    unsigned k = kleft[(size_t)which * rc + px];
+    if (pass == 0) {
+        unsigned tot = 0;
+        for (int b = 0; b < 256; b++) tot += h[b];
+        total[px] = tot;
+        k = tot ? (which ? tot / 2 : (tot - 1) / 2) : 0;
+    }
+    const int shift = 56 - 8 * pass;
+    unsigned cum = 0;
+    for (int b = 0; b < 256; b++) {
+        const unsigned hb = h[b];
+        if (cum + hb > k) { prefix[(size_t)which * rc + px] |= (unsigned long long)b << shift; k -= cum; break; }
+        cum += hb;
+    }
+    kleft[(size_t)which * rc + px] = k;
+}
+__global__ void shard_med_final_kernel(long long rc, const int *__restrict__ need, const unsigned long long *__restrict__ prefix,
+                                       const unsigned *__restrict__ total, double *__restrict__ med) {
+    const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (px >= rc) return;
+    double m = nan("");
+    if (need[px] && total[px]) {
+        const double v1 = key_value(prefix[px]), v2 = key_value(prefix[rc + px]);
+        m = (total[px] & 1u) ? v1 : v1 / 2 + v2 / 2;
+    }
+    med[px] = m;
+}
+// mode 2: this shard's share of V'P for the flagged pixels, NaN values replaced by the catalogue-wide median
+template <int DEG>
+__global__ void __launch_bounds__(MED_THREADS) shard_refill_kernel(const double *__restrict__ pgf, long long rc,
+                                                                   const double *__restrict__ u, const double *__restrict__ v,
+                                                                   const long long *__restrict__ idx, long long n_bound,
+                                                                   const long long *__restrict__ n_ptr,
+                                                                   const double *__restrict__ ctr, const int *__restrict__ need,
+                                                                   const double *__restrict__ med, double *__restrict__ fix) {
+    constexpr int K = PolyCfg<DEG>::K;
+    const long long n = n_ptr ? *n_ptr : n_bound;
+    __shared__ double red[MED_LANES][MED_PX];
+    const int pl = threadIdx.x % MED_PX, lane = threadIdx.x / MED_PX;
+    const long long px = (long long)blockIdx.x * MED_PX + pl;
+    const bool fixp = px < rc && need[px];
+    if (!__syncthreads_or(fixp)) return;
+    double a[K];
+#pragma unroll
+    for (int k = 0; k < K; k++) a[k] = 0.0;
+    if (fixp) {
+        const double m = med[px];
+        for (long long t = lane; t < n; t += MED_LANES) {
+            const long long star = idx ? idx[t] : t;
+            double z = __ldg(pgf + star * rc + px);
+            if (isnan(z)) z = m;
+            double b[K], cu = u[star], cv = v[star];
+            centre_uv(ctr, cu, cv);
+            basis_eval<DEG>(cu, cv, b);
+#pragma unroll
+            for (int k = 0; k < K; k++) a[k] = fma(b[k], z, a[k]);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        __syncthreads();
+        red[lane][pl] = a[k];
+        __syncthreads();
+        if (lane == 0 && fixp) {
+            double sum = red[0][pl];
+            for (int l = 1; l < MED_LANES; l++) sum += red[l][pl];
+            fix[(size_t)k * rc + px] = sum;
+        }
+    }
+}
+__global__ void shard_apply_fix_kernel(long long rc, int K, const int *__restrict__ need, const double *__restrict__ fix,
+                                       double *__restrict__ vtp) {
+    const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (px >= rc || !need[px]) return;
+    for (int k = 0; k < K; k++) vtp[(size_t)k * rc + px] = fix[(size_t)k * rc + px];
+}
+
 // ---- launch -----------------------------------------------------------------------------------
 static int pick_chunks(long long n, int tiles) {
     long long want = ((long long)sm_count() * 16 + tiles - 1) / tiles;
@@ -791,6 +929,72 @@ int polyfit_median_launch(const double *pgf, long long rc, const double *u, cons
 #define CALL(D) median_launch_t<D>(pgf, rc, u, v, sl, ctr, mode, acc, med, st)
     DEG_SWITCH(degree, CALL)
 #undef CALL
+}
+
+// ---- sharded median: buffers and driver ----------------------------------------------------------------------
+constexpr long long SHARD_MED_TILE = 16384;
+size_t polyfit_shard_median_bytes(long long rc, int degree) {
+    const size_t tile = (size_t)std::min<long long>(rc, SHARD_MED_TILE);
+    return (size_t)rc * (2 * 8 + 2 * 4 + 4 + 4) + tile * 256 * 4 + (size_t)num_terms(degree) * rc * 8 + 8 * 256;   // Bump pads every block to 256 bytes
+}
+template <int DEG>
+static int shard_refill_launch_t(const double *pgf, long long rc, const double *u, const double *v, StarList sl,
+                                 const double *ctr, const int *need, const double *med, double *fix, cudaStream_t st) {
+    shard_refill_kernel<DEG><<<(unsigned)((rc + MED_PX - 1) / MED_PX), MED_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev,
+                                                                                             ctr, need, med, fix);
+    count_launches(1);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+static int shard_refill_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
+                               const double *ctr, const int *need, const double *med, double *fix, cudaStream_t st) {
+#define CALL(D) shard_refill_launch_t<D>(pgf, rc, u, v, sl, ctr, need, med, fix, st)
+    DEG_SWITCH(degree, CALL)
+#undef CALL
+}
+// mode 1: med (rc) = per-pixel median over the training stars of EVERY rank; mode 2: the NaN -> median repair of acc.
+// work: polyfit_shard_median_bytes(rc, degree) bytes of device scratch.  Every rank must call it (collectives inside).
+int polyfit_median_sharded_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
+                                  const double *ctr, int mode, double *acc, double *med, void *work, const Exchange &ex,
+                                  cudaStream_t st) {
+    if (mode < 1 || mode > 2 || !work || !med || (mode == 2 && !acc) || degree < 0 || degree > 8) return SHOPT_E_BADARG;
+    const int K = num_terms(degree);
+    const long long tile = std::min<long long>(rc, SHARD_MED_TILE);
+    Bump a(work);
+    unsigned long long *prefix = a.take<unsigned long long>(2 * (size_t)rc);
+    unsigned *kleft = a.take<unsigned>(2 * (size_t)rc), *total = a.take<unsigned>((size_t)rc);
+    int *need = a.take<int>((size_t)rc);
+    unsigned *hist = a.take<unsigned>((size_t)tile * 256);
+    double *fix = a.take<double>((size_t)K * rc);
+    const unsigned g256 = (unsigned)((rc + 255) / 256);
+    shard_med_init_kernel<<<g256, 256, 0, st>>>(acc ? acc + (size_t)K * K : nullptr, rc, mode, need, prefix, kleft, total);
+    count_launches(1);
+    const size_t smem = (size_t)256 * MED_PX * sizeof(unsigned int);
+    SHOPT_CUDA_TRY(cudaFuncSetAttribute(shard_med_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    for (long long px0 = 0; px0 < rc; px0 += tile) {
+        const long long npx = std::min<long long>(tile, rc - px0);
+        for (int which = 0; which < 2; which++)
+            for (int pass = 0; pass < 8; pass++) {
+                SHOPT_CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)npx * 256 * 4, st));
+                shard_med_hist_kernel<<<(unsigned)((npx + MED_PX - 1) / MED_PX), MED_THREADS, smem, st>>>(
+                    pgf, rc, sl.idx, sl.n, sl.n_dev, px0, npx, pass, need, prefix + (size_t)which * rc, hist);
+                TRY(ex.sum(hist, npx * 256, 1));
+                shard_med_pick_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, st>>>(hist, rc, px0, npx, pass, which, need, prefix,
+                                                                                     kleft, total);
+                count_launches(2);
+            }
+    }
+    shard_med_final_kernel<<<g256, 256, 0, st>>>(rc, need, prefix, total, med);
+    count_launches(1);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    if (mode == 1) return SHOPT_OK;
+    SHOPT_CUDA_TRY(cudaMemsetAsync(fix, 0, (size_t)K * rc * 8, st));
+    TRY(shard_refill_launch(pgf, rc, u, v, sl, degree, ctr, need, med, fix, st));
+    TRY(ex.sum(fix, (long long)K * rc, 0));
+    shard_apply_fix_kernel<<<g256, 256, 0, st>>>(rc, K, need, fix, acc + (size_t)K * K);
+    count_launches(1);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
 }
 
 }  // namespace shopt

@@ -46,8 +46,40 @@ def main():
     gathered = [torch.empty_like(got["poly"]) for _ in range(world)]
     dist.all_gather(gathered, got["poly"])
     assert all(torch.equal(g, gathered[0]) for g in gathered)
+    # ---- options that need a per-pixel median over the training stars of EVERY shard (interpolate.jl:118-130) ----
+    from shopt_b200 import _lib
+
+    def sharded_vs_single(params, stamps, **kw):
+        sh = {k: v[a:b].contiguous().cuda() for k, v in kw.items()}
+        g = pipeline.run_stage_dev(params, stamps[a:b].contiguous().cuda(), shard["u"], shard["v"], shard["x0_model"],
+                                   shard["x0_learned"], perm, n_global=N, offset=a, **sh)
+        torch.cuda.synchronize()
+        one = pipeline.run_stage_dev(params, stamps.cuda(), full["u"], full["v"], full["x0_model"], full["x0_learned"], perm,
+                                     exchange="none", **{k: v.cuda() for k, v in kw.items()})
+        torch.cuda.synchronize()
+        assert g["counts"] == one["counts"], (g["counts"], one["counts"])
+        assert g["n_per_round"].tolist() == one["n_per_round"].tolist()
+        assert torch.equal(g["flags"], one["flags"][a:b])
+        gp, rp = g["poly"].cpu().numpy(), one["poly"].cpu().numpy()
+        assert np.isfinite(rp).all() and np.isfinite(gp).all()
+        sc = np.abs(rp).max(axis=(1, 2), keepdims=True)
+        return gp, rp, float(np.max(np.abs(gp - rp) / sc))
+
+    # (B) median_constraint: coefficient 1 IS the median, selected by integer radix passes -> bit-identical
+    pm = pipeline.default_params(n_a=n_a, degree=2, iterations=2, training_ratio=0.9, median_constraint=1)
+    gp, rp, err_b = sharded_vs_single(pm, cat["stamps"])
+    assert np.array_equal(gp[0], rp[0]), "per-pixel medians differ between the sharded and the single-GPU run"
+    assert err_b < 1e-10, err_b
+    # (C) NaN pixel-grid values among the training stars (mode chisq, masked pixels keep a NaN start value): the NaN ->
+    #     median repair before the solve needs the other shards' values of that pixel
+    catm = synth.make_catalog(N, r, n_a, frac_masked=0.01)
+    pc = pipeline.default_params(n_a=n_a, degree=2, iterations=2, training_ratio=0.9, mode=_lib.MODE_CHISQ,
+                                 chisq_fill=float("nan"))
+    gp, rp, err_c = sharded_vs_single(pc, catm["stamps"], weights=torch.ones_like(catm["stamps"]))
+    assert err_c < 1e-10, err_c
     if rank == 0:
-        print("MULTIRANK_OK world=%d coef_err=%.2e counts=%s" % (world, err, got["counts"]))
+        print("MULTIRANK_OK world=%d coef_err=%.2e median_constraint_err=%.2e nan_repair_err=%.2e counts=%s"
+              % (world, err, err_b, err_c, got["counts"]))
     dist.destroy_process_group()
 
 
