@@ -45,7 +45,7 @@ int shopt_field_interp(const double *u, const double *v, const double *const *va
         if (std::isfinite(vv) && vv > 1e-12 * v0 * v0 && vv > 0.0) sc_v = std::sqrt(3.0 * vv);
         ctr[0] = std::isfinite(u0) ? u0 : 0.0; ctr[1] = 1.0 / sc_u; ctr[2] = std::isfinite(v0) ? v0 : 0.0; ctr[3] = 1.0 / sc_v;
     }
-    std::vector<double> G(K * K, 0.0), B((size_t)K * nvalues, 0.0), work(6 * K * K);
+    std::vector<double> G(K * K, 0.0), B((size_t)K * nvalues, 0.0), work(7 * K * K + 2 * K);
     for (int64_t i = 0; i < n; i++) {
         const double a = (u[i] - ctr[0]) * ctr[1], b = (v[i] - ctr[2]) * ctr[3];
         const double t[K] = {1.0, b, b * b, b * b * b, a, a * b, a * b * b, a * a, a * a * b, a * a * a};   // p outer, q inner

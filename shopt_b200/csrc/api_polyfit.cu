@@ -57,7 +57,7 @@ int shopt_polyfit_factor_host(const double *G, int degree, const double *centre,
                               double *coef, int32_t *info_out) {
     if (!G || degree < 0 || degree > 8 || n_rows < 0 || nrhs < 0 || (nrhs > 0 && (!b || !coef))) return SHOPT_E_BADARG;
     const int K = (degree + 1) * (degree + 2) / 2;
-    std::vector<double> work((size_t)6 * K * K);
+    std::vector<double> work((size_t)7 * K * K + 2 * K);
     std::vector<PolyFactor> F(1);
     polyfit_factor(degree, G, centre, n_rows, 0, work.data(), F.data());
     for (int j = 0; j < nrhs; j++) {

@@ -124,6 +124,134 @@ __global__ void __launch_bounds__(POLY_THREADS) normal_kernel(const double *__re
         }
 }
 
+// ---------------------------------------------------------------------------------------------
+// The same V'P partials with the pixel-grid fits staged through shared memory by 1-D bulk (TMA) copies.
+// normal_kernel keeps at most UNR x PX 8-byte loads per thread in flight and runs at 3 CTAs per SM (140 registers):
+// 61 % of the measured copy bandwidth.  Here a CTA owns a tile of NB_TP pixels and walks its chunk of stars in stages
+// of NB_S stars: one bulk copy per star row (NB_TP x 8 bytes) into a ring of NB_ST stages, completion on an mbarrier,
+// so 2 x (NB_ST - 1) x NB_S x 4 KB are in flight per SM whatever the register budget, and the FMA loop reads its
+// operands from shared memory (LDS.64 along the pixels, broadcast LDS of the basis values).
+// r c is odd at the BASELINE sizes, so a star's tile starts on an odd multiple of 8 bytes every other star: the copy
+// takes the enclosing 16-byte-aligned range (one leading double, recorded per row) and stops at the last even boundary
+// inside the tile; a trailing odd element is fetched by a plain load.  No copy ever leaves the star's own pixels.
+// Same operations in the same order as normal_kernel: the partials are bit-identical.
+// ---------------------------------------------------------------------------------------------
+constexpr int NB_TP = 512, NB_S = 8, NB_ST = 3, NB_PITCH = NB_TP + 2;
+template <int DEG>
+__global__ void __launch_bounds__(POLY_THREADS) normal_bulk_kernel(const double *__restrict__ pgf, long long rc,
+                                                                   const double *__restrict__ u, const double *__restrict__ v,
+                                                                   const long long *__restrict__ idx, long long n_bound,
+                                                                   const long long *__restrict__ n_ptr,
+                                                                   const double *__restrict__ ctr, double *__restrict__ part) {
+    constexpr int K = PolyCfg<DEG>::K, PX = NB_TP / POLY_THREADS;
+    extern __shared__ __align__(16) unsigned char nb_smem[];
+    double *ring = reinterpret_cast<double *>(nb_smem);                        // [NB_ST][NB_S][NB_PITCH]
+    double *sV = ring + (size_t)NB_ST * NB_S * NB_PITCH;                         // [2][NB_S][K]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sV + 2 * NB_S * K);            // [NB_ST]
+    int *sM = reinterpret_cast<int *>(bars + NB_ST);                             // [NB_ST][NB_S] leading doubles of each row
+    const int tid = threadIdx.x, lane = tid & 31;
+    const long long n = n_ptr ? *n_ptr : n_bound;
+    const long long per_chunk = (n + gridDim.y - 1) / gridDim.y;
+    const long long t0 = (long long)blockIdx.y * per_chunk;
+    const long long t1 = (t0 + per_chunk < n) ? t0 + per_chunk : n;
+    const long long px0 = (long long)blockIdx.x * NB_TP;
+    const int cnt = (int)((rc - px0 < NB_TP) ? (rc - px0) : NB_TP);             // pixels of this tile
+    const long long nstage = (t1 > t0) ? (t1 - t0 + NB_S - 1) / NB_S : 0;
+    if (tid == 0) {
+        for (int i = 0; i < NB_ST; i++) mbar_init(&bars[i], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    // warp 0 issues stage `stg` (rows = stars t0 + stg NB_S ...): lane r < rows copies row r
+    auto issue = [&](long long stg) {
+        const int slot = (int)(stg % NB_ST);
+        const long long base = t0 + stg * NB_S;
+        const int rows = (int)((t1 - base < NB_S) ? (t1 - base) : NB_S);
+        uint32_t bytes = 0;
+        const double *src = nullptr;
+        double *dst = ring + ((size_t)slot * NB_S + lane) * NB_PITCH;
+        long long off = 0;
+        int m = 0, tail = 0;
+        if (lane < rows) {
+            const long long star = idx ? idx[base + lane] : base + lane;
+            off = star * rc + px0;
+            m = (int)(((reinterpret_cast<uintptr_t>(pgf) >> 3) + (unsigned long long)off) & 1ULL);   // doubles before the tile
+            const long long start = off - m, end = off + cnt;                   // needed: [off, end)
+            const long long cend = end - (((reinterpret_cast<uintptr_t>(pgf) >> 3) + (unsigned long long)end) & 1ULL);
+            tail = (cend < end);
+            bytes = (uint32_t)((cend - start) * 8);
+            src = pgf + start;
+            sM[slot * NB_S + lane] = m;
+        }
+        uint32_t total = bytes;
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+        if (lane == 0) mbar_arrive_expect_tx(&bars[slot], total);
+        __syncwarp();
+        if (lane < rows) {
+            if (bytes) bulk_g2s(dst, src, bytes, &bars[slot]);
+            if (tail) dst[m + cnt - 1] = __ldg(pgf + off + cnt - 1);            // visible after the next __syncthreads
+        }
+    };
+    auto stage_basis = [&](long long stg) {
+        const long long base = t0 + stg * NB_S;
+        const int rows = (int)((t1 - base < NB_S) ? (t1 - base) : NB_S);
+        if (tid < rows) {
+            const long long star = idx ? idx[base + tid] : base + tid;
+            double b[K], cu = u[star], cv = v[star];
+            centre_uv(ctr, cu, cv);
+            basis_eval<DEG>(cu, cv, b);
+            double *o = sV + ((size_t)(stg & 1) * NB_S + tid) * K;
+#pragma unroll
+            for (int k = 0; k < K; k++) o[k] = b[k];
+        }
+    };
+    double acc[K][PX];
+#pragma unroll
+    for (int k = 0; k < K; k++)
+#pragma unroll
+        for (int j = 0; j < PX; j++) acc[k][j] = 0.0;
+    if (tid < 32) for (long long g = 0; g < NB_ST - 1 && g < nstage; g++) issue(g);
+    if (nstage > 0) stage_basis(0);
+    for (long long it = 0; it < nstage; it++) {
+        __syncthreads();                                         // stage it-1 consumed by everyone: its slot is free
+        if (tid < 32 && it + NB_ST - 1 < nstage) {
+            fence_proxy_async();                                 // generic reads of that slot before the async writes
+            issue(it + NB_ST - 1);
+        }
+        if (it + 1 < nstage) stage_basis(it + 1);
+        const int slot = (int)(it % NB_ST);
+        mbar_wait(&bars[slot], (uint32_t)((it / NB_ST) & 1));
+        const long long base = t0 + it * NB_S;
+        const int rows = (int)((t1 - base < NB_S) ? (t1 - base) : NB_S);
+        const double *bv = sV + (size_t)(it & 1) * NB_S * K;
+#pragma unroll 2
+        for (int s = 0; s < rows; s++) {
+            const double *row = ring + ((size_t)slot * NB_S + s) * NB_PITCH + sM[slot * NB_S + s];
+            double z[PX];
+#pragma unroll
+            for (int j = 0; j < PX; j++) {
+                const int p = tid + j * POLY_THREADS;
+                z[j] = (p < cnt) ? row[p] : 0.0;
+            }
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+                const double vk = bv[s * K + k];
+#pragma unroll
+                for (int j = 0; j < PX; j++) acc[k][j] = fma(vk, z[j], acc[k][j]);
+            }
+        }
+    }
+    double *out = part + (size_t)blockIdx.y * ((size_t)K * K + (size_t)K * rc);
+#pragma unroll
+    for (int k = 0; k < K; k++)
+#pragma unroll
+        for (int j = 0; j < PX; j++) {
+            const long long px = px0 + tid + (long long)j * POLY_THREADS;
+            if (px < rc) out[(size_t)K * K + (size_t)k * rc + px] = acc[k][j];
+        }
+}
+
 // G = V'V partials: one block per chunk, the K*K entries strided over the threads
 template <int DEG>
 __global__ void __launch_bounds__(POLY_THREADS) gram_kernel(const double *__restrict__ u, const double *__restrict__ v,
@@ -191,8 +319,7 @@ __global__ void factor_kernel(int degree, const double *__restrict__ G, const do
                               const long long *__restrict__ nrows_ptr, long long nrows, int drop_const,
                               PolyFactor *__restrict__ F) {
     extern __shared__ __align__(16) double fac_work[];
-    if (threadIdx.x != 0) return;
-    polyfit_factor(degree, G, ctr, nrows_ptr ? *nrows_ptr : nrows, drop_const, fac_work, F);
+    polyfit_factor(degree, G, ctr, nrows_ptr ? *nrows_ptr : nrows, drop_const, fac_work, F, (int)threadIdx.x, 32);
 }
 
 template <int DEG>
@@ -768,9 +895,42 @@ static int normal_launch_v(const double *pgf, long long rc, const double *u, con
     return SHOPT_OK;
 }
 template <int DEG>
+static int normal_bulk_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, const double *ctr,
+                              double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
+    constexpr int K = PolyCfg<DEG>::K;
+    const long long len = (long long)K * K + (long long)K * rc;
+    if (sl.n == 0) { SHOPT_CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)len * 8, st)); return SHOPT_OK; }
+    const int tiles = (int)((rc + NB_TP - 1) / NB_TP);
+    int nchunk = pick_chunks(sl.n, tiles);
+    while (nchunk > 1 && (size_t)nchunk * len * 8 > scratch_bytes) nchunk--;
+    if ((size_t)nchunk * len * 8 > scratch_bytes) return SHOPT_E_NOMEM;
+    const size_t smem = ((size_t)NB_ST * NB_S * NB_PITCH + (size_t)2 * NB_S * K) * 8 + NB_ST * 8 + (size_t)NB_ST * NB_S * 4;
+    auto kern = normal_bulk_kernel<DEG>;
+    SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<dim3(tiles, nchunk), POLY_THREADS, smem, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, ctr, scratch);
+    gram_kernel<DEG><<<nchunk, POLY_THREADS, 0, st>>>(u, v, sl.idx, sl.n, sl.n_dev, ctr, rc, scratch);
+    reduce_kernel<<<(unsigned)((len + 255) / 256), 256, 0, st>>>(scratch, len, nchunk, acc);
+    count_launches(3);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+// SHOPT_POLY_BULK=1 selects the bulk-copy staged kernel where it applies (4 pixels per thread: K <= 10).  Measured on the
+// bench workload (87k x 131 x 131, K = 10): 3.54 ms against 3.00 ms for plain loads (52 % vs 61 % of the copy bandwidth),
+// with 128 KB in flight per SM instead of ~49 KB: bytes in flight are NOT what holds normal_kernel back -- its FMA loop
+// (40 DFMA + 14 LDS per star and thread on 8-12 resident warps) is; see DESIGN.md 4.3.  Kept as a measurement switch.
+static int poly_bulk() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("SHOPT_POLY_BULK"); v = e ? atoi(e) : 0; }
+    return v;
+}
+template <int DEG>
 static int normal_launch_t(const double *pgf, long long rc, const double *u, const double *v, StarList sl, const double *ctr,
                            double *acc, double *scratch, size_t scratch_bytes, cudaStream_t st) {
     constexpr int P0 = PolyCfg<DEG>::PX, P1 = (P0 > 1 ? P0 / 2 : 1);
+    if constexpr (PolyCfg<DEG>::K <= 10) {
+        if (poly_bulk() && (reinterpret_cast<uintptr_t>(pgf) & 7) == 0)
+            return normal_bulk_launch<DEG>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
+    }
     switch (poly_cfg()) {
         case 0: return normal_launch_v<DEG, P0, 2>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
         case 1: return normal_launch_v<DEG, P1, 2>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
@@ -863,7 +1023,7 @@ int polyfit_factor_launch(const double *G, int degree, const double *ctr, const 
                           int drop_const, PolyFactor *F, cudaStream_t st) {
     if (degree < 0 || degree > 8) return SHOPT_E_BADARG;
     const int K = num_terms(degree);
-    const size_t smem = (size_t)6 * K * K * sizeof(double);
+    const size_t smem = ((size_t)7 * K * K + 2 * K) * sizeof(double);
     if (smem > 48 * 1024)
         SHOPT_CUDA_TRY(cudaFuncSetAttribute(factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     factor_kernel<<<1, 32, smem, st>>>(degree, G, ctr, nrows_dev, nrows, drop_const, F);

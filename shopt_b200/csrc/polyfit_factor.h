@@ -29,6 +29,7 @@ constexpr int KMAX = 45;   // degree 8
 struct PolyFactor {
     int K, rc_rank, rank, info;
     int piv[KMAX];
+    int jp[KMAX];             // column permutation of the change-of-basis QR (work space of polyfit_factor)
     double dsc[KMAX];
     double L[KMAX * KMAX];    // [m][k], m in pivoted order
     double W2[KMAX * KMAX];   // [j][i]: c_raw[j] = sum_{i < rc_rank} W2[j][i] y[i]
@@ -41,115 +42,166 @@ SHOPT_HD double binom(int n, int k) {
 }
 SHOPT_HD double ipow_(double x, int n) { double r = 1.0; for (int i = 0; i < n; i++) r *= x; return r; }
 
-// work: 6 K^2 doubles.  G: K x K row-major.  ctr = {u0, 1/su, v0, 1/sv} or null (centred basis == raw basis).
+// work: 7 K^2 + 2 K doubles.  G: K x K row-major.  ctr = {u0, 1/su, v0, 1/sv} or null (centred basis == raw basis).
 // nrows: rows of the design matrix (training stars).  drop_const: solve without the raw constant column (its
 // coefficient comes out 0) -- median_constraint with a zero first column (interpolate.jl:118-124).
+//
+// lane / nl: the routine is written for `nl` cooperating lanes of ONE warp (device: factor_kernel, nl = 32, work in
+// shared memory) or a single caller (host: lane 0 of 1).  Every matrix entry is computed by one lane with the serial
+// code's operations in the serial code's order, so the result does not depend on nl; the lanes only share out the
+// entries and meet at FACTOR_SYNC between phases.  On one thread the K = 21 factorisation took 2.9 ms (12 % of a
+// degree-5 stage step: K^2 entries of the two changes of basis each re-deriving binomials and powers inside a K-term
+// sum); shared out, with the basis maps formed once, it is tens of microseconds.
+#ifdef __CUDA_ARCH__
+#define FACTOR_SYNC() __syncwarp()
+#else
+#define FACTOR_SYNC() ((void)0)
+#endif
 SHOPT_HD void polyfit_factor(int degree, const double *G, const double *ctr, long long nrows, int drop_const, double *work,
-                             PolyFactor *F) {
+                             PolyFactor *F, int lane = 0, int nl = 1) {
     const int K = (degree + 1) * (degree + 2) / 2;
     double *A = work, *T = work + K * K, *M = work + 2 * K * K, *Qm = work + 3 * K * K, *Li = work + 4 * K * K,
-           *Cc = work + 5 * K * K;
-    int tp[KMAX], tq[KMAX], jp[KMAX];
+           *Cc = work + 5 * K * K, *S = work + 6 * K * K, *cn = work + 7 * K * K, *wv = work + 7 * K * K + K;
+    int tp[KMAX], tq[KMAX];
     {
         int k = 0;
         for (int p = 0; p <= degree; p++) for (int q = 0; q <= degree - p; q++) { tp[k] = p; tq[k] = q; k++; }
     }
-    F->K = K; F->info = 0;
     double *L = F->L, *W2 = F->W2, *d = F->dsc;
-    for (int i = 0; i < K * K; i++) { L[i] = 0.0; W2[i] = 0.0; if (!isfinite(G[i])) F->info |= SHOPT_POLY_NONFINITE; }
-    if (ctr) for (int i = 0; i < 4; i++) if (!isfinite(ctr[i])) F->info |= SHOPT_POLY_NONFINITE;
-    if (F->info & SHOPT_POLY_NONFINITE) {
-        for (int i = 0; i < K; i++) { F->piv[i] = i; d[i] = 1.0; L[i * K + i] = 1.0; }
-        for (int i = 0; i < K * K; i++) W2[i] = nan("");
-        F->rc_rank = K; F->rank = 0;
+    int *jp = F->jp;
+    if (lane == 0) { F->K = K; F->info = 0; }
+    FACTOR_SYNC();
+    int bad = 0;
+    for (int i = lane; i < K * K; i += nl) { L[i] = 0.0; W2[i] = 0.0; if (!isfinite(G[i])) bad = 1; }
+    if (ctr) for (int i = 0; i < 4; i++) if (!isfinite(ctr[i])) bad = 1;
+#ifdef __CUDA_ARCH__
+    bad = __any_sync(0xffffffffu, bad);
+#endif
+    if (bad) {
+        FACTOR_SYNC();
+        if (lane == 0) {
+            F->info |= SHOPT_POLY_NONFINITE;
+            for (int i = 0; i < K; i++) { F->piv[i] = i; d[i] = 1.0; L[i * K + i] = 1.0; }
+            for (int i = 0; i < K * K; i++) W2[i] = nan("");
+            F->rc_rank = K; F->rank = 0;
+        }
+        FACTOR_SYNC();
         return;
     }
     // 1. equilibrate
-    for (int i = 0; i < K; i++) { d[i] = (G[i * K + i] > 0.0) ? 1.0 / sqrt(G[i * K + i]) : 0.0; F->piv[i] = i; }
-    for (int i = 0; i < K; i++) for (int j = 0; j < K; j++) A[i * K + j] = G[i * K + j] * d[i] * d[j];
+    for (int i = lane; i < K; i += nl) { d[i] = (G[i * K + i] > 0.0) ? 1.0 / sqrt(G[i * K + i]) : 0.0; F->piv[i] = i; }
+    FACTOR_SYNC();
+    for (int e = lane; e < K * K; e += nl) { const int i = e / K, j = e % K; A[e] = G[e] * d[i] * d[j]; }
+    FACTOR_SYNC();
     // 2. diagonally pivoted Cholesky  A[piv,piv] = L L'
     int rc = 0;
     double minpiv = 1.0;
     for (int k = 0; k < K; k++) {
-        int pv = k;
+        int pv = k;                                       // (every lane finds the same pivot: same reads, same compares)
         for (int i = k + 1; i < K; i++) if (A[F->piv[i] * K + F->piv[i]] > A[F->piv[pv] * K + F->piv[pv]]) pv = i;
-        { const int t = F->piv[k]; F->piv[k] = F->piv[pv]; F->piv[pv] = t; }
-        for (int c = 0; c < k; c++) { const double t = L[k * K + c]; L[k * K + c] = L[pv * K + c]; L[pv * K + c] = t; }
+        FACTOR_SYNC();
+        if (lane == 0) { const int t = F->piv[k]; F->piv[k] = F->piv[pv]; F->piv[pv] = t; }
+        for (int c = lane; c < k; c += nl) { const double t = L[k * K + c]; L[k * K + c] = L[pv * K + c]; L[pv * K + c] = t; }
+        FACTOR_SYNC();
         const int p = F->piv[k];
         const double a = A[p * K + p];
         if (!(a > 1e-13)) break;
         if (a < minpiv) minpiv = a;
         const double l = sqrt(a);
-        L[k * K + k] = l;
-        for (int i = k + 1; i < K; i++) L[i * K + k] = A[F->piv[i] * K + p] / l;
-        for (int i = k + 1; i < K; i++)
-            for (int j = k + 1; j <= i; j++) {
+        if (lane == 0) L[k * K + k] = l;
+        for (int i = k + 1 + lane; i < K; i += nl) L[i * K + k] = A[F->piv[i] * K + p] / l;
+        FACTOR_SYNC();
+        const int mrem = K - k - 1;
+        for (int e = lane; e < mrem * mrem; e += nl) {
+            const int i = k + 1 + e / mrem, j = k + 1 + e % mrem;
+            if (j <= i) {
                 const double v = A[F->piv[i] * K + F->piv[j]] - L[i * K + k] * L[j * K + k];
                 A[F->piv[i] * K + F->piv[j]] = v; A[F->piv[j] * K + F->piv[i]] = v;
             }
+        }
+        FACTOR_SYNC();
         rc++;
     }
-    F->rc_rank = rc;
-    if (minpiv < 1e-8) F->info |= SHOPT_POLY_ILL_CONDITIONED;
-    for (int i = rc; i < K; i++) L[i * K + i] = 1.0;     // keeps the (unused) tail of the forward substitution finite
-    // 3. T: raw monomial kr = (i,j) in centred monomials kc = (p,q)
+    if (lane == 0) {
+        F->rc_rank = rc;
+        if (minpiv < 1e-8) F->info |= SHOPT_POLY_ILL_CONDITIONED;
+    }
+    for (int i = rc + lane; i < K; i += nl) L[i * K + i] = 1.0;     // keeps the (unused) tail of the forward substitution finite
+    // 3. T: raw monomial kr = (i,j) in centred monomials kc = (p,q);  S: its inverse (centred -> raw), used in 6a
     const double u0 = ctr ? ctr[0] : 0.0, su = ctr ? 1.0 / ctr[1] : 1.0, v0 = ctr ? ctr[2] : 0.0, sv = ctr ? 1.0 / ctr[3] : 1.0;
-    for (int kc = 0; kc < K; kc++)
-        for (int kr = 0; kr < K; kr++) {
+    {
+        const double ia = 1.0 / su, ib = -u0 / su, ic = 1.0 / sv, ie = -v0 / sv;
+        for (int e = lane; e < K * K; e += nl) {
+            const int kc = e / K, kr = e % K;
             const int p = tp[kc], q = tq[kc], i = tp[kr], j = tq[kr];
             double t = 0.0;
             if (p <= i && q <= j) t = binom(i, p) * ipow_(su, p) * ipow_(u0, i - p) * binom(j, q) * ipow_(sv, q) * ipow_(v0, j - q);
             if (drop_const && kr == 0) t = 0.0;
             T[kc * K + kr] = t;
+            // S[kr][kc]: coefficient of raw monomial kr = (i, j) in centred monomial kc = (p, q)
+            double sv_ = 0.0;
+            if (i <= p && j <= q) sv_ = binom(p, i) * ipow_(ia, i) * ipow_(ib, p - i) * binom(q, j) * ipow_(ic, j) * ipow_(ie, q - j);
+            S[kr * K + kc] = sv_;
         }
+    }
+    FACTOR_SYNC();
     // 4. M = Rc T,  Rc[i][piv[m]] = L[m][i] / d[piv[m]]
-    for (int i = 0; i < rc; i++)
-        for (int kr = 0; kr < K; kr++) {
-            double s = 0.0;
-            for (int m = i; m < K; m++) {
-                const int c = F->piv[m];
-                if (d[c] != 0.0) s += (L[m * K + i] / d[c]) * T[c * K + kr];
-            }
-            M[i * K + kr] = s;
+    for (int e = lane; e < rc * K; e += nl) {
+        const int i = e / K, kr = e % K;
+        double s = 0.0;
+        for (int m = i; m < K; m++) {
+            const int c = F->piv[m];
+            if (d[c] != 0.0) s += (L[m * K + i] / d[c]) * T[c * K + kr];
         }
+        M[i * K + kr] = s;
+    }
     // 5. column-pivoted Householder QR of M (rc x K); Qm (rc x rc) accumulated explicitly
-    for (int i = 0; i < rc; i++) for (int j = 0; j < rc; j++) Qm[i * K + j] = (i == j) ? 1.0 : 0.0;
-    for (int j = 0; j < K; j++) jp[j] = j;
+    for (int e = lane; e < rc * rc; e += nl) { const int i = e / rc, j = e % rc; Qm[i * K + j] = (i == j) ? 1.0 : 0.0; }
+    for (int j = lane; j < K; j += nl) jp[j] = j;
+    FACTOR_SYNC();
     const int mn = rc < K ? rc : K;
     for (int k = 0; k < mn; k++) {
-        int pv = k; double best = -1.0;
-        for (int j = k; j < K; j++) {
+        for (int j = k + lane; j < K; j += nl) {          // squared norms of the trailing columns
             double s = 0.0;
             for (int i = k; i < rc; i++) s += M[i * K + j] * M[i * K + j];
-            if (s > best) { best = s; pv = j; }
+            cn[j] = s;
         }
+        FACTOR_SYNC();
+        int pv = k; double best = -1.0;
+        for (int j = k; j < K; j++) if (cn[j] > best) { best = cn[j]; pv = j; }
+        FACTOR_SYNC();
         if (pv != k) {
-            for (int i = 0; i < rc; i++) { const double t = M[i * K + k]; M[i * K + k] = M[i * K + pv]; M[i * K + pv] = t; }
-            const int t = jp[k]; jp[k] = jp[pv]; jp[pv] = t;
+            for (int i = lane; i < rc; i += nl) { const double t = M[i * K + k]; M[i * K + k] = M[i * K + pv]; M[i * K + pv] = t; }
+            if (lane == 0) { const int t = jp[k]; jp[k] = jp[pv]; jp[pv] = t; }
         }
+        FACTOR_SYNC();
         double xn = 0.0;
         for (int i = k + 1; i < rc; i++) xn += M[i * K + k] * M[i * K + k];
         const double alpha = M[k * K + k];
-        if (xn == 0.0) continue;                          // H = I
+        if (xn == 0.0) continue;                          // H = I   (uniform: every lane read the same column)
         const double beta = -copysign(sqrt(alpha * alpha + xn), alpha);
         const double tau = (beta - alpha) / beta, sc = 1.0 / (alpha - beta);
-        for (int i = k + 1; i < rc; i++) M[i * K + k] *= sc;   // v (v[k] = 1 implicit)
-        M[k * K + k] = beta;
-        for (int j = k + 1; j < K; j++) {
+        FACTOR_SYNC();
+        for (int i = k + 1 + lane; i < rc; i += nl) M[i * K + k] *= sc;   // v (v[k] = 1 implicit)
+        if (lane == 0) M[k * K + k] = beta;
+        FACTOR_SYNC();
+        for (int j = k + 1 + lane; j < K; j += nl) {
             double w = M[k * K + j];
             for (int i = k + 1; i < rc; i++) w += M[i * K + k] * M[i * K + j];
             w *= tau;
             M[k * K + j] -= w;
             for (int i = k + 1; i < rc; i++) M[i * K + j] -= w * M[i * K + k];
         }
-        for (int r = 0; r < rc; r++) {                    // Qm <- Qm H
+        for (int r = lane; r < rc; r += nl) {             // Qm <- Qm H
             double w = Qm[r * K + k];
             for (int i = k + 1; i < rc; i++) w += Qm[r * K + i] * M[i * K + k];
             w *= tau;
             Qm[r * K + k] -= w;
             for (int i = k + 1; i < rc; i++) Qm[r * K + i] -= w * M[i * K + k];
         }
-        for (int i = k + 1; i < rc; i++) M[i * K + k] = 0.0;
+        FACTOR_SYNC();
+        for (int i = k + 1 + lane; i < rc; i += nl) M[i * K + k] = 0.0;
+        FACTOR_SYNC();
     }
     // numerical rank, the oracle's / LAPACK's rule on the diagonal of R
     const long long mnr = nrows < (long long)K ? nrows : (long long)K;
@@ -157,12 +209,15 @@ SHOPT_HD void polyfit_factor(int degree, const double *G, const double *ctr, lon
     int rank = 0;
     const double r11 = mn > 0 ? fabs(M[0]) : 0.0;
     if (r11 != 0.0) for (rank = 1; rank < mn; rank++) if (!(fabs(M[rank * K + rank]) > rcond * r11)) break;
-    F->rank = rank;
-    if (rank < K && !drop_const) F->info |= SHOPT_POLY_RANK_DEFICIENT;
+    if (lane == 0) {
+        F->rank = rank;
+        if (rank < K && !drop_const) F->info |= SHOPT_POLY_RANK_DEFICIENT;
+    }
     if (rank == K && rc == K && !drop_const) {
         // 6a. W2 = S D Pi L^-T
-        for (int i = 0; i < K * K; i++) Li[i] = 0.0;
-        for (int c = 0; c < K; c++) {                     // Li = L^-1, column by column
+        for (int i = lane; i < K * K; i += nl) Li[i] = 0.0;
+        FACTOR_SYNC();
+        for (int c = lane; c < K; c += nl) {              // Li = L^-1, one column per lane
             Li[c * K + c] = 1.0 / L[c * K + c];
             for (int i = c + 1; i < K; i++) {
                 double s = 0.0;
@@ -170,36 +225,45 @@ SHOPT_HD void polyfit_factor(int degree, const double *G, const double *ctr, lon
                 Li[i * K + c] = s / L[i * K + i];
             }
         }
-        for (int m = 0; m < K; m++) for (int i = 0; i < K; i++) Cc[F->piv[m] * K + i] = (i >= m) ? d[F->piv[m]] * Li[i * K + m] : 0.0;
-        const double a = 1.0 / su, b = -u0 / su, c = 1.0 / sv, e = -v0 / sv;
-        for (int kr = 0; kr < K; kr++)
-            for (int i = 0; i < K; i++) {
-                double s = 0.0;
-                for (int kc = 0; kc < K; kc++) {
-                    const int ii = tp[kr], jj = tq[kr], p = tp[kc], q = tq[kc];
-                    if (ii <= p && jj <= q)
-                        s += binom(p, ii) * ipow_(a, ii) * ipow_(b, p - ii) * binom(q, jj) * ipow_(c, jj) * ipow_(e, q - jj) * Cc[kc * K + i];
-                }
-                W2[kr * K + i] = s;
+        FACTOR_SYNC();
+        for (int e = lane; e < K * K; e += nl) {
+            const int m = e / K, i = e % K;
+            Cc[F->piv[m] * K + i] = (i >= m) ? d[F->piv[m]] * Li[i * K + m] : 0.0;
+        }
+        FACTOR_SYNC();
+        for (int e = lane; e < K * K; e += nl) {
+            const int kr = e / K, i = e % K;
+            double s = 0.0;
+            for (int kc = 0; kc < K; kc++) {
+                const int ii = tp[kr], jj = tq[kr], p = tp[kc], q = tq[kc];
+                if (ii <= p && jj <= q) s += S[kr * K + kc] * Cc[kc * K + i];
             }
+            W2[kr * K + i] = s;
+        }
+        FACTOR_SYNC();
         return;
     }
-    if (rank == 0) return;
+    if (rank == 0) { FACTOR_SYNC(); return; }
     // 6b. W2 = Pm R1'(R1 R1')^-1 Qm1'
     double *Gm = Li;                                       // rank x rank, lower Cholesky in place
-    for (int a = 0; a < rank; a++)
-        for (int b = 0; b <= a; b++) {
+    for (int e = lane; e < rank * rank; e += nl) {
+        const int a = e / rank, b = e % rank;
+        if (b <= a) {
             double s = 0.0;
             for (int j = a; j < K; j++) s += M[a * K + j] * M[b * K + j];
             Gm[a * K + b] = s;
         }
-    for (int a = 0; a < rank; a++)
-        for (int b = 0; b <= a; b++) {
-            double s = Gm[a * K + b];
-            for (int t = 0; t < b; t++) s -= Gm[a * K + t] * Gm[b * K + t];
-            Gm[a * K + b] = (a == b) ? sqrt(s) : s / Gm[b * K + b];
-        }
-    for (int i = 0; i < rc; i++) {
+    }
+    FACTOR_SYNC();
+    if (lane == 0)
+        for (int a = 0; a < rank; a++)
+            for (int b = 0; b <= a; b++) {
+                double s = Gm[a * K + b];
+                for (int t = 0; t < b; t++) s -= Gm[a * K + t] * Gm[b * K + t];
+                Gm[a * K + b] = (a == b) ? sqrt(s) : s / Gm[b * K + b];
+            }
+    FACTOR_SYNC();
+    for (int i = lane; i < rc; i += nl) {
         double cc[KMAX];
         for (int a = 0; a < rank; a++) { double s = Qm[i * K + a]; for (int t = 0; t < a; t++) s -= Gm[a * K + t] * cc[t]; cc[a] = s / Gm[a * K + a]; }
         for (int a = rank - 1; a >= 0; a--) { double s = cc[a]; for (int t = a + 1; t < rank; t++) s -= Gm[t * K + a] * cc[t]; cc[a] = s / Gm[a * K + a]; }
@@ -209,6 +273,8 @@ SHOPT_HD void polyfit_factor(int degree, const double *G, const double *ctr, lon
             W2[jp[j] * K + i] = s;
         }
     }
+    (void)wv;
+    FACTOR_SYNC();
 }
 
 // coefficients of one right-hand side b = Vc'z through the factorisation (what solve_kernel does per pixel)
