@@ -399,6 +399,11 @@ int64_t shopt_training_split_sharded_host(const int32_t *flags_local, int64_t n_
                                           void *user, int64_t *train_idx_out, uint32_t *train_pos_out, int64_t *counts_out);
 int64_t shopt_select_worst_sharded_host(const double *err_local, const uint32_t *pos_local, int64_t n_local, int64_t m,
                                         shopt_host_allreduce_fn allreduce, void *user, uint8_t *reject_out);
+/* per-pixel median(filter(!isnan, z)) (interpolate.jl:119,128,140) over the training stars of EVERY rank: z_local
+ * (n_local, npx) row-major; med_out (npx), identical on every rank.  Radix select with a 256-bin histogram exchange per
+ * pass, the protocol of the sharded stage's median_constraint / NaN -> median repair (csrc/polyfit.cu shard_med_*). */
+int shopt_median_sharded_host(const double *z_local, int64_t n_local, int64_t npx, shopt_host_allreduce_fn allreduce,
+                              void *user, double *med_out);
 
 /* device-resident shard; comm == NULL runs a single GPU.  Blocks until the stage is done; the control flow between
  * the kernels (survivor counts, training split, worst_10_percent, list compaction) runs on the device, the call

@@ -135,6 +135,7 @@ SIGNATURES = {
                                                       C.POINTER(C.c_uint32), lp]),
     "shopt_select_worst_sharded_host": (C.c_int64, [dp, C.POINTER(C.c_uint32), C.c_int64, C.c_int64, vp, vp,
                                                     C.POINTER(C.c_uint8)]),
+    "shopt_median_sharded_host": (C.c_int, [dp, C.c_int64, C.c_int64, vp, vp, dp]),
     "shopt_stage_run_dev": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO), C.c_void_p, C.c_void_p, C.c_void_p]),
     "shopt_stage_run": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO)]),
     "shopt_stage_run_comm": (C.c_int, [C.POINTER(Params), C.POINTER(StageIO), C.c_void_p, C.c_void_p]),

@@ -3,7 +3,8 @@
 // the single-process training split (shopt.jl:472-478) and rejection sequence (shopt.jl:513-520, 557-575), including
 // the stable tie order.  Same order relations (select_core.h), same messages as the device path:
 //   split:   N_global / 32 words of survivor bits along the permutation + 3 counters, one sum-all-reduce;
-//   select:  8 radix passes, each one sum-all-reduce of a 4096-bin histogram.
+//   select:  8 radix passes, each one sum-all-reduce of a 4096-bin histogram;
+//   median:  per pixel, 2 x 8 radix passes of 256 bins (lower and upper middle order statistic; polyfit.cu shard_med_*).
 #include <cmath>
 #include <cstring>
 #include <vector>
@@ -92,6 +93,60 @@ int64_t shopt_select_worst_sharded_host(const double *err_local, const uint32_t 
         nrej += !keep;
     }
     return nrej;
+}
+
+// median(filter(!isnan, z)) of interpolate.jl:119,128,140 per pixel when the training stars are sharded: z_local is this
+// rank's (n_local, npx) block, row-major (star, pixel).  Every rank returns the same med_out (npx): NaN for a pixel
+// without finite values, Statistics.middle(v1, v2) = v1/2 + v2/2 for an even count.  The exchange is one int32
+// sum-all-reduce of npx x 256 histogram bins per pass, 16 passes: what polyfit_median_sharded_launch does on the device.
+int shopt_median_sharded_host(const double *z_local, int64_t n_local, int64_t npx, shopt_host_allreduce_fn allreduce, void *user,
+                              double *med_out) {
+    if (n_local < 0 || npx < 0 || (npx > 0 && !med_out) || (n_local > 0 && npx > 0 && !z_local)) return SHOPT_E_BADARG;
+    auto order_key = [](double z) {
+        unsigned long long b; std::memcpy(&b, &z, 8);
+        return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+    };
+    auto key_value = [](unsigned long long k) {
+        const unsigned long long b = (k >> 63) ? (k & 0x7fffffffffffffffULL) : ~k;
+        double z; std::memcpy(&z, &b, 8); return z;
+    };
+    std::vector<unsigned long long> prefix((size_t)2 * npx, 0ULL);
+    std::vector<uint32_t> kleft((size_t)2 * npx, 0u), total((size_t)npx, 0u), hist((size_t)npx * 256);
+    for (int which = 0; which < 2; which++)
+        for (int pass = 0; pass < 8; pass++) {
+            const int shift = 56 - 8 * pass;
+            std::fill(hist.begin(), hist.end(), 0u);
+            for (int64_t t = 0; t < n_local; t++)
+                for (int64_t px = 0; px < npx; px++) {
+                    const double z = z_local[(size_t)t * npx + px];
+                    if (std::isnan(z)) continue;
+                    const unsigned long long key = order_key(z), pre = prefix[(size_t)which * npx + px];
+                    if (pass == 0 || (key >> (shift + 8)) == (pre >> (shift + 8))) hist[(size_t)px * 256 + ((key >> shift) & 255ULL)]++;
+                }
+            if (allreduce && npx > 0 && allreduce(hist.data(), npx * 256, 1, user) != 0) return SHOPT_E_CUDA;
+            for (int64_t px = 0; px < npx; px++) {
+                const uint32_t *h = &hist[(size_t)px * 256];
+                uint32_t k = kleft[(size_t)which * npx + px];
+                if (pass == 0) {
+                    uint32_t tot = 0;
+                    for (int b = 0; b < 256; b++) tot += h[b];
+                    total[(size_t)px] = tot;
+                    k = tot ? (which ? tot / 2 : (tot - 1) / 2) : 0;
+                }
+                uint32_t cum = 0;
+                for (int b = 0; b < 256; b++) {
+                    if (cum + h[b] > k) { prefix[(size_t)which * npx + px] |= (unsigned long long)b << shift; k -= cum; break; }
+                    cum += h[b];
+                }
+                kleft[(size_t)which * npx + px] = k;
+            }
+        }
+    for (int64_t px = 0; px < npx; px++) {
+        if (!total[(size_t)px]) { med_out[px] = std::nan(""); continue; }
+        const double v1 = key_value(prefix[(size_t)px]), v2 = key_value(prefix[(size_t)npx + px]);
+        med_out[px] = (total[(size_t)px] & 1u) ? v1 : v1 / 2 + v2 / 2;
+    }
+    return SHOPT_OK;
 }
 
 }  // extern "C"

@@ -162,3 +162,65 @@ def test_shard_bounds_cover_and_split_rule():
     assert len(pipeline.training_split(np.zeros(7, np.int32), np.arange(7), 0.5)) == 4
     flags = np.array([0, 1, 0, 2, 4, 0, 8, 16], np.int32)                 # bits 8/16 (training/rejected) do not exclude
     assert pipeline.training_split(flags, np.arange(8)[::-1].copy(), 1.0).tolist() == [7, 6, 5, 2, 0]
+
+
+# ---- per-pixel median across shards (median_constraint / NaN -> median repair, interpolate.jl:118-130) -----------------
+def median_inputs(n, npx):
+    rng = np.random.default_rng(7)
+    z = np.round(rng.normal(size=(n, npx)), 1)            # many exact ties
+    z[rng.uniform(size=z.shape) < 0.05] = np.nan
+    z[:, 0] = np.nan                                      # a pixel without a finite value: median NaN
+    z[:, 1] = 0.25                                        # a constant pixel
+    z[: n // 2, 2] = -0.0                                 # signed zeros order below +0
+    z[n // 2:, 2] = 0.0
+    z[:, 3] = np.where(np.arange(n) % 2 == 0, -3.0, 5.0)  # even count, distinct middles -> v1/2 + v2/2
+    return z
+
+
+def median_worker(rank, world, port, n, npx, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        z = median_inputs(n, npx)
+        a, b = pipeline.shard_bounds(n, world, rank)
+        cb = host_allreduce()
+        zl = np.ascontiguousarray(z[a:b])
+        med = np.zeros(npx)
+        rc = _lib.lib().shopt_median_sharded_host(zl.ctypes.data_as(_lib.dp), b - a, npx, C.cast(cb, C.c_void_p), None,
+                                                  med.ctypes.data_as(_lib.dp))
+        q.put((rank, rc, med))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n", [(2, 200), (3, 201)])
+def test_sharded_median_matches_numpy(world, n):
+    npx = 40
+    z = median_inputs(n, npx)
+    with np.errstate(all="ignore"):
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            want = np.nanmedian(z, axis=0)                # numpy: mean of the two middle values = v1/2 + v2/2 here
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=median_worker, args=(r, world, port, n, npx, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, rc, med in res:
+        assert rc == 0
+        assert np.isnan(med[0]) and med[1] == 0.25 and med[3] == (1.0 if n % 2 == 0 else -3.0)
+        assert np.array_equal(np.isnan(med), np.isnan(want))
+        ok = ~np.isnan(want)
+        assert np.array_equal(med[ok], want[ok]), (rank, np.abs(med[ok] - want[ok]).max())
+    assert all(np.array_equal(res[0][2], r[2], equal_nan=True) for r in res)      # identical on every rank
+    # and a world of one (no exchange) gives the same numbers
+    med1 = np.zeros(npx)
+    assert _lib.lib().shopt_median_sharded_host(np.ascontiguousarray(z).ctypes.data_as(_lib.dp), n, npx, None, None,
+                                                med1.ctypes.data_as(_lib.dp)) == 0
+    assert np.array_equal(med1, res[0][2], equal_nan=True)
