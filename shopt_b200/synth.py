@@ -68,8 +68,6 @@ def make_catalog(N, r, n_a, seed=SEED, noise=1e-5, device="cpu", chunk=2048, fra
         if frac_contaminated > 0:
             cont = torch.rand(b - a, generator=g, device=dev, dtype=f64) < frac_contaminated
             off = (torch.rand(b - a, 2, generator=g, device=dev, dtype=f64) - 0.5) * 12.0
-            for axis_c in (0,):
-                pass
             st2 = torch.zeros_like(st)
             idx = torch.nonzero(cont).flatten()
             for j in idx.tolist():
