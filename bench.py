@@ -425,7 +425,7 @@ def stage_breakdown(args, p, cat, pgf, out):
         return res
     t = timed(lambda: _lib.check(L.shopt_pca_batch_dev(cat["stamps"].data_ptr(), r, r, n, p.pca_terms, p.pratio, p.lanczos,
                                                        p.unity_sum, pgf.data_ptr(), ist[0].data_ptr(), ist[1].data_ptr(), st)))
-    res["pca_kernel"] = {"ms": t, "bytes": 2 * 8 * rc * n, "gbs": 2 * 8 * rc * n / t / 1e6, "per_step": 1}
+    res["pca_power_kernel(+pca_kernel)"] = {"ms": t, "bytes": 2 * 8 * rc * n, "gbs": 2 * 8 * rc * n / t / 1e6, "per_step": 1}
     t = timed(lambda: fit(pgf, cat["x0_learned"], p.g_tol_learned))
     res["fit_kernel(learned)"] = {"ms": t, "bytes": fit_bytes, "gbs": fit_bytes / t / 1e6, "per_step": 1}
     train = torch.nonzero(out["flags"] & _lib.FLAG_TRAINING).flatten().contiguous()

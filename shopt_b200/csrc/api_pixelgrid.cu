@@ -30,7 +30,7 @@ int shopt_pca_batch_dev(const double *d_stamps, int r, int c, int64_t N, int nco
                         int unity_sum, double *d_pgf, int32_t *d_k_out, int32_t *d_status, void *stream) {
     if (!d_stamps || !d_pgf || r < 1 || c < 2 || N < 0 || ncomp < 1) return SHOPT_E_BADARG;
     Ctx *ctx; TRY(get_ctx(&ctx));
-    TRY(ctx->need_scratch(pca_scratch_bytes(r, c, ncomp)));
+    TRY(ctx->need_scratch(pca_scratch_bytes(r, c, ncomp, (long long)N)));
     return pca_launch(d_stamps, r, c, (long long)N, ncomp, pratio, lanczos_a, unity_sum, d_pgf, d_k_out, d_status,
                       ctx->next_counter(), (double *)ctx->scratch, ctx->scratch_bytes, (cudaStream_t)stream);
 }
@@ -43,7 +43,7 @@ int shopt_pca_batch(const double *stamps, int r, int c, int64_t N, int ncomp, do
     const size_t rc = (size_t)r * c, n = (size_t)N;
     DevBuf din, dout, dint;
     TRY(din.alloc(n * rc * 8)); TRY(dout.alloc(n * rc * 8)); TRY(dint.alloc(n * 8));
-    TRY(ctx->need_scratch(pca_scratch_bytes(r, c, ncomp)));
+    TRY(ctx->need_scratch(pca_scratch_bytes(r, c, ncomp, (long long)N)));
     cudaStream_t st = ctx->stream;
     SHOPT_CUDA_TRY(cudaEventRecord(ctx->ev[0], st));
     SHOPT_CUDA_TRY(cudaMemcpyAsync(din.p, stamps, n * rc * 8, cudaMemcpyHostToDevice, st));

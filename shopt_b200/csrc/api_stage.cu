@@ -180,7 +180,7 @@ static int stage_check_args(const shopt_params *p, const shopt_stage_io *io) {
     return SHOPT_OK;
 }
 static size_t stage_scratch_bytes(const shopt_params *p, const shopt_stage_io *io) {
-    return std::max(p->mode == SHOPT_MODE_PCA ? pca_scratch_bytes(io->r, io->c, p->pca_terms) : (size_t)0,
+    return std::max(p->mode == SHOPT_MODE_PCA ? pca_scratch_bytes(io->r, io->c, p->pca_terms, io->n_local) : (size_t)0,
                     polyfit_scratch_bytes((long long)io->r * io->c, io->n_local, p->degree));
 }
 

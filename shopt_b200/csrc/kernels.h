@@ -72,7 +72,22 @@ int uv_centre_launch(const double *u, const double *v, long long n, double *sums
                      cudaStream_t st);
 
 // pixelgrid.cu  (scratch: pca_scratch_bytes(r, c, ncomp), 0 when the stamp fits shared memory)
-size_t pca_scratch_bytes(int r, int c, int ncomp);
+size_t pca_scratch_bytes(int r, int c, int ncomp, long long N);
+// pca_power.cu: stage 1 of the PCA pixel-grid fit (stars whose reconstruction has one component)
+struct PcaPowerArgs {
+    const double *stamps;
+    int r, c;
+    long long N;
+    double pratio;
+    int lanczos_a, unity_sum;
+    double *pgf;
+    int *k_out, *status;
+    unsigned long long *counter;        // work counter (zeroed by the launch)
+    long long *defer_list;              // stars handed over to pca_kernel ...
+    unsigned long long *defer_count;    // ... and how many (zeroed by the launch)
+    double kz[15];                      // 1-D lanczos factor (2a+1 taps)
+};
+int pca_power_launch(const PcaPowerArgs &a, cudaStream_t st);
 int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, double pratio, int lanczos_a, int unity_sum,
                double *d_pgf, int *d_k, int *d_status, unsigned long long *d_counter, double *scratch,
                size_t scratch_bytes, cudaStream_t st);

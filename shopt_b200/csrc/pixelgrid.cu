@@ -44,6 +44,8 @@ struct PcaArgs {
     int debug;            // status |= (subspace iterations used by the fast path; 100 direct path, 200 Jacobi) << 8
     double *eigscratch;   // non-null: per-CTA global scratch (eigstride doubles: Gram matrix + reflectors) of the direct path
     size_t eigstride;
+    const long long *list;              // non-null: the stars to process are list[0 .. *nlist) (what pca_power_kernel
+    const unsigned long long *nlist;    //   left over); null: stars 0 .. N-1
     double kern[15 * 15]; // normalised lanczos kernel (2a+1)^2, a <= 7, column-major like the reference's
     double kz[15];        // its 1-D factor: kern = kz (x) kz / sum
 };
@@ -697,11 +699,13 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
     double *FQ = Y, *FQn = FQ + FB * ldq, *FT = FQn + FB * ldq, *FG = FT + FB * c;
     int buf = 0;
 
+    const long long ntot = a.list ? (long long)*a.nlist : a.N;
     if (tid == 0) *s_next = (long long)atomicAdd(a.counter, 1ULL);
     for (;;) {
         __syncthreads();
-        const long long star = *s_next;
-        if (star >= a.N) break;
+        const long long work = *s_next;                          // position in the work list
+        if (work >= ntot) break;
+        const long long star = a.list ? a.list[work] : work;
         __syncthreads();                                         // everyone has read s_next before it is replaced
         // the next star's index is fetched now and published at the end of this one: the atomic's latency is hidden
         long long nxt = 0;
@@ -875,8 +879,9 @@ __global__ void __launch_bounds__(NW * 32, 1) pca_kernel(const PcaArgs a) {
         }
         if (prof && tid == 0) prof[10] = clock64();
         // the next star's stamp starts its way into L2 now (one bulk prefetch); its load phase then hits L2
-        if (tid == 0 && nxt < a.N && !(a.debug & 2)) {
-            const uintptr_t p0 = (uintptr_t)(a.stamps + nxt * rc), p1 = (uintptr_t)(a.stamps + (nxt + 1) * rc);
+        if (tid == 0 && nxt < ntot && !(a.debug & 2)) {
+            const long long nstar = a.list ? a.list[nxt] : nxt;
+            const uintptr_t p0 = (uintptr_t)(a.stamps + nstar * rc), p1 = (uintptr_t)(a.stamps + (nstar + 1) * rc);
             const uintptr_t lo = p0 & ~(uintptr_t)15, hi = p1 & ~(uintptr_t)15;      // stays inside the batch
             if (hi > lo)
                 asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(lo), "r"((uint32_t)(hi - lo)) : "memory");
@@ -1197,13 +1202,16 @@ static size_t pca_w_doubles(int r, int c, int kmax) {      // W plus the region 
     return (size_t)r * c + (y > f ? y : f);
 }
 #ifndef SHOPT_PCA_RT
-size_t pca_scratch_bytes(int r, int c, int ncomp) {
+static size_t pca_heavy_scratch_bytes(int r, int c, int ncomp) {
     int kmax = ncomp < r ? ncomp : r; if (c < kmax) kmax = c; if (kmax < 1) kmax = 1;
     const size_t wdoubles = pca_w_doubles(r, c, kmax);
     if (pca_fixed_smem(32, r, c, kmax) + wdoubles * 8 <= 227 * 1024)
         return (r <= c && r >= 16) ? (size_t)sm_count() * 2 * r * r * 8 : 0;       // direct path: Gram matrix + reflectors
     return (size_t)sm_count() * wdoubles * 8;
 }
+// work list of the stars pca_power_kernel hands over (N indices) + its two counters, in front of pca_kernel's scratch
+static size_t pca_list_bytes(long long N) { return N > 0 ? (((size_t)N * 8 + 64 + 255) & ~(size_t)255) : 0; }
+size_t pca_scratch_bytes(int r, int c, int ncomp, long long N) { return pca_list_bytes(N) + pca_heavy_scratch_bytes(r, c, ncomp); }
 #endif
 
 template <int NW, int RT>
@@ -1294,6 +1302,28 @@ int pca_launch(const double *d_stamps, int r, int c, long long N, int ncomp, dou
     a.fast = (getenv("SHOPT_PCA_NO_FAST") == nullptr);
     a.debug = getenv("SHOPT_PCA_DEBUG") ? atoi(getenv("SHOPT_PCA_DEBUG")) : 0;   // 1: report iterations, 2: no L2 prefetch, 4: eig8 small-pair cut on, 8: first acceptance check after 2 iterations, 16: print cycles per phase, 32: no power path, 64: masked stars try the fast paths too
     if (lanczos_a > 0) lanczos_kernel2d(lanczos_a, a.kern, a.kz);
+    a.list = nullptr; a.nlist = nullptr;
+    // ---- stage 1: one-component stars by pca_power_kernel (pca_power.cu: no shared-memory copy of the stamp, several
+    //      stars in flight per SM); what it does not accept lands on a work list that pca_kernel then serves ----
+    const size_t lb = pca_list_bytes(N);
+    if (a.fast && a.debug == 0 && !getenv("SHOPT_PCA_NO_LIGHT") && r >= 2 * FB && c >= 2 * FB && scratch &&
+        scratch_bytes >= lb + pca_heavy_scratch_bytes(r, c, ncomp)) {
+        PcaPowerArgs pa;
+        pa.stamps = d_stamps; pa.r = r; pa.c = c; pa.N = N; pa.pratio = pratio; pa.lanczos_a = lanczos_a; pa.unity_sum = unity_sum;
+        pa.pgf = d_pgf; pa.k_out = d_k; pa.status = d_status;
+        pa.defer_list = reinterpret_cast<long long *>(scratch);
+        pa.counter = reinterpret_cast<unsigned long long *>(pa.defer_list + N);
+        pa.defer_count = pa.counter + 1;
+        for (int i = 0; i < 15; i++) pa.kz[i] = lanczos_a > 0 ? a.kz[i] : 0.0;
+        const int rcl = pca_power_launch(pa, st);
+        if (rcl == SHOPT_OK) {
+            a.list = pa.defer_list; a.nlist = pa.defer_count;
+            scratch = reinterpret_cast<double *>(reinterpret_cast<char *>(scratch) + lb);
+            scratch_bytes -= lb;
+        } else if (rcl != SHOPT_E_UNSUPPORTED) {
+            return rcl;
+        }
+    }
     const int rt = ((r > c ? r : c) + 31) / 32;
     switch (rt) {
         case 1: return pca_launch_rt1(a, scratch, scratch_bytes, st);
