@@ -247,6 +247,7 @@ struct EvalShared {
     int n_a, pitch, TV, m0, rodd, plane, have_last, cmd;
     int newstar, parity;               // first evaluation of a star: the workers look at the crop's mbarrier phase too
     int profile;                       // SHOPT_PROFILE_GAUSSIAN / _KOLMOGOROV
+    int sym;                           // pass A over pixel pairs (SHOPT_FIT_SYM=0: every pixel on its own)
 };
 struct FG {
     double f, g0, g1, g2;
@@ -412,7 +413,70 @@ __device__ __forceinline__ void eval_pixels(int slot) {
     const int inc0 = TV * pitch * 8 + ((((m0 + tv * rodd) & 1) == 0) ? flip : -flip), incsum = 2 * TV * pitch * 8;
     // pass A: profile moments over ALL pixels (analyticLBFGS.jl:24-34)
     double S0 = 0.0, S1 = 0.0, S2 = 0.0;
-    if (active) {
+    double E0 = 0.0, E1 = 0.0, E2 = 0.0, E3 = 0.0;                 // pixels this thread serves outside its own row (below)
+    if (tame && plane && es.sym) {
+        // The profile is symmetric under the point reflection about its centre (n_a/2, n_a/2):
+        //     pixel (ui, vi) <-> (n_a-2-ui, n_a-2-vi)  has  du -> -du, dv -> -dv,  c1 -> -c1,  hence the SAME exponent bits,
+        // and the products the moments are made of (f, f du^2, f du dv, f dv^2) are even under it.  So the exp of a
+        // pixel pair is evaluated once, stored to both places of the plane (pass B needs f everywhere: the data are not
+        // symmetric) and counted twice.  Only row n_a-1 and column n_a-1 have no partner inside the window: those
+        // 2 n_a - 1 pixels are shared out one per thread, whatever row the thread owns, and enter the reduction with
+        // their own du, dv.  Pass A drops from n_a^2 to ~n_a^2 / 2 + 2 n_a exps and moment updates.
+        const int nm2 = n_a - 2;
+        if (active && tu < n_a - 1) {
+            const int up = nm2 - tu;                                  // partner row
+            double T0 = 0.0, T1 = 0.0, T2 = 0.0;
+            int vi = tv;
+            double dv = dv0;
+            for (; 2 * (vi + 3 * TV) < nm2; vi += 4 * TV) {           // four pairs at a time
+                double dvj[4], fv[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) { dvj[j] = dv; dv += step; }
+#pragma unroll
+                for (int j = 0; j < 4; j++) fv[j] = exp_profile(-fma(dvj[j], fma(cc, dvj[j], c1), c0), tab);
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int v1 = vi + j * TV, v2 = nm2 - v1;
+                    sts_f64(fbuf_s + (uint32_t)((v1 * pitch + ((m0 + v1 * rodd) & 1) + tu) * 8), fv[j]);
+                    sts_f64(fbuf_s + (uint32_t)((v2 * pitch + ((m0 + v2 * rodd) & 1) + up) * 8), fv[j]);
+                    const double fd = fv[j] * dvj[j];
+                    T0 += fv[j];
+                    T1 += fd;
+                    T2 = fma(fd, dvj[j], T2);
+                }
+            }
+            for (; 2 * vi < nm2; vi += TV, dv += step) {
+                const double fv = exp_profile(-fma(dv, fma(cc, dv, c1), c0), tab);
+                const int v2 = nm2 - vi;
+                sts_f64(fbuf_s + (uint32_t)((vi * pitch + ((m0 + vi * rodd) & 1) + tu) * 8), fv);
+                sts_f64(fbuf_s + (uint32_t)((v2 * pitch + ((m0 + v2 * rodd) & 1) + up) * 8), fv);
+                const double fd = fv * dv;
+                T0 += fv;
+                T1 += fd;
+                T2 = fma(fd, dv, T2);
+            }
+            S0 = 2.0 * T0; S1 = 2.0 * T1; S2 = 2.0 * T2;
+            if (2 * vi == nm2 && tu <= up) {                          // the column that is its own partner (n_a even): rows pair up
+                const double fv = exp_profile(-fma(dv, fma(cc, dv, c1), c0), tab);
+                const double w = (tu == up) ? 1.0 : 2.0;
+                sts_f64(fbuf_s + (uint32_t)((vi * pitch + ((m0 + vi * rodd) & 1) + tu) * 8), fv);
+                if (tu != up) sts_f64(fbuf_s + (uint32_t)((vi * pitch + ((m0 + vi * rodd) & 1) + up) * 8), fv);
+                const double fd = (w * fv) * dv;
+                S0 += w * fv;
+                S1 += fd;
+                S2 = fma(fd, dv, S2);
+            }
+        }
+        const int e = threadIdx.x;
+        if (e < 2 * n_a - 1) {                                        // the unpaired row and column
+            const int ui = e < n_a ? n_a - 1 : e - n_a, vi = e < n_a ? e : n_a - 1;
+            const double pdu = (double)(ui + 1) - n_a / 2.0, pdv = (double)(vi + 1) - n_a / 2.0;
+            const double pc0 = (MS * qa) * (pdu * pdu), pc1 = (MS * qb) * pdu;
+            const double fv = exp_profile(-fma(pdv, fma(cc, pdv, pc1), pc0), tab);
+            sts_f64(fbuf_s + (uint32_t)((vi * pitch + ((m0 + vi * rodd) & 1) + ui) * 8), fv);
+            E0 = fv; E1 = fv * (pdu * pdu); E2 = fv * (pdu * pdv); E3 = fv * (pdv * pdv);
+        }
+    } else if (active) {
         double dv = dv0;
         uint32_t o = o0;
         int inc = inc0;
@@ -449,7 +513,7 @@ __device__ __forceinline__ void eval_pixels(int slot) {
         }
     }
     {   // sum f, sum f du^2, sum f du dv, sum f dv^2
-        const double k = warp_reduce4(S0, (du * du) * S0, du * S1, S2);
+        const double k = warp_reduce4(S0 + E0, (du * du) * S0 + E1, du * S1 + E2, S2 + E3);
         if ((lane & 7) == 0) scrA[warp * 4 + (lane >> 3)] = k;
     }
     bar_eval<THREADS>(slot);
@@ -934,6 +998,7 @@ struct FitArgs {
     int nbuf, pitch, plane;
     double *f_out, *g_out;         // non-null: evaluate cost / gradient at x0 only (cost, g! of analyticLBFGS.jl)
     int profile;                   // 0: fGaussian (radialProfiles.jl:5-9), 1: fkolmogorov (:16-24)
+    int sym;
 };
 
 // Issue the bulk copies of one star's crop (thread 0 only).  A column whose 16-byte-aligned superset would
@@ -1020,7 +1085,7 @@ __global__ void __launch_bounds__(THREADS + 32 * NSLOT, MINB) fit_kernel(const F
             es.crop_s = smem_u32(crop); es.fbuf_s = smem_u32(fplane); es.tab_s = smem_u32(exp_tab);
             es.n_a = a.n_a; es.pitch = a.pitch; es.TV = THREADS / a.n_a;      // n_a <= THREADS (checked at launch)
             es.m0 = (int)((base + mis0) & 1); es.rodd = a.r & 1; es.plane = a.plane;
-            es.have_last = 0; es.cmd = 0; es.newstar = 1; es.parity = (int)phase; es.profile = a.profile;
+            es.have_last = 0; es.cmd = 0; es.newstar = 1; es.parity = (int)phase; es.profile = a.profile; es.sym = a.sym;
         }
         mbar_wait(&bars[slot], phase);
         phase ^= 1u;
@@ -1112,6 +1177,8 @@ int fit_analytic_launch(const double *d_stamps, int r, int c, long long N, int n
     a.stamps = d_stamps; a.r = r; a.c = c; a.n_a = n_a; a.N = N; a.x0 = d_x0; a.g_tol = g_tol; a.max_iter = max_iter;
     a.s = d_s; a.g1 = d_g1; a.g2 = d_g2; a.status = d_status; a.iters = d_iters; a.counter = d_counter;
     a.nbuf = 2; a.pitch = 0; a.plane = 1; a.f_out = d_f; a.g_out = d_g; a.profile = profile;
+    static const int sym = getenv("SHOPT_FIT_SYM") ? atoi(getenv("SHOPT_FIT_SYM")) : 1;   // measurement switch
+    a.sym = sym;
     if (n_a <= 32) return launch_fit<128, 4, 6>(a, stream);
     if (n_a <= 80) return launch_fit<256, 2, 3>(a, stream);
     if (n_a <= 160) return launch_fit<512, 1, 1>(a, stream);

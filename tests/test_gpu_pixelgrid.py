@@ -11,13 +11,16 @@ from shopt_b200 import synth
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["fast", "direct", "jacobi"], autouse=True)
+@pytest.fixture(params=["fast", "one-stage", "direct", "jacobi"], autouse=True)
 def pca_path(request, monkeypatch):
-    """Every case runs three times: with the block-subspace fast path enabled (stars it gives up on go to the direct
-    Gram-matrix eigen path, and from there to the Jacobi SVD when a check fails), with the fast path off (direct path
-    first for every star), and with the full Jacobi SVD forced for every star."""
-    for name in ("SHOPT_PCA_NO_FAST", "SHOPT_PCA_NO_EIG", "SHOPT_PCA_DEBUG"):
+    """Every case runs four times: as shipped (pca_power_kernel first, pca_kernel on what it leaves: power path, block
+    subspace iteration, direct Gram-matrix eigen path, Jacobi SVD when a check fails), with stage 1 off (pca_kernel's own
+    power / block paths serve the one-component stars), with the fast paths off (direct path first for every star), and
+    with the full Jacobi SVD forced for every star."""
+    for name in ("SHOPT_PCA_NO_FAST", "SHOPT_PCA_NO_EIG", "SHOPT_PCA_DEBUG", "SHOPT_PCA_NO_LIGHT"):
         monkeypatch.delenv(name, raising=False)
+    if request.param == "one-stage":
+        monkeypatch.setenv("SHOPT_PCA_NO_LIGHT", "1")
     if request.param in ("direct", "jacobi"):
         monkeypatch.setenv("SHOPT_PCA_NO_FAST", "1")
     if request.param == "jacobi":
@@ -40,6 +43,24 @@ def test_pca_star_stamps(stage, orc, N, r, kw):
         pgf, k, status = stage.pca_batch(st, 50, 0.99, 3, unity)
         want, kw_, st_ = orc.pixel_grid_pca_batch(st, 50, 0.99, 3, unity, nthreads=orc.max_threads())
         assert np.array_equal(status, st_) and np.array_equal(k, kw_)
+        assert close(pgf, want)
+
+
+def test_few_masked_pixels_stay_one_component(stage, orc):
+    """A handful of masked pixels (NaN -> 0.001) does not add components: stage 1 serves these stars through its
+    NaN-aware pass; and a stamp with an Inf is a failed star whichever kernel meets it first."""
+    cat = synth.make_catalog(20, 131, 64)
+    st = cat["stamps"].numpy().copy()
+    rng = np.random.default_rng(3)
+    for i in range(20):
+        for _ in range(1 + i % 3):
+            st[i, rng.integers(0, 131), rng.integers(0, 131)] = np.nan
+    st[7, 5, 9] = np.inf
+    for unity in (False, True):
+        pgf, k, status = stage.pca_batch(st, 50, 0.99, 3, unity)
+        want, kw_, st_ = orc.pixel_grid_pca_batch(st, 50, 0.99, 3, unity, nthreads=orc.max_threads())
+        assert np.array_equal(status, st_) and np.array_equal(k, kw_) and status[7] == 1
+        assert (k[np.arange(20) != 7] == 1).all()
         assert close(pgf, want)
 
 
