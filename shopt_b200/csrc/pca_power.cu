@@ -31,7 +31,7 @@ constexpr int PW_NW = 4, PW_THREADS = PW_NW * 32;
 
 __device__ __forceinline__ double pw_ntz(double x) { return isnan(x) ? 0.001 : x; }   // masks.jl:43
 
-// shared memory (doubles): mu r | q r | qn r | part NW*r | t c | Ys c | red 2*NW*3
+// shared memory (doubles): mu r | q r | qn r | part NW*r | part2 NW*r | t c | Ys c | red 2*NW*3
 template <int RT>
 __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(const PcaPowerArgs a) {
     extern __shared__ __align__(16) double pw_smem[];
@@ -39,7 +39,8 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
     const int r = a.r, c = a.c;
     const long long rc = (long long)r * c;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    double *mu = pw_smem, *q = mu + r, *qn = q + r, *part = qn + r, *t = part + PW_NW * r, *Ys = t + c, *red = Ys + c;
+    double *mu = pw_smem, *q = mu + r, *qn = q + r, *part = qn + r, *part2 = part + PW_NW * r, *t = part2 + PW_NW * r, *Ys = t + c,
+           *red = Ys + c;
     int buf = 0;
     const double den = (double)(c - 1);
     for (;;) {
@@ -51,53 +52,94 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
         const double *X = a.stamps + star * rc;
         double *out = a.pgf + star * rc;
         bool defer = false;
-        // ---- pass 1 (HBM): row sums -> mean over the columns; masked pixels, non-finite pixels ----
+        // ---- pass 1 (HBM): row sums -> mean over the columns; masked pixels, non-finite pixels; AND a first power step.
+        //      With q0 = the (uncentred) central column, normalised, and a = X'q0:  Z Z'q0 = X a - mean (1'a)  for
+        //      Z = X - mean 1' (the terms in mean'q0 cancel), so the first application of Z Z' needs no mean and rides
+        //      along with the pass that computes it.  It only supplies the start vector of the iteration below (whose
+        //      passes use the centred pixels and decide acceptance a posteriori), and saves one pass over the stamp. ----
         double nrep = 0.0;
         bool hasnan = false;
         {
-            double rs[RT];
-#pragma unroll
-            for (int k = 0; k < RT; k++) rs[k] = 0.0;
-            int nrepi = 0;
             const double *xl = X + lane;
-            for (int j = warp; j < c; j += PW_NW) {
-                const double *col = xl + (size_t)j * r;
+            const double *xc = xl + (size_t)(c / 2) * r;
+            double q0[RT], v0[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+            for (int k = 0; k < RT; k++) {
+                q0[k] = (k < RT - 1 || lane + 32 * k < r) ? pw_ntz(__ldg(xc + 32 * k)) : 0.0;
+                if (warp == 0) v0[0] = fma(q0[k], q0[k], v0[0]);
+            }
+            cta_sum<3, PW_NW>(v0, red, buf);
+            const double inv0 = (v0[0] > 0.0 && isfinite(v0[0])) ? 1.0 / sqrt(v0[0]) : 0.0;   // 0: the later checks defer the star
+#pragma unroll
+            for (int k = 0; k < RT; k++) q0[k] *= inv0;
+            double rs[RT], xa[RT];
+#pragma unroll
+            for (int k = 0; k < RT; k++) { rs[k] = 0.0; xa[k] = 0.0; }
+            int nrepi = 0;
+            double suma = 0.0;
+            const bool hi16 = lane & 16;
+            for (int j = warp; j < c; j += 2 * PW_NW) {
+                const int j2 = j + PW_NW;
+                const bool two = j2 < c;
+                const double *c1 = xl + (size_t)j * r, *c2 = xl + (size_t)(two ? j2 : j) * r;
+                double x1[RT], x2[RT], d1 = 0.0, d2 = 0.0;
 #pragma unroll
                 for (int k = 0; k < RT; k++) {
-                    if (k < RT - 1 || lane + 32 * k < r) {       // only the last slice of rows can be short
-                        const double x0 = __ldg(col + 32 * k);
-                        const bool isn = x0 != x0;
-                        nrepi += isn;
-                        rs[k] += isn ? 0.001 : x0;
+                    x1[k] = 0.0; x2[k] = 0.0;
+                    if (k < RT - 1 || lane + 32 * k < r) {
+                        const double y1 = __ldg(c1 + 32 * k), y2 = __ldg(c2 + 32 * k);
+                        const bool n1 = y1 != y1, n2 = two && (y2 != y2);
+                        nrepi += n1; nrepi += n2;
+                        x1[k] = n1 ? 0.001 : y1;
+                        x2[k] = two ? (n2 ? 0.001 : y2) : 0.0;
                     }
+                    rs[k] += x1[k] + x2[k];
+                    d1 = fma(x1[k], q0[k], d1);
+                    d2 = fma(x2[k], q0[k], d2);
                 }
+                double sx = (hi16 ? d2 : d1) + __shfl_xor_sync(0xffffffffu, hi16 ? d1 : d2, 16);
+                sx += __shfl_xor_sync(0xffffffffu, sx, 8);
+                sx += __shfl_xor_sync(0xffffffffu, sx, 4);
+                sx += __shfl_xor_sync(0xffffffffu, sx, 2);
+                sx += __shfl_xor_sync(0xffffffffu, sx, 1);
+                d1 = __shfl_sync(0xffffffffu, sx, 0);
+                d2 = __shfl_sync(0xffffffffu, sx, 16);
+#pragma unroll
+                for (int k = 0; k < RT; k++) xa[k] = fma(x2[k], d2, fma(x1[k], d1, xa[k]));
+                if (lane == 0) suma += d1 + d2;
             }
             double tot = 0.0;                                    // an Inf anywhere makes this row sum non-finite
 #pragma unroll
-            for (int k = 0; k < RT; k++) { const int i = lane + 32 * k; if (i < r) part[warp * r + i] = rs[k]; tot += rs[k]; }
+            for (int k = 0; k < RT; k++) {
+                const int i = lane + 32 * k;
+                if (i < r) { part[warp * r + i] = rs[k]; part2[warp * r + i] = xa[k]; }
+                tot += rs[k];
+            }
             nrep = (double)nrepi;
             hasnan = __syncthreads_or(nrepi) != 0;
             if (__syncthreads_or(!isfinite(tot))) defer = true;  // LAPACK raises on Inf: pca_kernel writes the failure
-        }
-        if (!defer) {
-            for (int i = tid; i < r; i += PW_THREADS) {
-                double s = part[i];
+            double v1[3] = {suma, 0.0, 0.0};
+            cta_sum<3, PW_NW>(v1, red, buf);
+            if (!defer) {
+                double v2[3] = {0.0, 0.0, 0.0};
+                for (int i = tid; i < r; i += PW_THREADS) {
+                    double sr = part[i], sa = part2[i];
 #pragma unroll
-                for (int w = 1; w < PW_NW; w++) s += part[w * r + i];
-                mu[i] = s / c;
+                    for (int w = 1; w < PW_NW; w++) { sr += part[w * r + i]; sa += part2[w * r + i]; }
+                    const double m = sr / c;
+                    mu[i] = m;
+                    const double z = sa - m * v1[0];             // (Z Z'q0)_i
+                    qn[i] = z;
+                    v2[0] = fma(z, z, v2[0]);
+                }
+                cta_sum<3, PW_NW>(v2, red, buf);
+                if (!(v2[0] > 0.0) || !isfinite(v2[0])) defer = true;
+                else {
+                    const double inv = 1.0 / sqrt(v2[0]);
+                    for (int i = tid; i < r; i += PW_THREADS) q[i] = qn[i] * inv;
+                }
+                __syncthreads();
             }
-            __syncthreads();
-            // start vector: the central column, normalised (as power_pca)
-            const double *z0 = X + (size_t)(c / 2) * r;
-            double v2[3] = {0.0, 0.0, 0.0};
-            for (int i = tid; i < r; i += PW_THREADS) { const double z = pw_ntz(__ldg(z0 + i)) - mu[i]; qn[i] = z; v2[0] = fma(z, z, v2[0]); }
-            cta_sum<3, PW_NW>(v2, red, buf);
-            if (!(v2[0] > 0.0) || !isfinite(v2[0])) defer = true;
-            else {
-                const double inv = 1.0 / sqrt(v2[0]);
-                for (int i = tid; i < r; i += PW_THREADS) q[i] = qn[i] * inv;
-            }
-            __syncthreads();
         }
         // ---- power iteration: one pass per step computes t = Z'q and Z t together ----
         double theta = 0.0, fro = 0.0;
@@ -266,7 +308,7 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
 
 template <int RT>
 static int pca_power_launch_t(const PcaPowerArgs &a, cudaStream_t st) {
-    const size_t smem = ((size_t)(3 + PW_NW) * a.r + (size_t)2 * a.c + 2 * PW_NW * 3) * sizeof(double);
+    const size_t smem = ((size_t)(3 + 2 * PW_NW) * a.r + (size_t)2 * a.c + 2 * PW_NW * 3) * sizeof(double);
     auto kern = pca_power_kernel<RT>;
     if (smem > 48 * 1024) SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
