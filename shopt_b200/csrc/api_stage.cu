@@ -477,13 +477,22 @@ int shopt_stage_run_comm(const shopt_params *p, shopt_stage_io *io, shopt_allred
     SHOPT_CUDA_TRY(cudaMemcpyAsync(small + 5 * n, io->x0_learned, n * 24, cudaMemcpyHostToDevice, st));
     TRY(stage_begin(p, &d, ex, b, st));
     // chunks: at least ~16 stars per resident CTA so the persistent kernels keep their tail short; at most NCHUNK_EV
+    // The LAST chunk's kernels cannot hide behind an upload, so it is tapered: half, quarter, quarter of a regular chunk.
     long long nchunks = (long long)n / (16LL * 3 * sm_count());
-    if (nchunks > Ctx::NCHUNK_EV) nchunks = Ctx::NCHUNK_EV;
+    if (nchunks > Ctx::NCHUNK_EV - 2) nchunks = Ctx::NCHUNK_EV - 2;
     if (nchunks < 1) nchunks = 1;
     const long long per = ((long long)n + nchunks - 1) / nchunks;
-    for (long long ck = 0; ck < nchunks; ck++) {
-        const long long first = ck * per, count = std::min<long long>(per, (long long)n - first);
-        if (count <= 0) break;
+    long long cuts[Ctx::NCHUNK_EV + 1];
+    int ncuts = 0;
+    for (long long ck = 0; ck < nchunks && ck * per < (long long)n; ck++) cuts[ncuts++] = ck * per;
+    if (ncuts >= 2) {                                            // split [cuts[last], n) into 1/2, 1/4, 1/4
+        const long long a0 = cuts[ncuts - 1], len = (long long)n - a0;
+        if (len >= 4 * 1024) { cuts[ncuts++] = a0 + len / 2; cuts[ncuts] = a0 + len / 2 + len / 4; ncuts++; }
+    }
+    cuts[ncuts] = (long long)n;
+    for (int ck = 0; ck < ncuts; ck++) {
+        const long long first = cuts[ck], count = cuts[ck + 1] - first;
+        if (count <= 0) continue;
         if (f32) {   // the raw float32 VIGNETs land in the (not yet written) pixel-grid region of the same chunk
             SHOPT_CUDA_TRY(cudaMemcpyAsync(dpgf.as<double>() + first * rc, (const float *)io->stamps + first * rc,
                                            (size_t)count * rc * 4, cudaMemcpyHostToDevice, cs));
