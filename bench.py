@@ -389,7 +389,8 @@ def measure_dfma(L):
 def stage_breakdown(args, p, cat, pgf, out):
     """Each kernel of the step timed alone with CUDA events on the launching (torch current) stream; GB/s from the
     ALGORITHMIC bytes of DESIGN.md (what must cross HBM once), not from counters.  per_step = how many launches of that
-    size one step holds (the polyfit rounds shrink by 10 % each: 1 + 0.9 + 0.81)."""
+    size one step holds (the polyfit rounds shrink by 10 % each: mse_kernel 1 + 0.9 + 0.81; normal_kernel reads every
+    training star in round 1 and only the rejected tenth in rounds 2 and 3: 1 + 0.1 + 0.09)."""
     import ctypes as C
     import torch
     from shopt_b200 import _lib
@@ -439,10 +440,12 @@ def stage_breakdown(args, p, cat, pgf, out):
         ctr = torch.empty(4, dtype=torch.float64, device=dev)
         _lib.check(L.shopt_polyfit_centre_dev(u.data_ptr(), v.data_ptr(), n, ctr.data_ptr(), st))
         w = 1 + 0.9 + 0.81
+        # rounds 2, 3 downdate the round-1 sums by the tenth each round rejected (api_stage.cu) unless switched off
+        wn = w if os.environ.get("SHOPT_POLY_DOWNDATE") == "0" else 1 + 0.1 + 0.09
         t = timed(lambda: _lib.check(L.shopt_polyfit_normal_dev(pgf.data_ptr(), r, r, u.data_ptr(), v.data_ptr(),
                                                                 train.data_ptr(), nt, args.degree, ctr.data_ptr(),
                                                                 acc.data_ptr(), st)), 3)
-        res["normal_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6, "per_step": w}
+        res["normal_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6, "per_step": wn}
         t = timed(lambda: _lib.check(L.shopt_polyfit_solve_dev(acc.data_ptr(), r, r, args.degree, ctr.data_ptr(), nt,
                                                                poly.data_ptr(), info.data_ptr(), st)), 3)
         res["solve_kernel(+factor)"] = {"ms": t, "bytes": 16 * K * rc, "gbs": 16 * K * rc / t / 1e6, "per_step": 3}

@@ -109,12 +109,14 @@ struct StageBufs {
     int *counters, *bad_perm;
     StageState *state;
     long long *idx[2];              // training list (local star indices), ping-pong
+    long long *rej_idx;             // the stars the last compaction dropped (n_rej of them): what the next round downdates by
     unsigned *pos[2];               // ... and each entry's position in the permutation (the tie-break of the selection)
     double *mse;
     unsigned *hist;                 // SEL_BINS
     int *blockcnt;
     long long *blockoff;
     double *acc, *rows, *med, *uvsums, *ctr, *clip;
+    double *acc_raw, *acc_sub;      // the rounds' normal equations before any NaN repair, and the rejected stars' share of them
     void *shard_med;                // sharded runs: work space of the cross-shard per-pixel median (polyfit_median_sharded_launch)
     PolyFactor *fac, *fac_red, *fac_field;
     double *field_part, *field_acc, *field_poly, *field_out;
@@ -135,12 +137,14 @@ static StageBufs stage_carve(void *base, const shopt_params *p, const shopt_stag
     b.bad_perm = a.take<int>(4);
     b.state = a.take<StageState>(1);
     for (int i = 0; i < 2; i++) { b.idx[i] = a.take<long long>(n); b.pos[i] = a.take<unsigned>(n); }
+    b.rej_idx = a.take<long long>(n);
     b.mse = a.take<double>(n);
     b.hist = a.take<unsigned>(SEL_BINS);
     const size_t nblk = (std::max(n, NG) + 1023) / 1024 + 1;
     b.blockcnt = a.take<int>(nblk);
     b.blockoff = a.take<long long>(nblk);
     b.acc = a.take<double>(K * K + K * rc);
+    b.acc_raw = a.take<double>(K * K + K * rc); b.acc_sub = a.take<double>(K * K + K * rc);
     b.rows = a.take<double>(4 * rc);
     b.med = a.take<double>(rc);
     b.shard_med = sharded ? (void *)a.take<char>(polyfit_shard_median_bytes((long long)rc, p->degree)) : nullptr;
@@ -303,6 +307,9 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, const Excha
     long long nc = n_train;                          // training stars alive in the whole catalogue
     int cur = 0;
     int nan_rounds = 0;
+    const bool downdate = !(getenv("SHOPT_POLY_DOWNDATE") && atoi(getenv("SHOPT_POLY_DOWNDATE")) == 0);
+    bool have_raw = false;                           // acc_raw holds the previous round's sums (over nc_raw stars)
+    long long nc_raw = 0;
     if (p->iterations == 0) {                        // ones(r, c, K), shopt.jl:492
         fill_kernel<<<(unsigned)(((long long)K * rc + 255) / 256), 256, 0, st>>>(io->poly, (long long)K * rc, 1.0);
         count_launches(1);
@@ -315,10 +322,27 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, const Excha
             TRY(small_gather_launch(io->pgf, rc, b.idx[cur], b.pos[cur], sl.n_dev, NG, b.gbits, b.rows, ex, st));
             TRY(small_median_launch(b.rows, rc, (int)nc, p->degree, io->poly, st));
         } else {
-            TRY(polyfit_normal_launch(io->pgf, rc, io->u, io->v, sl, p->degree, b.ctr, b.acc, (double *)ctx->scratch,
-                                      ctx->scratch_bytes, st));
+            // Rounds after the first DOWNDATE the normal equations: [V'V | V'P] of the survivors = that of the previous
+            // round minus the share of the stars it rejected (a tenth of the reads of summing the survivors again).  The
+            // sums kept across rounds are the raw ones (acc_raw): a NaN there stays NaN after the subtraction, and the
+            // repair below rebuilds exactly those columns from the current list, so a rejected NaN star heals itself.
+            // Not used when a round dropped more than a quarter (sigma clipping can): the difference would cancel.
+            const long long acc_len = (long long)K * K + (long long)K * rc;
+            if (downdate && have_raw && (nc_raw - nc) * 4 <= nc_raw) {
+                StarList gone;                       // this shard's share of the stars the last round dropped
+                gone.idx = b.rej_idx; gone.n = std::min(n, nc_raw - nc); gone.n_dev = &b.state->n_rej;
+                TRY(polyfit_normal_launch(io->pgf, rc, io->u, io->v, gone, p->degree, b.ctr, b.acc_sub, (double *)ctx->scratch,
+                                          ctx->scratch_bytes, st));
+                if (ex.on()) TRY(ex.sum(b.acc_sub, acc_len, 0));
+                TRY(polyfit_sub_launch(b.acc_raw, b.acc_sub, acc_len, st));
+            } else {
+                TRY(polyfit_normal_launch(io->pgf, rc, io->u, io->v, sl, p->degree, b.ctr, b.acc_raw, (double *)ctx->scratch,
+                                          ctx->scratch_bytes, st));
+                if (ex.on()) TRY(ex.sum(b.acc_raw, acc_len, 0));
+            }
+            have_raw = true; nc_raw = nc;
+            SHOPT_CUDA_TRY(cudaMemcpyAsync(b.acc, b.acc_raw, (size_t)acc_len * sizeof(double), cudaMemcpyDeviceToDevice, st));
             if (ex.on()) {
-                TRY(ex.sum(b.acc, (long long)K * K + (long long)K * rc, 0));
                 // NaN pixel-grid values (interpolate.jl:126-130): the per-pixel median needs the values of every shard.
                 // The all-reduced V'P tells every rank the same thing, so all of them enter the exchange or none does;
                 // the host has to know, which costs sharded runs one stream synchronisation per round.
@@ -362,7 +386,7 @@ static int stage_run_impl(const shopt_params *p, shopt_stage_io *io, const Excha
             nc -= mrej;
         }
         TRY(compact_training_launch(b.mse, b.pos[cur], n, cur, p->sigma_clip, b.state, b.idx[cur], b.idx[1 - cur],
-                                    b.pos[1 - cur], io->flags, b.blockcnt, b.blockoff, st));
+                                    b.pos[1 - cur], io->flags, b.blockcnt, b.blockoff, st, b.rej_idx));
         cur = 1 - cur;
         if (p->sigma_clip) {                         // the new size of the whole catalogue's training set: one int
             long long *cnt = reinterpret_cast<long long *>(b.clip + 3);

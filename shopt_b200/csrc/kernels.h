@@ -37,6 +37,7 @@ int polyfit_mse_launch(const double *pgf, long long rc, const double *u, const d
 // for the pixels whose sums are NaN, with NaN values replaced by the median (interpolate.jl:126-130)
 int polyfit_median_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
                           const double *ctr, int mode, double *acc, double *med, cudaStream_t st);
+int polyfit_sub_launch(double *acc, const double *sub, long long len, cudaStream_t st);
 size_t polyfit_shard_median_bytes(long long rc, int degree);
 int polyfit_median_sharded_launch(const double *pgf, long long rc, const double *u, const double *v, StarList sl, int degree,
                                   const double *ctr, int mode, double *acc, double *med, void *work, const Exchange &ex,
@@ -67,7 +68,7 @@ int clip_threshold_launch(const double *mse, const long long *n_ptr, double nc, 
                           const Exchange &ex, cudaStream_t st);
 int compact_training_launch(const double *mse, const unsigned *pos, long long n_bound, int cur, int sigma, StageState *state,
                             const long long *in_idx, long long *out_idx, unsigned *out_pos, int *flags, int *blockcnt,
-                            long long *blockoff, cudaStream_t st);
+                            long long *blockoff, cudaStream_t st, long long *rej_idx = nullptr);
 int uv_centre_launch(const double *u, const double *v, long long n, double *sums, double *ctr, const Exchange &ex,
                      cudaStream_t st);
 

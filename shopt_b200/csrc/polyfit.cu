@@ -1091,6 +1091,18 @@ int polyfit_median_launch(const double *pgf, long long rc, const double *u, cons
 #undef CALL
 }
 
+// acc -= sub (the downdate of the normal equations by the stars a round rejected)
+__global__ void sub_kernel(double *__restrict__ acc, const double *__restrict__ sub, long long len) {
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < len) acc[e] -= sub[e];
+}
+int polyfit_sub_launch(double *acc, const double *sub, long long len, cudaStream_t st) {
+    sub_kernel<<<(unsigned)((len + 255) / 256), 256, 0, st>>>(acc, sub, len);
+    count_launches(1);
+    SHOPT_CUDA_TRY(cudaGetLastError());
+    return SHOPT_OK;
+}
+
 // ---- sharded median: buffers and driver ----------------------------------------------------------------------
 constexpr long long SHARD_MED_TILE = 16384;
 size_t polyfit_shard_median_bytes(long long rc, int degree) {

@@ -165,14 +165,15 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int *__restric
     }
 }
 // kept entries go to out_idx/out_pos in order; mode 0: source = permutation positions (idx = perm[i] - off, pos = i,
-// flags |= TRAINING); mode 1: source = current list (copy idx/pos; dropped entries get flags |= REJECTED)
+// flags |= TRAINING); mode 1: source = current list (copy idx/pos; dropped entries get flags |= REJECTED and, when
+// rej_idx is given, are listed there in order: entry i is dropped entry number i - slot)
 template <class Pred>
 __global__ void __launch_bounds__(CB) compact_write_kernel(Pred pred, long long n_bound, const long long *__restrict__ n_ptr,
                                                            const long long *__restrict__ blockoff, int mode,
                                                            const long long *__restrict__ perm, long long off,
                                                            const long long *__restrict__ in_idx, const unsigned *__restrict__ in_pos,
                                                            long long *__restrict__ out_idx, unsigned *__restrict__ out_pos,
-                                                           int *__restrict__ flags) {
+                                                           int *__restrict__ flags, long long *__restrict__ rej_idx) {
     __shared__ int s_warp[32];
     const long long n = n_ptr ? *n_ptr : n_bound;
     const long long i = (long long)blockIdx.x * CB + threadIdx.x;
@@ -201,20 +202,25 @@ __global__ void __launch_bounds__(CB) compact_write_kernel(Pred pred, long long 
         }
     } else if (live) {
         if (keep) { out_idx[slot] = in_idx[i]; out_pos[slot] = in_pos[i]; }
-        else flags[in_idx[i]] |= SHOPT_FLAG_REJECTED;
+        else {
+            const long long li = in_idx[i];
+            flags[li] |= SHOPT_FLAG_REJECTED;
+            if (rej_idx) rej_idx[i - slot] = li;
+        }
     }
 }
 
 template <class Pred>
 static int compact_launch(Pred pred, long long n_bound, const long long *n_ptr, int mode, const long long *perm, long long off,
                           const long long *in_idx, const unsigned *in_pos, long long *out_idx, unsigned *out_pos, int *flags,
-                          int *blockcnt, long long *blockoff, long long *total_out, long long *dropped_out, cudaStream_t st) {
+                          int *blockcnt, long long *blockoff, long long *total_out, long long *dropped_out, cudaStream_t st,
+                          long long *rej_idx = nullptr) {
     const int nblocks = (int)((n_bound + CB - 1) / CB);
     if (nblocks > 0) compact_count_kernel<Pred><<<nblocks, CB, 0, st>>>(pred, n_ptr, n_bound, blockcnt);
     compact_scan_kernel<<<1, 1024, 0, st>>>(blockcnt, nblocks, blockoff, total_out, dropped_out, n_ptr, n_bound);
     if (nblocks > 0)
         compact_write_kernel<Pred><<<nblocks, CB, 0, st>>>(pred, n_bound, n_ptr, blockoff, mode, perm, off, in_idx, in_pos,
-                                                          out_idx, out_pos, flags);
+                                                          out_idx, out_pos, flags, rej_idx);
     SHOPT_CUDA_TRY(cudaGetLastError());
     count_launches(nblocks > 0 ? 3 : 1);
     return SHOPT_OK;
@@ -407,10 +413,10 @@ int clip_threshold_launch(const double *mse, const long long *n_ptr, double nc, 
 }
 int compact_training_launch(const double *mse, const unsigned *pos, long long n_bound, int cur, int sigma, StageState *state,
                             const long long *in_idx, long long *out_idx, unsigned *out_pos, int *flags, int *blockcnt,
-                            long long *blockoff, cudaStream_t st) {
+                            long long *blockoff, cudaStream_t st, long long *rej_idx) {
     PredKeep pred{mse, pos, state, sigma};
     return compact_launch(pred, n_bound, &state->nl[cur], 1, nullptr, 0, in_idx, pos, out_idx, out_pos, flags, blockcnt,
-                          blockoff, &state->nl[1 - cur], &state->n_rej, st);
+                          blockoff, &state->nl[1 - cur], &state->n_rej, st, rej_idx);
 }
 int uv_centre_launch(const double *u, const double *v, long long n, double *sums, double *ctr, const Exchange &ex,
                      cudaStream_t st) {

@@ -97,3 +97,38 @@ def test_stage_device_entry_point_matches_host(orc):
     for k in ("model", "learned", "flags", "pca_k", "poly", "pgf"):
         assert np.array_equal(dev[k].cpu().numpy(), host[k], equal_nan=True), k    # same kernels, same bits
     assert dev["counts"] == host["counts"]
+
+
+@pytest.mark.parametrize("case", ["pca", "sigma_clip", "median_constraint", "nan_values"])
+def test_rounds_downdating_the_normal_equations_match_fresh_sums(case, monkeypatch):
+    """Rounds 2.. take [V'V | V'P] of the survivors as the previous round's minus the rejected stars' share
+    (api_stage.cu); SHOPT_POLY_DOWNDATE=0 sums the survivors again like shopt.jl:534-577 does.  Same selection, same
+    coefficients to rounding -- also when NaN pixel-grid values (repaired per round, interpolate.jl:126-130) sit among
+    the training stars, rejected or not."""
+    import torch
+    from shopt_b200 import _lib, pipeline
+    N, r, n_a = 300, 33, 32
+    kw, extra = {}, {}
+    cat = synth.make_catalog(N, r, n_a, frac_contaminated=0.05, frac_masked=0.01 if case == "nan_values" else 0.0)
+    if case == "sigma_clip":
+        kw = dict(sigma_clip=1)
+    elif case == "median_constraint":
+        kw = dict(median_constraint=1)
+    elif case == "nan_values":
+        kw = dict(mode=_lib.MODE_CHISQ, chisq_fill=float("nan"))
+        extra = dict(weights=torch.ones_like(cat["stamps"]).numpy())
+    p = pipeline.default_params(n_a=n_a, degree=2, iterations=4, training_ratio=0.9, **kw)
+    a = [cat[k].numpy() for k in ("stamps", "u", "v", "x0_model", "x0_learned", "perm")]
+    monkeypatch.setenv("SHOPT_POLY_DOWNDATE", "0")
+    fresh = pipeline.run_stage(p, *a, **extra)
+    monkeypatch.setenv("SHOPT_POLY_DOWNDATE", "1")
+    down = pipeline.run_stage(p, *a, **extra)
+    assert np.array_equal(down["flags"], fresh["flags"])
+    assert down["n_per_round"].tolist() == fresh["n_per_round"].tolist() and down["counts"] == fresh["counts"]
+    assert fresh["n_per_round"][-1] < fresh["n_per_round"][0]                 # something was rejected
+    if case == "nan_values":
+        train = (fresh["flags"] & _lib.FLAG_TRAINING) != 0
+        assert np.isnan(fresh["pgf"][train]).any()
+    assert np.isfinite(fresh["poly"]).all() and np.isfinite(down["poly"]).all()
+    scale = np.abs(fresh["poly"]).max(axis=(1, 2), keepdims=True)
+    assert np.max(np.abs(down["poly"] - fresh["poly"]) / scale) < 1e-10
