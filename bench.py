@@ -340,7 +340,7 @@ def run_ours(args):
                 "fp64_pipe_pct": kf.get("fp64_pipe_pct"), "dfma_peak_tflops_measured": dfma,
                 "note": "the dominant kernel is FP64-pipe/issue bound (hundreds of flops per byte), so its HBM fraction is "
                         "small by construction; fp64_pipe_pct (ncu sm__pipe_fp64_cycles_active) is its own roofline. The "
-                        "HBM-bound kernels (normal_kernel, mse_kernel) are listed under stages with their fractions",
+                        "HBM-bound kernels (normal_ring_kernel, mse_ring_kernel) are listed under stages with their fractions",
                 "stages": {k: dict(v, frac=v["gbs"] / peak, **{kk: vv for kk, vv in facts.get(k.split("(")[0], {}).items()
                                                              if kk in ("fp64_pipe_pct", "dram_bytes_per_launch")})
                            for k, v in stages.items()},
@@ -445,14 +445,15 @@ def stage_breakdown(args, p, cat, pgf, out):
         t = timed(lambda: _lib.check(L.shopt_polyfit_normal_dev(pgf.data_ptr(), r, r, u.data_ptr(), v.data_ptr(),
                                                                 train.data_ptr(), nt, args.degree, ctr.data_ptr(),
                                                                 acc.data_ptr(), st)), 3)
-        res["normal_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6, "per_step": wn}
+        ring = int(os.environ.get("SHOPT_POLY_RING", "3"))       # the cp.async-ring kernels are the default (polyfit.cu)
+        res["normal_ring_kernel(round 1)" if ring & 1 else "normal_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6, "per_step": wn}
         t = timed(lambda: _lib.check(L.shopt_polyfit_solve_dev(acc.data_ptr(), r, r, args.degree, ctr.data_ptr(), nt,
                                                                poly.data_ptr(), info.data_ptr(), st)), 3)
         res["solve_kernel(+factor)"] = {"ms": t, "bytes": 16 * K * rc, "gbs": 16 * K * rc / t / 1e6, "per_step": 3}
         t = timed(lambda: _lib.check(L.shopt_polyfit_mse_dev(pgf.data_ptr(), r, r, u.data_ptr(), v.data_ptr(),
                                                              train.data_ptr(), nt, args.degree, poly.data_ptr(),
                                                              mse.data_ptr(), st)), 3)
-        res["mse_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6, "per_step": w}
+        res["mse_ring_kernel(round 1)" if ring & 2 else "mse_kernel(round 1)"] = {"ms": t, "bytes": 8 * rc * nt, "gbs": 8 * rc * nt / t / 1e6, "per_step": w}
     return res
 
 

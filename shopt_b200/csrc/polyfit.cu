@@ -18,7 +18,11 @@
 //   reduce_kernel  sums the chunk partials in chunk order (deterministic; no floating-point atomics anywhere);
 //   solve_kernel   equilibrated Cholesky of G in shared memory, then one thread per pixel back-substitutes;
 //   mse_kernel     same tiling as normal_kernel with the K*PX coefficients of the thread's pixels in registers;
-//                  per-star partial sums per pixel tile, reduced in tile order by mse_reduce_kernel.
+//                  per-star partial sums per pixel tile, reduced in tile order by mse_reduce_kernel;
+//   normal_ring_kernel, mse_ring_kernel   THE DEFAULT: the same two kernels (same arithmetic, same order, bit-identical
+//                  results) with each lane prefetching its own pixels of the next stars into a private ring in shared
+//                  memory by 8-byte cp.async, so 256 bytes per thread are in flight whatever the register budget:
+//                  92 % / 84 % of the measured copy bandwidth at K = 10 against 61 % / 53 % with plain loads.
 #include <algorithm>
 #include <cstdlib>
 
@@ -114,6 +118,111 @@ __global__ void __launch_bounds__(POLY_THREADS) normal_kernel(const double *__re
             }
         }
     }
+    double *out = part + (size_t)blockIdx.y * ((size_t)K * K + (size_t)K * rc);
+#pragma unroll
+    for (int k = 0; k < K; k++)
+#pragma unroll
+        for (int j = 0; j < PX; j++) {
+            const long long px = px0 + (long long)j * POLY_THREADS;
+            if (px < rc) out[(size_t)K * K + (size_t)k * rc + px] = acc[k][j];
+        }
+}
+
+// ---------------------------------------------------------------------------------------------
+// The same V'P partials with every lane prefetching ITS OWN pixels RING_D - 1 stars ahead into a private slot ring in
+// shared memory (8-byte cp.async: no alignment demands on the odd-length star rows, no registers held by loads in
+// flight, and -- each lane reading back only what it copied -- no barrier besides cp.async.wait_group).  ncu on
+// normal_kernel: 72 % of the warp samples wait on the long scoreboard with 16 loads per thread in flight; here
+// RING_D - 1 stars x PX loads per thread are in flight all the time, across the 64-star basis refills as well.
+// Same operations in the same order as normal_kernel: the partials are bit-identical.
+// ---------------------------------------------------------------------------------------------
+constexpr int RING_BYTES_PER_THREAD = 256;   // in flight per thread: RING_D = 32 / PX slots of PX doubles
+#ifndef RING_U
+#define RING_U 1
+#endif
+constexpr int RING_UNR = RING_U;
+__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int DEG, int PX>
+__global__ void __launch_bounds__(POLY_THREADS, 4) normal_ring_kernel(const double *__restrict__ pgf, long long rc,
+                                                                      const double *__restrict__ u, const double *__restrict__ v,
+                                                                      const long long *__restrict__ idx, long long n_bound,
+                                                                      const long long *__restrict__ n_ptr,
+                                                                      const double *__restrict__ ctr, double *__restrict__ part) {
+    constexpr int K = PolyCfg<DEG>::K;
+    constexpr int RING_D = (K <= 21) ? RING_BYTES_PER_THREAD / 8 / PX : 16;   // static shared memory stays under 48 KB
+    static_assert(POLY_THREADS >= 2 * SCHUNK && (SCHUNK & (SCHUNK - 1)) == 0 && RING_D <= SCHUNK, "staging layout");
+    __shared__ __align__(16) double sV[SCHUNK][K + (K & 1)];
+    __shared__ long long sOff[2 * SCHUNK];                       // row offsets of this and of the next 64 stars
+    __shared__ double ring[RING_D][PX][POLY_THREADS];            // [slot][j][thread]: conflict-free 8-byte rows
+    const long long n = n_ptr ? *n_ptr : n_bound;
+    const long long per_chunk = (n + gridDim.y - 1) / gridDim.y;
+    const long long t0 = (long long)blockIdx.y * per_chunk;
+    const long long t1 = (t0 + per_chunk < n) ? t0 + per_chunk : n;
+    const int nloc = (t1 > t0) ? (int)(t1 - t0) : 0;             // stars of this chunk, addressed by local index below
+    const long long px0 = (long long)blockIdx.x * (POLY_THREADS * PX) + threadIdx.x;
+    int nlive = 0;                                               // this thread's pixels j < nlive exist (a prefix: px grows with j)
+#pragma unroll
+    for (int j = 0; j < PX; j++) nlive += (px0 + (long long)j * POLY_THREADS < rc) ? 1 : 0;
+    double acc[K][PX];
+#pragma unroll
+    for (int k = 0; k < K; k++)
+#pragma unroll
+        for (int j = 0; j < PX; j++) acc[k][j] = 0.0;
+    const double *mine = pgf + px0;
+    double *my_slot = &ring[0][0][threadIdx.x];
+    auto stage_off = [&](int i) {                                // local star i -> offset of its row
+        if (i < nloc) sOff[i & (2 * SCHUNK - 1)] = (idx ? idx[t0 + i] : t0 + i) * rc;
+    };
+    auto issue = [&](int i) {                                    // local star i -> slot i mod RING_D; one group per star
+        if (i < nloc) {
+            const double *row = mine + sOff[i & (2 * SCHUNK - 1)];
+            double *dst = my_slot + (i & (RING_D - 1)) * (PX * POLY_THREADS);
+#pragma unroll
+            for (int j = 0; j < PX; j++)
+                if (j < nlive) cp_async8(dst + j * POLY_THREADS, row + (long long)j * POLY_THREADS);
+        }
+        cp_async_commit();
+    };
+    if (threadIdx.x < SCHUNK) stage_off(threadIdx.x);
+    __syncthreads();
+    for (int d = 0; d < RING_D - 1; d++) issue(d);
+    for (int base = 0; base < nloc; base += SCHUNK) {
+        const int m = (nloc - base < SCHUNK) ? (nloc - base) : SCHUNK;
+        __syncthreads();
+        if (threadIdx.x < m) {
+            const long long star = idx ? idx[t0 + base + threadIdx.x] : t0 + base + threadIdx.x;
+            double b[K], cu = u[star], cv = v[star];
+            centre_uv(ctr, cu, cv);
+            basis_eval<DEG>(cu, cv, b);
+#pragma unroll
+            for (int k = 0; k < K; k++) sV[threadIdx.x][k] = b[k];
+        } else if (threadIdx.x >= SCHUNK && threadIdx.x < 2 * SCHUNK) {
+            stage_off(base + threadIdx.x);                       // the NEXT 64 stars: the prefetch runs across the refill
+        }
+        __syncthreads();
+#pragma unroll RING_UNR
+        for (int s = 0; s < m; s++) {
+            const int i = base + s;
+            issue(i + RING_D - 1);                               // into the slot star i - 1 was read from
+            cp_async_wait<RING_D - 1>();                         // all but the newest RING_D - 1 groups: star i has landed
+            const double *src = my_slot + (i & (RING_D - 1)) * (PX * POLY_THREADS);
+            double z[PX];
+#pragma unroll
+            for (int j = 0; j < PX; j++) z[j] = (j < nlive) ? src[j * POLY_THREADS] : 0.0;
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+                const double vk = sV[s][k];
+#pragma unroll
+                for (int j = 0; j < PX; j++) acc[k][j] = fma(vk, z[j], acc[k][j]);
+            }
+        }
+    }
+    cp_async_wait<0>();
     double *out = part + (size_t)blockIdx.y * ((size_t)K * K + (size_t)K * rc);
 #pragma unroll
     for (int k = 0; k < K; k++)
@@ -475,6 +584,117 @@ __global__ void __launch_bounds__(POLY_THREADS) mse_kernel(const double *__restr
             part[(size_t)blockIdx.x * n + base + threadIdx.x] = e;
         }
     }
+}
+// mse_kernel with the per-lane cp.async ring of normal_ring_kernel (see there): same arithmetic in the same order, the
+// loads of the next RING_D - 1 stars in flight while a star is evaluated.
+template <int DEG, int PX>
+__global__ void __launch_bounds__(POLY_THREADS, 4) mse_ring_kernel(const double *__restrict__ pgf, long long rc,
+                                                                   const double *__restrict__ u, const double *__restrict__ v,
+                                                                   const long long *__restrict__ idx, long long n_bound,
+                                                                   const long long *__restrict__ n_ptr, const double *__restrict__ poly,
+                                                                   double *__restrict__ part) {
+    constexpr int K = PolyCfg<DEG>::K;
+    constexpr int RING_D = (K <= 21) ? RING_BYTES_PER_THREAD / 8 / PX : 16;   // static shared memory stays under 48 KB
+    constexpr int NW = POLY_THREADS / 32;
+    static_assert(RING_D % 8 == 0 && RING_D <= SCHUNK, "groups of eight stars stay inside the ring");
+    __shared__ __align__(16) double sV[SCHUNK][K + (K & 1)];
+    __shared__ long long sOff[2 * SCHUNK];
+    __shared__ double sE[SCHUNK][NW];
+    __shared__ double ring[RING_D][PX][POLY_THREADS];
+    const long long n = n_ptr ? *n_ptr : n_bound;
+    const long long per_chunk = ((n + gridDim.y - 1) / gridDim.y + SCHUNK - 1) / SCHUNK * SCHUNK;
+    const long long t0 = (long long)blockIdx.y * per_chunk;
+    const long long t1 = (t0 + per_chunk < n) ? t0 + per_chunk : n;
+    const int nloc = (t1 > t0) ? (int)(t1 - t0) : 0;
+    const long long px0 = (long long)blockIdx.x * (POLY_THREADS * PX) + threadIdx.x;
+    double cf[K][PX];
+    int nlive = 0;
+#pragma unroll
+    for (int j = 0; j < PX; j++) {
+        const long long px = px0 + (long long)j * POLY_THREADS;
+        const bool lv = px < rc;
+        nlive += lv ? 1 : 0;
+#pragma unroll
+        for (int k = 0; k < K; k++) cf[k][j] = lv ? poly[px + (size_t)k * rc] : 0.0;
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const double *mine = pgf + px0;
+    double *my_slot = &ring[0][0][threadIdx.x];
+    auto stage_off = [&](int i) {
+        if (i < nloc) sOff[i & (2 * SCHUNK - 1)] = (idx ? idx[t0 + i] : t0 + i) * rc;
+    };
+    auto issue = [&](int i) {
+        if (i < nloc) {
+            const double *row = mine + sOff[i & (2 * SCHUNK - 1)];
+            double *dst = my_slot + (i & (RING_D - 1)) * (PX * POLY_THREADS);
+#pragma unroll
+            for (int j = 0; j < PX; j++)
+                if (j < nlive) cp_async8(dst + j * POLY_THREADS, row + (long long)j * POLY_THREADS);
+        }
+        cp_async_commit();
+    };
+    if (threadIdx.x < SCHUNK) stage_off(threadIdx.x);
+    __syncthreads();
+    for (int d = 0; d < RING_D - 1; d++) issue(d);
+    for (int base = 0; base < nloc; base += SCHUNK) {
+        const int m = (nloc - base < SCHUNK) ? (nloc - base) : SCHUNK;
+        __syncthreads();
+        if (threadIdx.x < m) {
+            const long long star = idx ? idx[t0 + base + threadIdx.x] : t0 + base + threadIdx.x;
+            double b[K];
+            basis_eval<DEG>(u[star], v[star], b);
+#pragma unroll
+            for (int k = 0; k < K; k++) sV[threadIdx.x][k] = b[k];
+        } else if (threadIdx.x >= SCHUNK && threadIdx.x < 2 * SCHUNK) {
+            stage_off(base + threadIdx.x);
+        }
+        __syncthreads();
+        for (int s0 = 0; s0 < m; s0 += 8) {
+            double e8[8];
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                const int i = base + s0 + q;
+                issue(i + RING_D - 1);                           // empty group past the end: the count stays in step
+                cp_async_wait<RING_D - 1>();
+                double e = 0.0;
+                if (s0 + q < m) {
+                    const double *src = my_slot + (i & (RING_D - 1)) * (PX * POLY_THREADS);
+                    double val[PX];
+#pragma unroll
+                    for (int j = 0; j < PX; j++) val[j] = (j < nlive) ? -src[j * POLY_THREADS] : 0.0;
+#pragma unroll
+                    for (int k = 0; k < K; k++) {
+                        const double vk = sV[s0 + q][k];
+#pragma unroll
+                        for (int j = 0; j < PX; j++) val[j] = fma(cf[k][j], vk, val[j]);
+                    }
+#pragma unroll
+                    for (int j = 0; j < PX; j++) e = fma(val[j], val[j], e);
+                }
+                e8[q] = e;
+            }
+            const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+            double k4[4], k2[2];
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                k4[i] = (b4 ? e8[i + 4] : e8[i]) + __shfl_xor_sync(0xffffffffu, b4 ? e8[i] : e8[i + 4], 16);
+#pragma unroll
+            for (int i = 0; i < 2; i++)
+                k2[i] = (b3 ? k4[i + 2] : k4[i]) + __shfl_xor_sync(0xffffffffu, b3 ? k4[i] : k4[i + 2], 8);
+            double tot = (b2 ? k2[1] : k2[0]) + __shfl_xor_sync(0xffffffffu, b2 ? k2[0] : k2[1], 4);
+            tot += __shfl_xor_sync(0xffffffffu, tot, 2);
+            tot += __shfl_xor_sync(0xffffffffu, tot, 1);
+            if ((lane & 3) == 0 && s0 + (lane >> 2) < m) sE[s0 + (lane >> 2)][warp] = tot;
+        }
+        __syncthreads();
+        if (threadIdx.x < m) {
+            double e = sE[threadIdx.x][0];
+#pragma unroll
+            for (int w = 1; w < NW; w++) e += sE[threadIdx.x][w];
+            part[(size_t)blockIdx.x * n + t0 + base + threadIdx.x] = e;
+        }
+    }
+    cp_async_wait<0>();
 }
 __global__ void mse_reduce_kernel(const double *__restrict__ part, long long n_bound, const long long *__restrict__ n_ptr,
                                   int ntile, double inv_rc, double *__restrict__ mse) {
@@ -871,6 +1091,14 @@ static int poly_cfg() {
     if (cfg < 0) { const char *e = getenv("SHOPT_POLY_CFG"); cfg = e ? atoi(e) & 3 : POLY_CFG_DEFAULT; }
     return cfg;
 }
+// SHOPT_POLY_RING: bit 0 = normal_ring_kernel, bit 1 = mse_ring_kernel (default 3: both; 0 = the plain-load kernels).
+// Measured on the bench workload (87k x 131 x 131, K = 10): normal 3.01 -> 1.99 ms (61 % -> 92 % of the measured copy
+// bandwidth), mse 3.43 -> 2.17 ms (53 % -> 84 %); K = 21 (5.4k x 301 x 301): 1.55 -> 1.21 and 1.91 -> 1.69 ms.
+static int poly_ring() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("SHOPT_POLY_RING"); v = e ? atoi(e) : 3; }
+    return v;
+}
 static int poly_px(int K, int cfg) {
     const int base = (K <= 10) ? 4 : (K <= 21 ? 2 : 1);
     return (cfg & 1) ? (base > 1 ? base / 2 : 1) : base;
@@ -887,7 +1115,10 @@ static int normal_launch_v(const double *pgf, long long rc, const double *u, con
     int nchunk = pick_chunks(sl.n, tiles);
     while (nchunk > 1 && (size_t)nchunk * len * 8 > scratch_bytes) nchunk--;
     if ((size_t)nchunk * len * 8 > scratch_bytes) return SHOPT_E_NOMEM;
-    normal_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, ctr, scratch);
+    if (poly_ring() & 1)
+        normal_ring_kernel<DEG, PX><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, ctr, scratch);
+    else
+        normal_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, ctr, scratch);
     gram_kernel<DEG><<<nchunk, POLY_THREADS, 0, st>>>(u, v, sl.idx, sl.n, sl.n_dev, ctr, rc, scratch);
     reduce_kernel<<<(unsigned)((len + 255) / 256), 256, 0, st>>>(scratch, len, nchunk, acc);
     count_launches(3);
@@ -957,7 +1188,10 @@ static int mse_launch_v(const double *pgf, long long rc, const double *u, const 
     const int tiles = (int)((rc + POLY_THREADS * PX - 1) / (POLY_THREADS * PX));
     if ((size_t)tiles * sl.n * 8 > scratch_bytes) return SHOPT_E_NOMEM;
     const int nchunk = pick_chunks(sl.n, tiles);
-    mse_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, poly, scratch);
+    if (poly_ring() & 2)
+        mse_ring_kernel<DEG, PX><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, poly, scratch);
+    else
+        mse_kernel<DEG, PX, UNR><<<dim3(tiles, nchunk), POLY_THREADS, 0, st>>>(pgf, rc, u, v, sl.idx, sl.n, sl.n_dev, poly, scratch);
     mse_reduce_kernel<<<(unsigned)((sl.n + 255) / 256), 256, 0, st>>>(scratch, sl.n, sl.n_dev, tiles, 1.0 / (double)rc, mse);
     count_launches(2);
     SHOPT_CUDA_TRY(cudaGetLastError());
