@@ -31,9 +31,15 @@ constexpr int PW_NW = 4, PW_THREADS = PW_NW * 32;
 
 __device__ __forceinline__ double pw_ntz(double x) { return isnan(x) ? 0.001 : x; }   // masks.jl:43
 
-// shared memory (doubles): mu r | q r | qn r | part NW*r | part2 NW*r | t c | Ys c | red 2*NW*3
-template <int RT>
-__global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(const PcaPowerArgs a) {
+// D > 0: the columns of the next D - 1 steps of a warp's walk over the stamp are in flight all the time: every lane copies
+// ITS OWN rows of the two columns of a step into a private slot ring in shared memory (8-byte cp.async; a lane reads back
+// only what it copied, so cp.async.wait_group is the only synchronisation).  Every pass walks the same columns in the same
+// order, so the ring runs on across the passes of a star: while the CTA reduces and decides after a pass, the first
+// columns of the next pass are already on their way (ncu on the D = 0 kernel: 41 % of the warp samples on the long
+// scoreboard).  The values and the arithmetic are those of the D = 0 kernel: results are bit-identical.
+// shared memory (doubles): mu r | q r | qn r | part NW*r | part2 NW*r | t c | Ys c | red 2*NW*3 | ring NW*D*2*RT*32
+template <int RT, int D>
+__global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? (D > 0 ? 4 : 5) : 3) pca_power_kernel(const PcaPowerArgs a) {
     extern __shared__ __align__(16) double pw_smem[];
     __shared__ long long s_star;
     const int r = a.r, c = a.c;
@@ -43,6 +49,9 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
            *red = Ys + c;
     int buf = 0;
     const double den = (double)(c - 1);
+    // ring: slot s of this warp holds step columns (j, j + NW) as [s][which][k][lane]
+    double *const ringw = red + 2 * PW_NW * 3 + (size_t)warp * (D * 2 * RT * 32) + lane;
+    const int niter = (c - warp + 2 * PW_NW - 1) / (2 * PW_NW);   // steps of this warp per pass (c >= 2 NW: at least one)
     for (;;) {
         __syncthreads();                                         // the previous star's shared data is dead
         if (tid == 0) s_star = (long long)atomicAdd(a.counter, 1ULL);
@@ -52,6 +61,33 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
         const double *X = a.stamps + star * rc;
         double *out = a.pgf + star * rc;
         bool defer = false;
+        int pn = 0, ps = 0, cs = 0;                              // ring: next step to prefetch, its slot, the slot to read next
+        auto issue = [&]() {
+            if constexpr (D > 0) {
+                const int j = warp + 2 * PW_NW * pn;
+                const double *c1 = X + lane + (size_t)j * r;
+                double *dst = ringw + ps * (2 * RT * 32);
+                const bool two = j + PW_NW < c;
+#pragma unroll
+                for (int k = 0; k < RT; k++)
+                    if (k < RT - 1 || lane + 32 * k < r) {
+                        cp_async8(dst + k * 32, c1 + 32 * k);
+                        if (two) cp_async8(dst + (RT + k) * 32, c1 + (size_t)PW_NW * r + 32 * k);
+                    }
+                cp_async_commit();
+                if (++pn == niter) pn = 0;
+                if (++ps == D) ps = 0;
+            }
+        };
+        auto landed = [&]() -> const double * {                  // one more step out, then the oldest one has arrived
+            issue();
+            if constexpr (D > 0) cp_async_wait<D - 1>();
+            const double *src = ringw + cs * (2 * RT * 32);
+            if (++cs == D) cs = 0;
+            return src;
+        };
+        if constexpr (D > 0)
+            for (int d = 0; d < D - 1; d++) issue();
         // ---- pass 1 (HBM): row sums -> mean over the columns; masked pixels, non-finite pixels; AND a first power step.
         //      With q0 = the (uncentred) central column, normalised, and a = X'q0:  Z Z'q0 = X a - mean (1'a)  for
         //      Z = X - mean 1' (the terms in mean'q0 cancel), so the first application of Z Z' needs no mean and rides
@@ -83,11 +119,15 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
                 const bool two = j2 < c;
                 const double *c1 = xl + (size_t)j * r, *c2 = xl + (size_t)(two ? j2 : j) * r;
                 double x1[RT], x2[RT], d1 = 0.0, d2 = 0.0;
+                const double *src = nullptr;
+                if constexpr (D > 0) src = landed();
 #pragma unroll
                 for (int k = 0; k < RT; k++) {
                     x1[k] = 0.0; x2[k] = 0.0;
                     if (k < RT - 1 || lane + 32 * k < r) {
-                        const double y1 = __ldg(c1 + 32 * k), y2 = __ldg(c2 + 32 * k);
+                        double y1, y2;
+                        if constexpr (D > 0) { y1 = src[k * 32]; y2 = two ? src[(RT + k) * 32] : 0.0; }
+                        else { y1 = __ldg(c1 + 32 * k); y2 = __ldg(c2 + 32 * k); }
                         const bool n1 = y1 != y1, n2 = two && (y2 != y2);
                         nrepi += n1; nrepi += n2;
                         x1[k] = n1 ? 0.001 : y1;
@@ -161,11 +201,15 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
                     const bool two = j2 < c;
                     const double *c1 = xl + (size_t)j * r, *c2 = xl + (size_t)(two ? j2 : j) * r;
                     double z1[RT], z2[RT], d1 = 0.0, d2 = 0.0;
+                    const double *src = nullptr;
+                    if constexpr (D > 0) src = landed();
 #pragma unroll
                     for (int k = 0; k < RT; k++) {
                         z1[k] = 0.0; z2[k] = 0.0;
                         if (k < RT - 1 || lane + 32 * k < r) {
-                            double x1 = __ldg(c1 + 32 * k), x2 = __ldg(c2 + 32 * k);
+                            double x1, x2;
+                            if constexpr (D > 0) { x1 = src[k * 32]; x2 = two ? src[(RT + k) * 32] : 0.0; }
+                            else { x1 = __ldg(c1 + 32 * k); x2 = __ldg(c2 + 32 * k); }
                             if (nans) { x1 = pw_ntz(x1); x2 = pw_ntz(x2); }
                             z1[k] = x1 - mur[k];
                             z2[k] = two ? x2 - mur[k] : 0.0;
@@ -295,6 +339,7 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
                 }
             }
         }
+        if constexpr (D > 0) cp_async_wait<0>();                 // the steps prefetched for a pass that did not happen
         if (tid == 0) {
             if (defer) {
                 a.defer_list[atomicAdd(a.defer_count, 1ULL)] = star;
@@ -306,10 +351,10 @@ __global__ void __launch_bounds__(PW_THREADS, RT <= 5 ? 5 : 3) pca_power_kernel(
     }
 }
 
-template <int RT>
-static int pca_power_launch_t(const PcaPowerArgs &a, cudaStream_t st) {
-    const size_t smem = ((size_t)(3 + 2 * PW_NW) * a.r + (size_t)2 * a.c + 2 * PW_NW * 3) * sizeof(double);
-    auto kern = pca_power_kernel<RT>;
+template <int RT, int D>
+static int pca_power_launch_d(const PcaPowerArgs &a, cudaStream_t st) {
+    const size_t smem = ((size_t)(3 + 2 * PW_NW) * a.r + (size_t)2 * a.c + 2 * PW_NW * 3 + (size_t)PW_NW * D * 2 * RT * 32) * sizeof(double);
+    auto kern = pca_power_kernel<RT, D>;
     if (smem > 48 * 1024) SHOPT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     SHOPT_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PW_THREADS, smem));
@@ -331,6 +376,18 @@ static int pca_power_launch_t(const PcaPowerArgs &a, cudaStream_t st) {
     count_launches(1);
     SHOPT_CUDA_TRY(cudaGetLastError());
     return SHOPT_OK;
+}
+
+// SHOPT_PCA_RING=0 / 1 forces the plain-load kernel (D = 0) / the ring.  Measured (B200, per 100k stars of 131 x 131):
+// 13.14 ms plain, 13.24 ms ring -- at four stamps per SM living in L2 the long-scoreboard samples overlap with the
+// butterfly chains and the CTA-wide reductions, and the ring's extra LDS / LDGSTS cost what the prefetch wins; per 6 250
+// stars of 301 x 301 (every pass streams from HBM): 4.52 -> 4.28 ms.  Default: the ring for stamps above 160 rows.
+template <int RT>
+static int pca_power_launch_t(const PcaPowerArgs &a, cudaStream_t st) {
+    static const int ring = getenv("SHOPT_PCA_RING") ? atoi(getenv("SHOPT_PCA_RING")) : -1;
+    constexpr int DD = RT <= 5 ? 4 : 3;
+    if (ring > 0 || (ring < 0 && RT > 5)) return pca_power_launch_d<RT, DD>(a, st);
+    return pca_power_launch_d<RT, 0>(a, st);
 }
 
 int pca_power_launch(const PcaPowerArgs &a, cudaStream_t st) {

@@ -141,12 +141,6 @@ constexpr int RING_BYTES_PER_THREAD = 256;   // in flight per thread: RING_D = 3
 #define RING_U 1
 #endif
 constexpr int RING_UNR = RING_U;
-__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
 template <int DEG, int PX>
 __global__ void __launch_bounds__(POLY_THREADS, 4) normal_ring_kernel(const double *__restrict__ pgf, long long rc,
                                                                       const double *__restrict__ u, const double *__restrict__ v,
