@@ -136,13 +136,15 @@ __global__ void __launch_bounds__(POLY_THREADS) normal_kernel(const double *__re
 // RING_D - 1 stars x PX loads per thread are in flight all the time, across the 64-star basis refills as well.
 // Same operations in the same order as normal_kernel: the partials are bit-identical.
 // ---------------------------------------------------------------------------------------------
+// resident CTAs per SM the ring kernels are compiled for, by accumulators per thread (K * PX doubles)
+__host__ __device__ constexpr int ring_ctas(int acc) { return acc <= 42 ? 4 : (acc <= 60 ? 3 : 2); }
 constexpr int RING_BYTES_PER_THREAD = 256;   // in flight per thread: RING_D = 32 / PX slots of PX doubles
 #ifndef RING_U
 #define RING_U 1
 #endif
 constexpr int RING_UNR = RING_U;
 template <int DEG, int PX>
-__global__ void __launch_bounds__(POLY_THREADS, 4) normal_ring_kernel(const double *__restrict__ pgf, long long rc,
+__global__ void __launch_bounds__(POLY_THREADS, ring_ctas(PolyCfg<DEG>::K * PX)) normal_ring_kernel(const double *__restrict__ pgf, long long rc,
                                                                       const double *__restrict__ u, const double *__restrict__ v,
                                                                       const long long *__restrict__ idx, long long n_bound,
                                                                       const long long *__restrict__ n_ptr,
@@ -582,7 +584,7 @@ __global__ void __launch_bounds__(POLY_THREADS) mse_kernel(const double *__restr
 // mse_kernel with the per-lane cp.async ring of normal_ring_kernel (see there): same arithmetic in the same order, the
 // loads of the next RING_D - 1 stars in flight while a star is evaluated.
 template <int DEG, int PX>
-__global__ void __launch_bounds__(POLY_THREADS, 4) mse_ring_kernel(const double *__restrict__ pgf, long long rc,
+__global__ void __launch_bounds__(POLY_THREADS, ring_ctas(PolyCfg<DEG>::K * PX)) mse_ring_kernel(const double *__restrict__ pgf, long long rc,
                                                                    const double *__restrict__ u, const double *__restrict__ v,
                                                                    const long long *__restrict__ idx, long long n_bound,
                                                                    const long long *__restrict__ n_ptr, const double *__restrict__ poly,
@@ -1093,6 +1095,13 @@ static int poly_ring() {
     if (v < 0) { const char *e = getenv("SHOPT_POLY_RING"); v = e ? atoi(e) : 3; }
     return v;
 }
+// SHOPT_POLY_PX4=1: four pixels per thread for 10 < K <= 21 as well (84 accumulators, two CTAs per SM: the ring keeps the
+// loads in flight whatever the occupancy).  Measurement switch.
+static int poly_px4() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("SHOPT_POLY_PX4"); v = e ? atoi(e) : 0; }
+    return v;
+}
 static int poly_px(int K, int cfg) {
     const int base = (K <= 10) ? 4 : (K <= 21 ? 2 : 1);
     return (cfg & 1) ? (base > 1 ? base / 2 : 1) : base;
@@ -1156,6 +1165,9 @@ static int normal_launch_t(const double *pgf, long long rc, const double *u, con
         if (poly_bulk() && (reinterpret_cast<uintptr_t>(pgf) & 7) == 0)
             return normal_bulk_launch<DEG>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
     }
+    if constexpr (PolyCfg<DEG>::K > 10 && PolyCfg<DEG>::K <= 21) {
+        if (poly_px4() && poly_ring()) return normal_launch_v<DEG, 4, 4>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
+    }
     switch (poly_cfg()) {
         case 0: return normal_launch_v<DEG, P0, 2>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
         case 1: return normal_launch_v<DEG, P1, 2>(pgf, rc, u, v, sl, ctr, acc, scratch, scratch_bytes, st);
@@ -1195,6 +1207,9 @@ template <int DEG>
 static int mse_launch_t(const double *pgf, long long rc, const double *u, const double *v, StarList sl, const double *poly,
                         double *mse, double *scratch, size_t scratch_bytes, cudaStream_t st) {
     constexpr int P0 = PolyCfg<DEG>::PX, P1 = (P0 > 1 ? P0 / 2 : 1);
+    if constexpr (PolyCfg<DEG>::K > 10 && PolyCfg<DEG>::K <= 21) {
+        if (poly_px4() && poly_ring()) return mse_launch_v<DEG, 4, 4>(pgf, rc, u, v, sl, poly, mse, scratch, scratch_bytes, st);
+    }
     switch (poly_cfg()) {
         case 0: return mse_launch_v<DEG, P0, 2>(pgf, rc, u, v, sl, poly, mse, scratch, scratch_bytes, st);
         case 1: return mse_launch_v<DEG, P1, 2>(pgf, rc, u, v, sl, poly, mse, scratch, scratch_bytes, st);
