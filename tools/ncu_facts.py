@@ -52,27 +52,28 @@ def main():
             continue
         name = re.sub(r"^(void\s+)?(shopt::)?", "", r[name_i])
         name = re.split(r"[<(]", name)[0]
-        e = per.setdefault(name, {k: [] for k in COLS})
+        row = {}
         for k, i in col.items():
             if i is None:
                 continue
             val = num(r[i])
-            if val is None:
-                continue
-            e[k].append(val * UNIT_SCALE.get(units[i], 1.0))
+            if val is not None:
+                row[k] = val * UNIT_SCALE.get(units[i], 1.0)
+        per.setdefault(name, []).append(row)
     facts = {}
-    for name, e in per.items():
-        n = len(e["time_ns"]) or 1
-        mean = lambda k: (sum(e[k]) / len(e[k])) if e[k] else None
-        rd, wr = mean("dram_rd"), mean("dram_wr")
+    for name, launches in per.items():
+        # the polyfit kernels run once per round on shrinking (or, for the downdate, much smaller) lists: the facts are
+        # those of the LONGEST launch in the capture (round 1), which is the launch bench.py's stage line describes
+        e = max(launches, key=lambda row: row.get("time_ns", 0.0))
+        rd, wr = e.get("dram_rd"), e.get("dram_wr")
         facts[name] = {
-            "launches_in_capture": n,
-            "ms_under_ncu": (mean("time_ns") or 0.0) / 1e6,
+            "launches_in_capture": len(launches),
+            "ms_under_ncu": e.get("time_ns", 0.0) / 1e6,
             "dram_bytes_per_launch": (rd + wr) if rd is not None and wr is not None else None,
             "dram_read_bytes_per_launch": rd, "dram_write_bytes_per_launch": wr,
-            "fp64_pipe_pct": mean("fp64"), "issue_slot_pct": mean("issue"), "dram_throughput_pct": mean("dram_pct"),
-            "registers": mean("regs"), "warps_active_pct": mean("warps"),
-            "source": "ncu --set full --clock-control none, %s" % label,
+            "fp64_pipe_pct": e.get("fp64"), "issue_slot_pct": e.get("issue"), "dram_throughput_pct": e.get("dram_pct"),
+            "registers": e.get("regs"), "warps_active_pct": e.get("warps"),
+            "source": "ncu --set full --clock-control none, %s (longest launch of the kernel in the capture)" % label,
         }
     path = os.path.join(ROOT, "profiles", "ncu_facts.json")
     try:
