@@ -22,6 +22,11 @@
 // parabola's vertex (two multiplications per pixel instead of a 12-operation exp, three seed exps per thread): 42.1 ms
 // against 41.9 ms per 100k stars and the 1e-12 cost parity lost -- the kernel is bound by dependent-operation latency in
 // the pixel passes and by the master / worker hand-offs, not by its FP64 operation count.
+// Also measured and dropped: the pairs of the symmetric pass A with their profile values kept in REGISTERS across the
+// barrier and pass B walking the same pairs (no plane stores / loads, one set of moment updates per pair: ~30 % fewer
+// instructions in the pixel passes on paper): 49.2 ms against 37.7 ms per 100k stars -- eight live doubles per thread
+// across the barrier and the fully unrolled guarded pair loop cost more than the plane traffic they replace, and merely
+// compiling that path in slowed the plane path to 42.8 ms (register allocation of the shared worker loop).
 #include <cstdlib>
 #include <type_traits>
 #include "common.cuh"
