@@ -1090,18 +1090,16 @@ static int poly_cfg() {
 // SHOPT_POLY_RING: bit 0 = normal_ring_kernel, bit 1 = mse_ring_kernel (default 3: both; 0 = the plain-load kernels).
 // Measured on the bench workload (87k x 131 x 131, K = 10): normal 3.01 -> 1.99 ms (61 % -> 92 % of the measured copy
 // bandwidth), mse 3.43 -> 2.17 ms (53 % -> 84 %); K = 21 (5.4k x 301 x 301): 1.55 -> 1.21 and 1.91 -> 1.69 ms.
-static int poly_ring() {
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("SHOPT_POLY_RING"); v = e ? atoi(e) : 3; }
-    return v;
+static int poly_ring() {           // read per launch: the parity tests compare both forms in one process
+    const char *e = getenv("SHOPT_POLY_RING");
+    return e ? atoi(e) : 3;
 }
 // Four pixels per thread for 10 < K <= 21 as well (84 accumulators at K = 21, two CTAs per SM: the ring keeps the loads in
 // flight whatever the occupancy, and a basis value read from shared memory feeds four FMAs instead of two).  Measured at
 // K = 21 (5.4k x 301 x 301): normal 1.21 -> 1.13 ms, mse 1.69 -> 1.31 ms.  SHOPT_POLY_PX4=0 goes back to two pixels.
 static int poly_px4() {
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("SHOPT_POLY_PX4"); v = e ? atoi(e) : 1; }
-    return v;
+    const char *e = getenv("SHOPT_POLY_PX4");
+    return e ? atoi(e) : 1;
 }
 static int poly_px(int K, int cfg) {
     const int base = (K <= 10) ? 4 : (K <= 21 ? 2 : 1);

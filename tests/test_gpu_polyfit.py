@@ -109,6 +109,49 @@ def test_building_blocks_shard_additively(stage):
     assert torch.equal(acc_of(idx), whole)                            # deterministic: no floating-point atomics
 
 
+@pytest.mark.parametrize("degree,N,r,c", [(3, 1500, 37, 35), (5, 900, 41, 43), (1, 700, 9, 7), (7, 600, 17, 19)])
+def test_ring_kernels_equal_the_plain_load_kernels_bit_for_bit(monkeypatch, degree, N, r, c):
+    """normal_ring_kernel / mse_ring_kernel (per-lane cp.async rings, the default) perform the arithmetic of normal_kernel /
+    mse_kernel in the same order: [V'V | V'P] and the per-star errors are bit-identical with SHOPT_POLY_RING=0 and 3, on
+    list lengths that are no multiple of the 64-star refill or of the ring depth, ragged pixel tiles and NaN values.
+    Pixels per thread (SHOPT_POLY_PX4, 10 < K <= 21) regroup the star chunks and the per-star pixel sums: rounding only."""
+    import ctypes as C
+    import torch
+    from shopt_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator(device="cuda").manual_seed(degree)
+    pgf = torch.rand(N, c, r, generator=g, device="cuda", dtype=torch.float64)
+    pgf[5, 3, 2] = float("nan")
+    u = torch.rand(N, generator=g, device="cuda", dtype=torch.float64) * 2 - 1
+    v = torch.rand(N, generator=g, device="cuda", dtype=torch.float64) * 2 - 1
+    K = (degree + 1) * (degree + 2) // 2
+    poly = torch.rand(K, c, r, generator=g, device="cuda", dtype=torch.float64)
+    n_acc = L.shopt_polyfit_acc_len(r, c, degree)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def run(idx, ring, px4="1"):
+        monkeypatch.setenv("SHOPT_POLY_RING", ring)
+        monkeypatch.setenv("SHOPT_POLY_PX4", px4)
+        acc = torch.empty(n_acc, device="cuda", dtype=torch.float64)
+        mse = torch.empty(len(idx), device="cuda", dtype=torch.float64)
+        _lib.check(L.shopt_polyfit_normal_dev(pgf.data_ptr(), r, c, u.data_ptr(), v.data_ptr(), idx.data_ptr(), len(idx),
+                                              degree, None, acc.data_ptr(), st))
+        _lib.check(L.shopt_polyfit_mse_dev(pgf.data_ptr(), r, c, u.data_ptr(), v.data_ptr(), idx.data_ptr(), len(idx),
+                                           degree, poly.data_ptr(), mse.data_ptr(), st))
+        torch.cuda.synchronize()
+        return acc.cpu().numpy(), mse.cpu().numpy()
+
+    for n in (N - 3, 131, 64, 9, 1):
+        idx = torch.randperm(N, generator=g, device="cuda")[:n].contiguous()
+        acc_r, mse_r = run(idx, "3", px4="0")                                    # same tiling in both forms
+        acc_p, mse_p = run(idx, "0", px4="0")
+        assert np.array_equal(acc_r, acc_p, equal_nan=True)
+        assert np.array_equal(mse_r, mse_p, equal_nan=True)
+        acc_4, mse_4 = run(idx, "3", px4="1")                                    # the default
+        assert np.allclose(acc_4, acc_r, rtol=1e-12, atol=1e-12, equal_nan=True)     # other tile: other star chunks
+        assert np.allclose(mse_4, mse_r, rtol=1e-13, atol=0, equal_nan=True)
+
+
 @pytest.mark.parametrize("degree,N,r,c", [(1, 301, 9, 7), (3, 500, 13, 13), (2, 1000, 21, 19)])
 def test_median_constraint(stage, orc, degree, N, r, c):
     """interpolate.jl:118-124, 139-141: coefficient 1 = per-pixel median over the training stars (radix select on the
