@@ -50,15 +50,11 @@ def test_bench_line_contract(path):
 
 def test_ncu_facts_parses_the_committed_export(tmp_path):
     src = os.path.join(ROOT, "profiles", "r02_ncu_full_c3_raw.csv")
-    facts_path = os.path.join(ROOT, "profiles", "ncu_facts.json")
-    before = open(facts_path).read()
-    try:
-        out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_facts.py"), src, "c3"],
-                             capture_output=True, text=True, check=True).stdout
-        facts = json.load(open(facts_path))["c3"]
-    finally:
-        with open(facts_path, "w") as f:                      # the committed file stays as it was
-            f.write(before)
+    facts_path = str(tmp_path / "ncu_facts.json")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_facts.py"), src, "c3"], capture_output=True,
+                         text=True, check=True, env=dict(os.environ, NCU_FACTS_OUT=facts_path)).stdout
+    facts = json.load(open(facts_path))["c3"]
+    assert facts == json.load(open(os.path.join(ROOT, "profiles", "ncu_facts.json")))["c3"]   # the committed facts are these
     assert "fit_kernel" in out
     for k in ("fit_kernel", "pca_power_kernel", "normal_ring_kernel", "mse_ring_kernel"):
         assert facts[k]["dram_bytes_per_launch"] > 0 and facts[k]["ms_under_ncu"] > 0

@@ -75,7 +75,7 @@ def main():
             "registers": e.get("regs"), "warps_active_pct": e.get("warps"),
             "source": "ncu --set full --clock-control none, %s (longest launch of the kernel in the capture)" % label,
         }
-    path = os.path.join(ROOT, "profiles", "ncu_facts.json")
+    path = os.environ.get("NCU_FACTS_OUT") or os.path.join(ROOT, "profiles", "ncu_facts.json")   # the tests write elsewhere
     try:
         with open(path) as f:
             allf = json.load(f)
